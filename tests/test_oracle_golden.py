@@ -1,0 +1,86 @@
+"""CPU: pin the oracle against the golden vectors produced by the reference's own code
+(tests/golden/make_golden.py) — SURVEY.md §8(c)."""
+import numpy as np
+import pytest
+
+from conftest import synth_image
+from lumen_b200.vit_config import OPENAI_MEAN, OPENAI_STD, VIT_CONFIGS, synthetic_weights
+from oracle import clip_oracle as O
+
+
+def test_resize_squash_bit_exact(golden_pre):
+    for n, (seed, h, w, S) in enumerate(golden_pre["cases"]):
+        img = synth_image(int(seed), int(h), int(w))
+        _, u8 = O.preprocess(img, int(S), mode=0, return_u8=True)
+        assert np.array_equal(u8, golden_pre[f"squash_u8_{n}"]), f"case {n}"
+
+
+def test_resize_crop_bit_exact(golden_pre):
+    for n, (seed, h, w, S) in enumerate(golden_pre["cases"]):
+        img = synth_image(int(seed), int(h), int(w))
+        _, u8 = O.preprocess(img, int(S), mode=1, return_u8=True)
+        assert np.array_equal(u8, golden_pre[f"crop_u8_{n}"]), f"case {n}"
+
+
+def test_closure_float_bit_exact(golden_pre):
+    hit = 0
+    for n, (seed, h, w, S) in enumerate(golden_pre["cases"]):
+        key = f"closure_f32_{n}"
+        if key in golden_pre.files:
+            out = O.preprocess(synth_image(int(seed), int(h), int(w)), int(S), mode=0)
+            assert np.array_equal(out, golden_pre[key])
+            hit += 1
+    assert hit >= 2
+
+
+def test_live_pillow_agrees():
+    Image = pytest.importorskip("PIL.Image")
+    for seed, (h, w, oh, ow) in enumerate([(61, 47, 33, 90), (200, 300, 224, 224), (17, 1000, 224, 224), (224, 225, 224, 224)]):
+        img = synth_image(100 + seed, h, w)
+        want = np.asarray(Image.fromarray(img, "RGB").resize((ow, oh), Image.Resampling.BICUBIC))
+        assert np.array_equal(O.resize_bicubic(img, oh, ow), want)
+
+
+def test_classify_matches_reference(golden_cls):
+    text = np.random.default_rng(7).standard_normal((1000, 512)).astype(np.float32)
+    scene = np.random.default_rng(8).standard_normal((8, 512)).astype(np.float32)
+    for r, q in enumerate(golden_cls["queries"]):
+        idx, p = O.classify(q, text, top_k=5)
+        assert np.array_equal(idx, golden_cls["cls_idx"][r])
+        np.testing.assert_allclose(p, golden_cls["cls_p"][r], rtol=1e-5, atol=1e-7)
+        si, sp = O.classify_scene(q, scene)
+        assert si == golden_cls["scene_idx"][r]
+        assert abs(sp - golden_cls["scene_p"][r]) < 1e-6
+
+
+def test_topk_matches_reference(golden_cls):
+    g = np.random.default_rng(10).standard_normal((5000, 512)).astype(np.float32)
+    g /= np.linalg.norm(g, axis=1, keepdims=True)
+    s, i = O.topk_cosine(golden_cls["queries"], g, 10, chunk=1024)
+    assert np.array_equal(i, golden_cls["bio_idx"])
+    np.testing.assert_allclose(s, golden_cls["bio_s"], rtol=0, atol=2e-6)
+
+
+def test_topk_tie_order_and_merge():
+    g = np.zeros((40, 8), np.float32)
+    g[:, 0] = np.array([3, 1, 3, 2, 3] * 8)                      # many exact ties
+    q = np.zeros((2, 8), np.float32); q[:, 0] = [1, -1]
+    s, i = O.topk_cosine(q, g, 6, chunk=7)
+    assert i[0].tolist() == [0, 2, 4, 5, 7, 9] and i[1].tolist() == [1, 6, 11, 16, 21, 26]
+    parts = [O.topk_cosine(q, g[lo:lo + 10], 6, index_base=lo) for lo in range(0, 40, 10)]
+    ms, mi = O.merge_topk([p[0] for p in parts], [p[1] for p in parts], 6)
+    assert np.array_equal(mi, i) and np.array_equal(ms, s)
+    s2, i2 = O.topk_cosine(q, g[:4], 6)                           # fewer rows than k -> padded
+    assert i2[0].tolist() == [0, 2, 3, 1, -1, -1] and np.isneginf(s2[0, 4:]).all()
+
+
+@pytest.mark.parametrize("name", ["ViT-tiny-test", "ViT-B-32"])
+def test_encoder_matches_transformers(golden_enc, name):
+    cfg = VIT_CONFIGS[name]
+    w = synthetic_weights(cfg, seed=0)
+    px = np.random.default_rng(11).standard_normal((4, 3, cfg["image_size"], cfg["image_size"])).astype(np.float32)
+    emb = O.vit_encode(w, px, cfg, normalize=False)
+    want = golden_enc[f"{name}/image_embeds"]
+    np.testing.assert_allclose(emb, want, rtol=2e-4, atol=2e-4)
+    cos = np.sum(O.l2_normalize(emb) * O.l2_normalize(want), axis=1)
+    assert cos.min() > 0.999999

@@ -1,0 +1,134 @@
+/*
+ * libb200clip — C ABI of the B200-native lumen-clip image path.
+ *
+ * The reference (EdwinZhanCN/Lumen) is pure Python and has no FFI of its own; these entry points are what
+ * a ctypes binding for its backend seam needs.  Each declaration cites the reference interface it stands
+ * behind (paths relative to packages/lumen-clip/src/lumen_clip/).  See INTEGRATION.md for the binding.
+ *
+ * Conventions
+ *   - every function returns 0 on success or a negative code (B200CLIP_E*); the message of the last failure
+ *     on the calling thread is available from b200clip_last_error();
+ *   - the caller owns every buffer it passes (PyTorch allocates device tensors and hands over data_ptr());
+ *     the library owns only what lives inside a handle: weights, activations workspace, resize tables,
+ *     search scratch;
+ *   - `stream` is a cudaStream_t passed as void* (NULL = the legacy default stream); calls only enqueue work
+ *     unless stated otherwise; one handle per GPU; calls on one handle are serialised by an internal mutex,
+ *     so the 10 gRPC worker threads of the reference server (server.py:294-297) may share it;
+ *   - there is no CPU fallback: without a CUDA device b200clip_create fails.
+ */
+#ifndef B200CLIP_H
+#define B200CLIP_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B200CLIP_OK        0
+#define B200CLIP_EINVAL   -1   /* bad argument                       */
+#define B200CLIP_ECUDA    -2   /* CUDA runtime / driver error        */
+#define B200CLIP_ESTATE   -3   /* wrong call order, missing weights  */
+#define B200CLIP_EDEVICE  -4   /* no usable sm_100 device            */
+#define B200CLIP_EKERNEL  -5   /* device-side watchdog tripped       */
+
+typedef struct b200clip_handle b200clip_handle;
+
+/* Model + preprocessing description: what ModelResources provides (resources/loader.py:80-139) plus the
+ * ViT shape.  layers == 0 builds a handle without an encoder (preprocess / classify / search only). */
+typedef struct b200clip_config {
+    int32_t device;          /* CUDA ordinal */
+    int32_t image_size;      /* S: get_image_size() */
+    int32_t patch;           /* P */
+    int32_t width;           /* d */
+    int32_t layers;          /* L */
+    int32_t heads;
+    int32_t mlp_dim;
+    int32_t embed_dim;       /* D */
+    int32_t activation;      /* 0 = QuickGELU (OpenAI / HF weights), 1 = exact GELU (LAION open_clip weights) */
+    int32_t max_batch;       /* images per encoder pass; larger requests are chunked internally */
+    float   ln_eps;
+    float   mean[3];         /* get_normalization_stats() */
+    float   std[3];
+} b200clip_config;
+
+/* lifecycle: BaseClipBackend.initialize()/close(), backends/base.py:126-134 */
+int  b200clip_create(const b200clip_config* cfg, b200clip_handle** out);
+void b200clip_destroy(b200clip_handle* h);
+const char* b200clip_last_error(void);
+/* Synchronise `stream` and report a tripped device-side watchdog (B200CLIP_EKERNEL). */
+int  b200clip_sync(b200clip_handle* h, void* stream);
+
+/* Weight upload — replaces ort.InferenceSession(vision.onnx) / CLIPModel.from_pretrained
+ * (backends/onnxrt_backend.py:166-170, backends/torch_backend.py:290-295).  `name` is a transformers key of the
+ * vision tower (vision_model.embeddings.patch_embedding.weight, ...encoder.layers.N.self_attn.q_proj.weight,
+ * visual_projection.weight, ...); data is host float32, C-contiguous.  q/k/v are fused and everything the GEMMs
+ * read is cast to bf16 on upload. */
+int b200clip_load_weight(b200clip_handle* h, const char* name, const float* host_data, const int64_t* shape, int32_t ndim);
+/* Verifies that every tensor of the configured tower has been loaded. */
+int b200clip_finalize_weights(b200clip_handle* h);
+
+/* K1 — preprocess: the closure at backends/onnxrt_backend.py:410-431 (mode 0, squash) and the open_clip transform of
+ * backends/torch_backend.py:201-204 (mode 1, shortest side + centre crop), on decoded uint8 RGB.
+ *   src_dev      packed HWC images in device memory, 16-byte aligned, 16 spare bytes after the last image
+ *   offsets      host array [B]: byte offset of each image inside src_dev (multiples of 16)
+ *   hw           host array [B][2]: height, width
+ *   out_dev      layout 0: [B,3,S,S]; layout 1: patch-major [B*(S/P)^2, kpad] with kpad = 3*P*P rounded up to 64
+ *   out_bf16     0 = float32 output, 1 = bfloat16 output */
+int b200clip_preprocess(b200clip_handle* h, const uint8_t* src_dev, const int64_t* offsets, const int32_t* hw,
+                        int32_t B, int32_t mode, int32_t layout, int32_t out_bf16, void* out_dev, void* stream);
+
+/* E1+E2 — encoder + L2 normalise: sess_vision.run + embedding/||embedding|| (backends/onnxrt_backend.py:485-489,
+ * 541-546).  patches_dev is the bf16 patch-major output of b200clip_preprocess(layout 1); emb_dev is float32 [B,D]
+ * unit vectors.  B may exceed max_batch (chunked). */
+int b200clip_encode(b200clip_handle* h, const void* patches_dev, int32_t B, float* emb_dev, void* stream);
+
+/* E3 — image_batch_to_vectors on decoded images already in device memory (backends/onnxrt_backend.py:497-551):
+ * preprocess -> encode -> normalise in one call. */
+int b200clip_embed_u8(b200clip_handle* h, const uint8_t* src_dev, const int64_t* offsets, const int32_t* hw,
+                      int32_t B, int32_t mode, float* emb_dev, void* stream);
+
+/* The same from HOST buffers (the call a Python backend makes): copies `src_host` (packed like src_dev,
+ * total_bytes long, ideally pinned) to the device, runs embed_u8, copies [B,D] float32 back into emb_host and
+ * synchronises. */
+int b200clip_embed_host(b200clip_handle* h, const uint8_t* src_host, int64_t total_bytes, const int64_t* offsets,
+                        const int32_t* hw, int32_t B, int32_t mode, float* emb_host, void* stream);
+
+/* Label / gallery upload for classify: replaces ModelResources.label_embeddings (resources/loader.py:366); rows are
+ * L2-normalised once on the device (general_clip/clip_model.py:289-291 does it per call). slot 0 = labels, 1 = scenes. */
+int b200clip_set_labels(b200clip_handle* h, int32_t slot, const float* host_labels, int32_t N, int32_t D, void* stream);
+
+/* K11 — CLIPModelManager.classify_image / classify_scene (general_clip/clip_model.py:274-315, 341-357) for a batch of
+ * image embeddings in device memory: cosine, optional softmax(scale * s), top-k (value desc, index asc).
+ * out_values float32 [B,k], out_index int64 [B,k] (device). */
+int b200clip_classify(b200clip_handle* h, int32_t slot, const float* emb_dev, int32_t B, float scale, int32_t softmax,
+                      int32_t k, float* out_values_dev, int64_t* out_index_dev, void* stream);
+
+/* K10 — BioCLIPModelManager.classify_image's search (expert_bioclip/bioclip_model.py:313-316), batched:
+ * top-k of queries . gallery^T over this GPU's gallery shard, score descending / index ascending.
+ * queries fp16 [Q,D], gallery fp16 [N,D] (device, row-major, D % 64 == 0, 16-byte aligned), k <= 768.
+ * out_scores float32 [Q,k], out_index int64 [Q,k] = index_base + local row; empty slots are (-inf, -1).
+ * Scratch lives in the handle and grows on demand (cudaMalloc on the first call of a given size). */
+int b200clip_topk(b200clip_handle* h, const void* queries_f16_dev, int32_t Q, const void* gallery_f16_dev, int64_t N,
+                  int32_t D, int32_t k, int64_t index_base, float* out_scores_dev, int64_t* out_index_dev, void* stream);
+
+/* K12 — merge `parts` candidate lists (scores float32 [parts][Q][k], index int64 [parts][Q][k], e.g. the result of an
+ * NCCL all-gather of every GPU's b200clip_topk output) into the global top-k with the same total order. */
+int b200clip_merge_topk(b200clip_handle* h, const float* part_scores_dev, const int64_t* part_index_dev, int32_t parts,
+                        int32_t Q, int32_t k, float* out_scores_dev, int64_t* out_index_dev, void* stream);
+
+/* Building blocks exported for the parity tests (same kernels the calls above use). */
+int b200clip_gemm_bf16(b200clip_handle* h, const void* A_bf16_dev, const void* W_bf16_dev, int32_t M, int32_t N, int32_t K,
+                       const float* bias_dev, void* out_dev, int32_t epilogue, int32_t activation, void* stream);
+int b200clip_attention(b200clip_handle* h, const void* qkv_bf16_dev, void* out_bf16_dev, int32_t B, int32_t S,
+                       int32_t width, int32_t heads, void* stream);
+int b200clip_layernorm(b200clip_handle* h, const float* x_dev, const float* gamma_dev, const float* beta_dev,
+                       void* out_bf16_dev, int32_t rows, int32_t width, float eps, void* stream);
+
+/* Introspection used by bench.py: kernels launched by this handle so far. */
+int64_t b200clip_launch_count(b200clip_handle* h);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200CLIP_H */

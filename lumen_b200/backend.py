@@ -1,0 +1,182 @@
+"""B200ClipBackend — the drop-in for lumen-clip's backend seam.
+
+Mirrors `BaseClipBackend` (reference: packages/lumen-clip/src/lumen_clip/backends/base.py:91-292) with the
+behaviour of the reference's ONNX backend (backends/onnxrt_backend.py:465-551): encoded image bytes in,
+unit-normalised float32 NumPy out, `InvalidInputError` on empty bytes, every other failure wrapped in
+`InferenceError`, `RuntimeError` when used before `initialize()`.  Decode (PIL) stays on the host; resize,
+normalise, the ViT tower and the L2 normalisation run in libb200clip on the GPU.  There is no CPU path."""
+from __future__ import annotations
+
+import io
+import threading
+from collections.abc import Sequence
+from dataclasses import dataclass, field
+from typing import Any
+
+import numpy as np
+
+from .engine import MODE_SHORTEST_CROP, MODE_SQUASH, Engine
+from .interface import (BackendInfo, BaseClipBackend, InferenceError, InvalidInputError, ModelLoadingError)
+from .vit_config import OPENAI_MEAN, OPENAI_STD, VIT_CONFIGS
+
+__all__ = ["B200ClipBackend", "SyntheticResources"]
+
+
+@dataclass
+class SyntheticResources:
+    """Stand-in for `ModelResources` (resources/loader.py:36-139) when no model directory exists: the same
+    accessors the backend and the model managers use."""
+    model_name: str = "ViT-B-32"
+    runtime: str = "b200"
+    config: dict[str, Any] = field(default_factory=dict)
+    labels: np.ndarray | None = None
+    label_embeddings: np.ndarray | None = None
+    weights: dict[str, np.ndarray] | None = None
+
+    def get_image_size(self):
+        s = self.config.get("image_size") or VIT_CONFIGS[self.model_name]["image_size"]
+        return (s, s) if isinstance(s, int) else (int(s[0]), int(s[1]))
+
+    def get_normalization_stats(self):
+        pc = self.config.get("preprocess_cfg") or {}
+        return {"mean": list(pc.get("mean", OPENAI_MEAN)), "std": list(pc.get("std", OPENAI_STD))}
+
+    def get_embedding_dim(self) -> int:
+        return VIT_CONFIGS[self.model_name]["embed_dim"]
+
+    def has_classification_support(self) -> bool:
+        return self.labels is not None
+
+
+def _vit_config_for(resources) -> dict:
+    cfg = getattr(resources, "config", {}) or {}
+    name = getattr(resources, "model_name", "")
+    if "b200_vit" in cfg:
+        return dict(cfg["b200_vit"])
+    for key in (name, name.replace("_", "-")):
+        if key in VIT_CONFIGS:
+            return dict(VIT_CONFIGS[key])
+    vc = cfg.get("vision_cfg")
+    if isinstance(vc, dict) and {"width", "layers", "patch_size"} <= set(vc):
+        d = int(vc["width"])
+        return dict(image_size=int(vc.get("image_size", 224)), patch=int(vc["patch_size"]), width=d, layers=int(vc["layers"]),
+                    heads=d // 64, mlp_dim=int(d * vc.get("mlp_ratio", 4.0)), embed_dim=int(cfg.get("embed_dim", 512)),
+                    activation="quick_gelu" if cfg.get("quick_gelu") else "gelu", ln_eps=1e-5)
+    raise ModelLoadingError(f"no ViT shape known for model '{name}'")
+
+
+class B200ClipBackend(BaseClipBackend):
+    def __init__(self, resources, device_preference: str | None = None, max_batch_size: int | None = None,
+                 weights: dict[str, np.ndarray] | None = None, preprocess_mode: str = "squash",
+                 text_backend: BaseClipBackend | None = None) -> None:
+        super().__init__(resources, device_preference, max_batch_size)
+        self._weights = weights if weights is not None else getattr(resources, "weights", None)
+        self._mode = MODE_SQUASH if preprocess_mode == "squash" else MODE_SHORTEST_CROP
+        self._text = text_backend
+        self._engine: Engine | None = None
+        self._lock = threading.Lock()          # the reference server calls from 10 threads (server.py:294-297)
+        self._device_index = 0
+        if device_preference and ":" in device_preference:
+            self._device_index = int(device_preference.split(":")[1])
+
+    # ---------------------------------------------------------------- lifecycle
+    def initialize(self) -> None:
+        if self._initialized:
+            return
+        try:
+            cfg = _vit_config_for(self.resources)
+            size = self.resources.get_image_size()
+            if size is not None:
+                if size[0] != size[1]:
+                    raise ModelLoadingError("non-square model input sizes are not supported")
+                cfg["image_size"] = int(size[0])
+            stats = self.resources.get_normalization_stats()
+            if self._weights is None:
+                raise ModelLoadingError("no vision-tower weights supplied (pass weights= or resources.weights)")
+            self._engine = Engine(cfg, device=self._device_index, max_batch=self._max_batch_size or 512,
+                                  mean=stats["mean"], std=stats["std"])
+            self._engine.load_weights(self._weights)
+            self._cfg = cfg
+            self._initialized = True
+        except ModelLoadingError:
+            raise
+        except Exception as e:  # noqa: BLE001
+            raise ModelLoadingError(f"B200 model loading failed: {e}") from e
+
+    def close(self) -> None:
+        if self._engine is not None:
+            self._engine.close()
+            self._engine = None
+        self._initialized = False
+
+    def _ensure_initialized(self) -> None:
+        if not self._initialized or self._engine is None:
+            raise RuntimeError("B200ClipBackend is not initialized. Call initialize() first.")
+
+    # ---------------------------------------------------------------- images
+    @staticmethod
+    def _decode(image_bytes: bytes) -> np.ndarray:
+        from PIL import Image
+        return np.asarray(Image.open(io.BytesIO(image_bytes)).convert("RGB"))
+
+    def embed_arrays(self, images: Sequence[np.ndarray]) -> np.ndarray:
+        """Batched entry on decoded uint8 HWC images (the reference's metric excludes decode)."""
+        self._ensure_initialized()
+        try:
+            with self._lock:
+                return self._engine.embed_host(images, self._mode)
+        except Exception as e:  # noqa: BLE001
+            raise InferenceError(f"Batch image encoding failed: {e}") from e
+
+    def image_to_vector(self, image_bytes: bytes) -> np.ndarray:
+        self._ensure_initialized()
+        if not image_bytes:
+            raise InvalidInputError("image_bytes cannot be empty")
+        try:
+            with self._lock:
+                return self._engine.embed_host([self._decode(image_bytes)], self._mode)[0]
+        except Exception as e:  # noqa: BLE001
+            raise InferenceError(f"Image encoding failed: {e}") from e
+
+    def image_batch_to_vectors(self, images: Sequence[bytes]) -> np.ndarray:
+        if not images:
+            return np.empty((0, 0), dtype=np.float32)       # onnxrt_backend.py:499-500
+        self._ensure_initialized()
+        try:
+            decoded = []
+            for b in images:
+                if not b:
+                    raise InvalidInputError("image bytes cannot be empty")
+                decoded.append(self._decode(b))
+            with self._lock:
+                return self._engine.embed_host(decoded, self._mode)
+        except Exception as e:  # noqa: BLE001
+            raise InferenceError(f"Batch image encoding failed: {e}") from e
+
+    # ---------------------------------------------------------------- text (out of scope: delegated or refused)
+    def text_to_vector(self, text: str) -> np.ndarray:
+        if self._text is not None:
+            return self._text.text_to_vector(text)
+        raise InferenceError("Text encoding failed: the B200 backend accelerates the image path only; "
+                             "supply precomputed label embeddings or a text_backend")
+
+    def text_batch_to_vectors(self, texts: Sequence[str]) -> np.ndarray:
+        if self._text is not None:
+            return self._text.text_batch_to_vectors(texts)
+        raise InferenceError("Batch text encoding failed: the B200 backend accelerates the image path only")
+
+    # ---------------------------------------------------------------- metadata
+    def get_info(self) -> BackendInfo:
+        size = self.resources.get_image_size()
+        dim = _vit_config_for(self.resources)["embed_dim"]
+        return BackendInfo(runtime="b200", device=f"cuda:{self._device_index}", model_id=self.resources.model_name,
+                           model_name=getattr(self.resources, "config", {}).get("model_name", self.resources.model_name),
+                           pretrained=None, version="libb200clip-0.1", image_embedding_dim=dim, text_embedding_dim=dim,
+                           precisions=["bf16"], max_batch_size=self._max_batch_size, supports_image_batch=True,
+                           extra={"image_size": f"{size[0]}x{size[1]}" if size else None,
+                                  "preprocess": "squash" if self._mode == MODE_SQUASH else "shortest+center_crop"})
+
+    @property
+    def engine(self) -> Engine:
+        self._ensure_initialized()
+        return self._engine

@@ -1,0 +1,448 @@
+// C ABI of libb200clip (declared in include/b200clip.h): handle, weight upload, and the orchestration of
+// the kernels in preprocess.cu / gemm_tc.cu / vit_ops.cu / topk.cu / classify.cu.
+#include "../../include/b200clip.h"
+#include "common.cuh"
+#include "kernels.h"
+
+#include <cstring>
+#include <mutex>
+#include <set>
+#include <string>
+#include <vector>
+
+namespace b200 {
+
+static thread_local std::string g_last_error;
+void set_error(const std::string& msg) { g_last_error = msg; }
+int fail(int code, const std::string& msg) { g_last_error = msg; return code; }
+
+// fp32 [rows, cols] -> bf16 rows of pitch ld (destination padding, if any, stays zero)
+__global__ void f32_to_bf16_rows(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, long long rows, int cols, int ld) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= rows * cols) return;
+    const long long r = i / cols; const int c = (int)(i - r * cols);
+    dst[r * ld + c] = __float2bfloat16(src[i]);
+}
+
+struct Layer {
+    __nv_bfloat16 *w_qkv = nullptr, *w_o = nullptr, *w_fc1 = nullptr, *w_fc2 = nullptr;
+    float *b_qkv = nullptr, *b_o = nullptr, *b_fc1 = nullptr, *b_fc2 = nullptr;
+    float *ln1_g = nullptr, *ln1_b = nullptr, *ln2_g = nullptr, *ln2_b = nullptr;
+};
+
+}  // namespace b200
+
+using namespace b200;
+
+struct b200clip_handle {
+    b200clip_config cfg{};
+    std::mutex mu;
+    int n = 0, S = 0, kpad = 0;
+    std::vector<void*> allocs;
+    // weights
+    __nv_bfloat16 *w_patch = nullptr, *w_proj = nullptr;
+    float *cls = nullptr, *pos = nullptr, *pre_g = nullptr, *pre_b = nullptr, *post_g = nullptr, *post_b = nullptr;
+    std::vector<Layer> layers;
+    std::set<std::string> loaded;
+    float* upload_tmp = nullptr; size_t upload_cap = 0;
+    // activations workspace
+    __nv_bfloat16 *patches = nullptr, *hbuf = nullptr, *qkv = nullptr, *mlp = nullptr, *cls_ln = nullptr;
+    float *patch_out = nullptr, *xres = nullptr, *emb_raw = nullptr;
+    // host-buffer path staging
+    uint8_t* img_dev = nullptr; size_t img_cap = 0;
+    float* emb_dev = nullptr; size_t emb_cap = 0;
+    // classify label sets
+    float* labels[2] = {nullptr, nullptr}; int labels_n[2] = {0, 0}, labels_d[2] = {0, 0};
+    // search scratch
+    void* topk_scratch = nullptr; size_t topk_cap = 0;
+    PreprocessState* pre = nullptr;
+    DeviceStatus* status = nullptr;
+    int64_t launches = 0;
+
+    template <class T> int alloc(T** p, size_t count, bool zero = false) {
+        void* q = nullptr;
+        B200_CUDA_OK(cudaMalloc(&q, count * sizeof(T) + 256));
+        if (zero) B200_CUDA_OK(cudaMemset(q, 0, count * sizeof(T) + 256));
+        allocs.push_back(q);
+        *p = reinterpret_cast<T*>(q);
+        return B200_OK;
+    }
+};
+
+static int set_device(b200clip_handle* h) {
+    B200_REQUIRE(h != nullptr, "null handle");
+    B200_CUDA_OK(cudaSetDevice(h->cfg.device));
+    return B200_OK;
+}
+
+extern "C" const char* b200clip_last_error(void) { return g_last_error.c_str(); }
+
+extern "C" int b200clip_create(const b200clip_config* cfg, b200clip_handle** out) {
+    B200_REQUIRE(cfg && out, "create: null argument");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+        return fail(B200CLIP_EDEVICE, "no CUDA device: libb200clip has no CPU fallback");
+    B200_REQUIRE(cfg->device >= 0 && cfg->device < ndev, "create: device ordinal out of range");
+    cudaDeviceProp prop;
+    B200_CUDA_OK(cudaGetDeviceProperties(&prop, cfg->device));
+    if (prop.major != 10) return fail(B200CLIP_EDEVICE, std::string("device is sm_") + std::to_string(prop.major * 10 + prop.minor) +
+                                                        ", libb200clip is built for sm_100a only");
+    B200_REQUIRE(cfg->image_size > 0 && cfg->image_size % 2 == 0, "create: image_size must be positive and even");
+    for (int c = 0; c < 3; ++c) B200_REQUIRE(cfg->std[c] != 0.f, "create: std must be non-zero");
+    B200_CUDA_OK(cudaSetDevice(cfg->device));
+    auto* h = new b200clip_handle();
+    h->cfg = *cfg;
+    int rc = B200_OK;
+    h->pre = preprocess_state_create(cfg->mean, cfg->std, &rc);
+    if (!h->pre) { delete h; return rc; }
+    auto bail = [&](int code) { b200clip_destroy(h); return code; };
+    if ((rc = h->alloc(&h->status, 1, true))) return bail(rc);
+    if (cfg->layers > 0) {
+        const int d = cfg->width, P = cfg->patch, L = cfg->layers, mlp = cfg->mlp_dim, D = cfg->embed_dim;
+        if (!(P > 0 && P % 2 == 0 && cfg->image_size % P == 0)) return bail(fail(B200CLIP_EINVAL, "create: image_size must be a multiple of an even patch size"));
+        if (!(d % 128 == 0 && d <= 1024 && d == cfg->heads * 64)) return bail(fail(B200CLIP_EINVAL, "create: width must be heads*64, a multiple of 128, at most 1024"));
+        if (!(mlp % 64 == 0 && D > 0 && cfg->max_batch > 0)) return bail(fail(B200CLIP_EINVAL, "create: mlp_dim must be a multiple of 64; embed_dim and max_batch positive"));
+        h->n = (cfg->image_size / P) * (cfg->image_size / P);
+        h->S = h->n + 1;
+        h->kpad = (3 * P * P + 63) / 64 * 64;
+        const size_t Bm = cfg->max_batch, M = Bm * h->S, Mp = Bm * h->n;
+        h->layers.resize(L);
+#define A_(call) if ((rc = (call))) return bail(rc)
+        A_(h->alloc(&h->w_patch, (size_t)d * h->kpad, true));
+        A_(h->alloc(&h->w_proj, (size_t)D * d));
+        A_(h->alloc(&h->cls, d)); A_(h->alloc(&h->pos, (size_t)h->S * d));
+        A_(h->alloc(&h->pre_g, d)); A_(h->alloc(&h->pre_b, d)); A_(h->alloc(&h->post_g, d)); A_(h->alloc(&h->post_b, d));
+        for (auto& l : h->layers) {
+            A_(h->alloc(&l.w_qkv, (size_t)3 * d * d)); A_(h->alloc(&l.b_qkv, 3 * d));
+            A_(h->alloc(&l.w_o, (size_t)d * d)); A_(h->alloc(&l.b_o, d));
+            A_(h->alloc(&l.w_fc1, (size_t)mlp * d)); A_(h->alloc(&l.b_fc1, mlp));
+            A_(h->alloc(&l.w_fc2, (size_t)d * mlp)); A_(h->alloc(&l.b_fc2, d));
+            A_(h->alloc(&l.ln1_g, d)); A_(h->alloc(&l.ln1_b, d)); A_(h->alloc(&l.ln2_g, d)); A_(h->alloc(&l.ln2_b, d));
+        }
+        A_(h->alloc(&h->patches, Mp * h->kpad, true));     // K padding must read as zero
+        A_(h->alloc(&h->patch_out, Mp * d));
+        A_(h->alloc(&h->xres, M * d));
+        A_(h->alloc(&h->hbuf, M * d));
+        A_(h->alloc(&h->qkv, M * 3 * d));
+        A_(h->alloc(&h->mlp, M * mlp));
+        A_(h->alloc(&h->cls_ln, Bm * d));
+        A_(h->alloc(&h->emb_raw, Bm * D));
+#undef A_
+    }
+    *out = h;
+    return B200_OK;
+}
+
+extern "C" void b200clip_destroy(b200clip_handle* h) {
+    if (!h) return;
+    cudaSetDevice(h->cfg.device);
+    cudaDeviceSynchronize();
+    for (void* p : h->allocs) cudaFree(p);
+    cudaFree(h->upload_tmp); cudaFree(h->img_dev); cudaFree(h->emb_dev); cudaFree(h->topk_scratch);
+    cudaFree(h->labels[0]); cudaFree(h->labels[1]);
+    if (h->pre) preprocess_state_destroy(h->pre);
+    delete h;
+}
+
+extern "C" int b200clip_sync(b200clip_handle* h, void* stream) {
+    int rc = set_device(h); if (rc) return rc;
+    B200_CUDA_OK(cudaStreamSynchronize((cudaStream_t)stream));
+    DeviceStatus st;
+    B200_CUDA_OK(cudaMemcpy(&st, h->status, sizeof(st), cudaMemcpyDeviceToHost));
+    if (st.code != 0) {
+        cudaMemset(h->status, 0, sizeof(DeviceStatus));
+        return fail(B200CLIP_EKERNEL, "device watchdog: pipeline barrier never completed (site " + std::to_string(st.where) + ")");
+    }
+    return B200_OK;
+}
+
+extern "C" int64_t b200clip_launch_count(b200clip_handle* h) { return h ? h->launches : 0; }
+
+// ------------------------------------------------------------------------------------------ weights
+static int upload_f32(b200clip_handle* h, const float* host, size_t count, float** dev_tmp) {
+    if (count > h->upload_cap) {
+        cudaFree(h->upload_tmp); h->upload_tmp = nullptr; h->upload_cap = 0;
+        B200_CUDA_OK(cudaMalloc(&h->upload_tmp, count * sizeof(float)));
+        h->upload_cap = count;
+    }
+    B200_CUDA_OK(cudaMemcpy(h->upload_tmp, host, count * sizeof(float), cudaMemcpyHostToDevice));
+    *dev_tmp = h->upload_tmp;
+    return B200_OK;
+}
+static int put_bf16(b200clip_handle* h, const float* host, long long rows, int cols, __nv_bfloat16* dst, int ld) {
+    float* tmp; int rc = upload_f32(h, host, (size_t)rows * cols, &tmp); if (rc) return rc;
+    const long long total = rows * cols;
+    f32_to_bf16_rows<<<(unsigned)((total + 255) / 256), 256>>>(tmp, dst, rows, cols, ld);
+    B200_CUDA_OK(cudaGetLastError());
+    B200_CUDA_OK(cudaDeviceSynchronize());
+    return B200_OK;
+}
+static int put_f32(const float* host, size_t count, float* dst) {
+    B200_CUDA_OK(cudaMemcpy(dst, host, count * sizeof(float), cudaMemcpyHostToDevice));
+    return B200_OK;
+}
+
+extern "C" int b200clip_load_weight(b200clip_handle* h, const char* name, const float* data, const int64_t* shape, int32_t ndim) {
+    int rc = set_device(h); if (rc) return rc;
+    B200_REQUIRE(name && data && shape && ndim >= 1 && ndim <= 4, "load_weight: null argument or bad rank");
+    B200_REQUIRE(h->cfg.layers > 0, "load_weight: handle was created without an encoder (layers == 0)");
+    std::lock_guard<std::mutex> lk(h->mu);
+    const std::string nm(name);
+    const int d = h->cfg.width, P = h->cfg.patch, mlp = h->cfg.mlp_dim, D = h->cfg.embed_dim;
+    size_t count = 1;
+    for (int i = 0; i < ndim; ++i) count *= (size_t)shape[i];
+    auto want = [&](std::initializer_list<int64_t> s) {
+        if ((int)s.size() != ndim) return false;
+        int i = 0; for (int64_t v : s) if (shape[i++] != v) return false;
+        return true;
+    };
+#define SHAPE_(...) B200_REQUIRE(want({__VA_ARGS__}), "load_weight: wrong shape for " + nm)
+    const std::string E = "vision_model.embeddings.", LP = "vision_model.encoder.layers.";
+    if (nm == E + "class_embedding") { SHAPE_(d); rc = put_f32(data, count, h->cls); }
+    else if (nm == E + "patch_embedding.weight") { SHAPE_(d, 3, P, P); rc = put_bf16(h, data, d, 3 * P * P, h->w_patch, h->kpad); }
+    else if (nm == E + "position_embedding.weight") { SHAPE_(h->S, d); rc = put_f32(data, count, h->pos); }
+    else if (nm == "vision_model.pre_layrnorm.weight") { SHAPE_(d); rc = put_f32(data, count, h->pre_g); }
+    else if (nm == "vision_model.pre_layrnorm.bias") { SHAPE_(d); rc = put_f32(data, count, h->pre_b); }
+    else if (nm == "vision_model.post_layernorm.weight") { SHAPE_(d); rc = put_f32(data, count, h->post_g); }
+    else if (nm == "vision_model.post_layernorm.bias") { SHAPE_(d); rc = put_f32(data, count, h->post_b); }
+    else if (nm == "visual_projection.weight") { SHAPE_(D, d); rc = put_bf16(h, data, D, d, h->w_proj, d); }
+    else if (nm.compare(0, LP.size(), LP) == 0) {
+        const size_t dot = nm.find('.', LP.size());
+        B200_REQUIRE(dot != std::string::npos, "load_weight: malformed layer key " + nm);
+        const int li = std::atoi(nm.substr(LP.size(), dot - LP.size()).c_str());
+        B200_REQUIRE(li >= 0 && li < h->cfg.layers, "load_weight: layer index out of range in " + nm);
+        Layer& l = h->layers[li];
+        const std::string t = nm.substr(dot + 1);
+        const char* qkvn[3] = {"q_proj", "k_proj", "v_proj"};
+        bool done = false;
+        for (int j = 0; j < 3 && !done; ++j) {
+            if (t == std::string("self_attn.") + qkvn[j] + ".weight") { SHAPE_(d, d); rc = put_bf16(h, data, d, d, l.w_qkv + (size_t)j * d * d, d); done = true; }
+            else if (t == std::string("self_attn.") + qkvn[j] + ".bias") { SHAPE_(d); rc = put_f32(data, count, l.b_qkv + j * d); done = true; }
+        }
+        if (done) {}
+        else if (t == "self_attn.out_proj.weight") { SHAPE_(d, d); rc = put_bf16(h, data, d, d, l.w_o, d); }
+        else if (t == "self_attn.out_proj.bias") { SHAPE_(d); rc = put_f32(data, count, l.b_o); }
+        else if (t == "layer_norm1.weight") { SHAPE_(d); rc = put_f32(data, count, l.ln1_g); }
+        else if (t == "layer_norm1.bias") { SHAPE_(d); rc = put_f32(data, count, l.ln1_b); }
+        else if (t == "layer_norm2.weight") { SHAPE_(d); rc = put_f32(data, count, l.ln2_g); }
+        else if (t == "layer_norm2.bias") { SHAPE_(d); rc = put_f32(data, count, l.ln2_b); }
+        else if (t == "mlp.fc1.weight") { SHAPE_(mlp, d); rc = put_bf16(h, data, mlp, d, l.w_fc1, d); }
+        else if (t == "mlp.fc1.bias") { SHAPE_(mlp); rc = put_f32(data, count, l.b_fc1); }
+        else if (t == "mlp.fc2.weight") { SHAPE_(d, mlp); rc = put_bf16(h, data, d, mlp, l.w_fc2, mlp); }
+        else if (t == "mlp.fc2.bias") { SHAPE_(d); rc = put_f32(data, count, l.b_fc2); }
+        else return fail(B200CLIP_EINVAL, "load_weight: unknown tensor " + nm);
+    } else return fail(B200CLIP_EINVAL, "load_weight: unknown tensor " + nm);
+#undef SHAPE_
+    if (rc == B200_OK) h->loaded.insert(nm);
+    return rc;
+}
+
+extern "C" int b200clip_finalize_weights(b200clip_handle* h) {
+    B200_REQUIRE(h != nullptr, "null handle");
+    std::lock_guard<std::mutex> lk(h->mu);
+    const size_t want = 8 + 16 * (size_t)h->cfg.layers;
+    if (h->cfg.layers == 0 || h->loaded.size() != want)
+        return fail(B200CLIP_ESTATE, "finalize_weights: " + std::to_string(h->loaded.size()) + " of " + std::to_string(want) + " tensors loaded");
+    cudaFree(h->upload_tmp); h->upload_tmp = nullptr; h->upload_cap = 0;
+    return B200_OK;
+}
+
+// ------------------------------------------------------------------------------------------ preprocess / encode
+extern "C" int b200clip_preprocess(b200clip_handle* h, const uint8_t* src_dev, const int64_t* offsets, const int32_t* hw, int32_t B,
+                                   int32_t mode, int32_t layout, int32_t out_bf16, void* out_dev, void* stream) {
+    int rc = set_device(h); if (rc) return rc;
+    B200_REQUIRE((reinterpret_cast<uintptr_t>(src_dev) & 15) == 0, "preprocess: src_dev must be 16-byte aligned");
+    std::lock_guard<std::mutex> lk(h->mu);
+    const int P = h->cfg.patch;
+    const int kpad = P > 0 ? (3 * P * P + 63) / 64 * 64 : 0;
+    rc = preprocess_run(h->pre, src_dev, reinterpret_cast<const long long*>(offsets), hw, B, h->cfg.image_size, mode, layout,
+                        out_bf16, P, kpad, out_dev, (cudaStream_t)stream);
+    if (rc == B200_OK && B > 0) h->launches += 1;
+    return rc;
+}
+
+static int encode_chunk(b200clip_handle* h, const __nv_bfloat16* patches, int B, float* emb_out, cudaStream_t st) {
+    const b200clip_config& c = h->cfg;
+    const int d = c.width, S = h->S, M = B * S, Mp = B * h->n, mlp = c.mlp_dim, D = c.embed_dim;
+    int rc;
+#define R_(call) if ((rc = (call))) return rc
+    R_(gemm_bf16_tc(patches, h->kpad, h->w_patch, h->kpad, Mp, d, h->kpad, nullptr, h->patch_out, d, EPI_F32, 0, h->status, st));
+    R_(launch_embed_preln(h->patch_out, h->cls, h->pos, h->pre_g, h->pre_b, h->xres, B, S, d, c.ln_eps, st));
+    for (const Layer& l : h->layers) {
+        R_(launch_layernorm(h->xres, 1, l.ln1_g, l.ln1_b, h->hbuf, M, d, c.ln_eps, st));
+        R_(gemm_bf16_tc(h->hbuf, d, l.w_qkv, d, M, 3 * d, d, l.b_qkv, h->qkv, 3 * d, EPI_BIAS_BF16, 0, h->status, st));
+        R_(launch_attention(h->qkv, h->hbuf, B, S, d, c.heads, st));
+        R_(gemm_bf16_tc(h->hbuf, d, l.w_o, d, M, d, d, l.b_o, h->xres, d, EPI_BIAS_RES_F32, 0, h->status, st));
+        R_(launch_layernorm(h->xres, 1, l.ln2_g, l.ln2_b, h->hbuf, M, d, c.ln_eps, st));
+        R_(gemm_bf16_tc(h->hbuf, d, l.w_fc1, d, M, mlp, d, l.b_fc1, h->mlp, mlp, EPI_BIAS_ACT_BF16, c.activation, h->status, st));
+        R_(gemm_bf16_tc(h->mlp, mlp, l.w_fc2, mlp, M, d, mlp, l.b_fc2, h->xres, d, EPI_BIAS_RES_F32, 0, h->status, st));
+    }
+    R_(launch_layernorm(h->xres, S, h->post_g, h->post_b, h->cls_ln, B, d, c.ln_eps, st));
+    R_(gemm_bf16_tc(h->cls_ln, d, h->w_proj, d, B, D, d, nullptr, h->emb_raw, D, EPI_F32, 0, h->status, st));
+    R_(launch_l2_normalize(h->emb_raw, emb_out, B, D, st));
+#undef R_
+    h->launches += 5 + 7 * (int64_t)h->layers.size();
+    return B200_OK;
+}
+
+static int require_encoder(b200clip_handle* h) {
+    B200_REQUIRE(h->cfg.layers > 0, "handle has no encoder (layers == 0)");
+    if (h->loaded.size() != 8 + 16 * (size_t)h->cfg.layers)
+        return fail(B200CLIP_ESTATE, "encoder weights are not fully loaded (call b200clip_load_weight for every tensor)");
+    return B200_OK;
+}
+
+extern "C" int b200clip_encode(b200clip_handle* h, const void* patches_dev, int32_t B, float* emb_dev, void* stream) {
+    int rc = set_device(h); if (rc) return rc;
+    std::lock_guard<std::mutex> lk(h->mu);
+    if ((rc = require_encoder(h))) return rc;
+    B200_REQUIRE(B >= 0 && (B == 0 || (patches_dev && emb_dev)), "encode: null buffer");
+    const __nv_bfloat16* p = reinterpret_cast<const __nv_bfloat16*>(patches_dev);
+    for (int b0 = 0; b0 < B; b0 += h->cfg.max_batch) {
+        const int nb = std::min(h->cfg.max_batch, B - b0);
+        if ((rc = encode_chunk(h, p + (size_t)b0 * h->n * h->kpad, nb, emb_dev + (size_t)b0 * h->cfg.embed_dim, (cudaStream_t)stream))) return rc;
+    }
+    return B200_OK;
+}
+
+static int embed_u8_locked(b200clip_handle* h, const uint8_t* src_dev, const int64_t* offsets, const int32_t* hw, int B, int mode,
+                           float* emb_dev, cudaStream_t st) {
+    int rc;
+    if ((rc = require_encoder(h))) return rc;
+    B200_REQUIRE((reinterpret_cast<uintptr_t>(src_dev) & 15) == 0, "embed: src_dev must be 16-byte aligned");
+    for (int b0 = 0; b0 < B; b0 += h->cfg.max_batch) {
+        const int nb = std::min(h->cfg.max_batch, B - b0);
+        rc = preprocess_run(h->pre, src_dev, reinterpret_cast<const long long*>(offsets) + b0, hw + 2 * b0, nb, h->cfg.image_size, mode,
+                            /*layout*/ 1, /*bf16*/ 1, h->cfg.patch, h->kpad, h->patches, st);
+        if (rc) return rc;
+        h->launches += 1;
+        if ((rc = encode_chunk(h, h->patches, nb, emb_dev + (size_t)b0 * h->cfg.embed_dim, st))) return rc;
+    }
+    return B200_OK;
+}
+
+extern "C" int b200clip_embed_u8(b200clip_handle* h, const uint8_t* src_dev, const int64_t* offsets, const int32_t* hw, int32_t B,
+                                 int32_t mode, float* emb_dev, void* stream) {
+    int rc = set_device(h); if (rc) return rc;
+    std::lock_guard<std::mutex> lk(h->mu);
+    B200_REQUIRE(B >= 0 && (B == 0 || (src_dev && offsets && hw && emb_dev)), "embed_u8: null buffer");
+    return embed_u8_locked(h, src_dev, offsets, hw, B, mode, emb_dev, (cudaStream_t)stream);
+}
+
+extern "C" int b200clip_embed_host(b200clip_handle* h, const uint8_t* src_host, int64_t total_bytes, const int64_t* offsets,
+                                   const int32_t* hw, int32_t B, int32_t mode, float* emb_host, void* stream) {
+    int rc = set_device(h); if (rc) return rc;
+    std::lock_guard<std::mutex> lk(h->mu);
+    B200_REQUIRE(B >= 0 && total_bytes >= 0, "embed_host: negative size");
+    if (B == 0) return B200_OK;
+    B200_REQUIRE(src_host && offsets && hw && emb_host, "embed_host: null buffer");
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t need = (size_t)total_bytes + 64;
+    if (need > h->img_cap) {
+        B200_CUDA_OK(cudaStreamSynchronize(st));
+        cudaFree(h->img_dev); h->img_dev = nullptr; h->img_cap = 0;
+        B200_CUDA_OK(cudaMalloc(&h->img_dev, need + need / 4));
+        h->img_cap = need + need / 4;
+    }
+    const size_t eneed = (size_t)B * h->cfg.embed_dim;
+    if (eneed > h->emb_cap) {
+        B200_CUDA_OK(cudaStreamSynchronize(st));
+        cudaFree(h->emb_dev); h->emb_dev = nullptr; h->emb_cap = 0;
+        B200_CUDA_OK(cudaMalloc(&h->emb_dev, eneed * sizeof(float)));
+        h->emb_cap = eneed;
+    }
+    B200_CUDA_OK(cudaMemcpyAsync(h->img_dev, src_host, (size_t)total_bytes, cudaMemcpyHostToDevice, st));
+    if ((rc = embed_u8_locked(h, h->img_dev, offsets, hw, B, mode, h->emb_dev, st))) return rc;
+    B200_CUDA_OK(cudaMemcpyAsync(emb_host, h->emb_dev, eneed * sizeof(float), cudaMemcpyDeviceToHost, st));
+    B200_CUDA_OK(cudaStreamSynchronize(st));
+    DeviceStatus ds;
+    B200_CUDA_OK(cudaMemcpy(&ds, h->status, sizeof(ds), cudaMemcpyDeviceToHost));
+    if (ds.code != 0) {
+        cudaMemset(h->status, 0, sizeof(DeviceStatus));
+        return fail(B200CLIP_EKERNEL, "device watchdog: pipeline barrier never completed (site " + std::to_string(ds.where) + ")");
+    }
+    return B200_OK;
+}
+
+// ------------------------------------------------------------------------------------------ classify / search
+extern "C" int b200clip_set_labels(b200clip_handle* h, int32_t slot, const float* host_labels, int32_t N, int32_t D, void* stream) {
+    int rc = set_device(h); if (rc) return rc;
+    B200_REQUIRE((slot == 0 || slot == 1) && host_labels && N > 0 && D > 0, "set_labels: bad argument");
+    std::lock_guard<std::mutex> lk(h->mu);
+    cudaStream_t st = (cudaStream_t)stream;
+    B200_CUDA_OK(cudaStreamSynchronize(st));
+    cudaFree(h->labels[slot]); h->labels[slot] = nullptr;
+    B200_CUDA_OK(cudaMalloc(&h->labels[slot], (size_t)N * D * sizeof(float)));
+    B200_CUDA_OK(cudaMemcpyAsync(h->labels[slot], host_labels, (size_t)N * D * sizeof(float), cudaMemcpyHostToDevice, st));
+    if ((rc = launch_l2_normalize(h->labels[slot], h->labels[slot], N, D, st))) return rc;
+    B200_CUDA_OK(cudaStreamSynchronize(st));
+    h->labels_n[slot] = N; h->labels_d[slot] = D;
+    h->launches += 1;
+    return B200_OK;
+}
+
+extern "C" int b200clip_classify(b200clip_handle* h, int32_t slot, const float* emb_dev, int32_t B, float scale, int32_t softmax,
+                                 int32_t k, float* out_values_dev, int64_t* out_index_dev, void* stream) {
+    int rc = set_device(h); if (rc) return rc;
+    B200_REQUIRE(slot == 0 || slot == 1, "classify: slot must be 0 (labels) or 1 (scenes)");
+    std::lock_guard<std::mutex> lk(h->mu);
+    if (!h->labels[slot]) return fail(B200CLIP_ESTATE, "classify: no label embeddings loaded in this slot");
+    rc = classify_run(emb_dev, h->labels[slot], B, h->labels_n[slot], h->labels_d[slot], scale, softmax, k, out_values_dev,
+                      reinterpret_cast<long long*>(out_index_dev), (cudaStream_t)stream);
+    if (rc == B200_OK && B > 0) h->launches += 1;
+    return rc;
+}
+
+extern "C" int b200clip_topk(b200clip_handle* h, const void* queries, int32_t Q, const void* gallery, int64_t N, int32_t D, int32_t k,
+                             int64_t index_base, float* out_scores, int64_t* out_index, void* stream) {
+    int rc = set_device(h); if (rc) return rc;
+    B200_REQUIRE(queries && gallery && out_scores && out_index, "topk: null buffer");
+    std::lock_guard<std::mutex> lk(h->mu);
+    TopkPlan plan;
+    if ((rc = topk_plan(Q, N, k, &plan))) return rc;
+    const size_t need = plan.cand_bytes + plan.part_bytes + 512;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (need > h->topk_cap) {
+        B200_CUDA_OK(cudaStreamSynchronize(st));
+        cudaFree(h->topk_scratch); h->topk_scratch = nullptr; h->topk_cap = 0;
+        B200_CUDA_OK(cudaMalloc(&h->topk_scratch, need));
+        h->topk_cap = need;
+    }
+    rc = topk_run(queries, gallery, Q, N, D, k, index_base, h->topk_scratch, plan, out_scores, reinterpret_cast<long long*>(out_index),
+                  h->status, st);
+    if (rc == B200_OK) h->launches += 2;
+    return rc;
+}
+
+extern "C" int b200clip_merge_topk(b200clip_handle* h, const float* part_scores, const int64_t* part_index, int32_t parts, int32_t Q,
+                                   int32_t k, float* out_scores, int64_t* out_index, void* stream) {
+    int rc = set_device(h); if (rc) return rc;
+    B200_REQUIRE(part_scores && part_index && out_scores && out_index, "merge_topk: null buffer");
+    rc = merge_topk_run(part_scores, reinterpret_cast<const long long*>(part_index), parts, Q, k, out_scores,
+                        reinterpret_cast<long long*>(out_index), (cudaStream_t)stream);
+    if (rc == B200_OK && Q > 0) h->launches += 1;
+    return rc;
+}
+
+// ------------------------------------------------------------------------------------------ building blocks (tests)
+extern "C" int b200clip_gemm_bf16(b200clip_handle* h, const void* A, const void* W, int32_t M, int32_t N, int32_t K, const float* bias,
+                                  void* out, int32_t epilogue, int32_t activation, void* stream) {
+    int rc = set_device(h); if (rc) return rc;
+    B200_REQUIRE(A && W && out && epilogue >= 0 && epilogue <= 3, "gemm: bad argument");
+    rc = gemm_bf16_tc(A, K, W, K, M, N, K, bias, out, N, epilogue, activation, h->status, (cudaStream_t)stream);
+    if (rc == B200_OK) h->launches += 1;
+    return rc;
+}
+extern "C" int b200clip_attention(b200clip_handle* h, const void* qkv, void* out, int32_t B, int32_t S, int32_t width, int32_t heads, void* stream) {
+    int rc = set_device(h); if (rc) return rc;
+    rc = launch_attention(qkv, out, B, S, width, heads, (cudaStream_t)stream);
+    if (rc == B200_OK) h->launches += 1;
+    return rc;
+}
+extern "C" int b200clip_layernorm(b200clip_handle* h, const float* x, const float* g, const float* b, void* out, int32_t rows, int32_t width,
+                                  float eps, void* stream) {
+    int rc = set_device(h); if (rc) return rc;
+    rc = launch_layernorm(x, 1, g, b, out, rows, width, eps, (cudaStream_t)stream);
+    if (rc == B200_OK) h->launches += 1;
+    return rc;
+}

@@ -1,0 +1,235 @@
+// K2/K4/K6/K7/K8/K9 — one persistent, warp-specialised tcgen05 GEMM with fused epilogues.
+//
+//   C[M,N] = epilogue( A[M,K] (bf16, K-major) x W[N,K]^T (bf16, K-major = torch Linear layout) )
+//
+// Replaces the encoder matmuls the reference reaches through onnxruntime / torch
+// (packages/lumen-clip/src/lumen_clip/backends/onnxrt_backend.py:485, torch_backend.py:652-666).
+//
+// Layout per CTA (192 threads, one CTA per SM, grid = min(#tiles, 148)):
+//   warp 0      TMA producer: 128x64 A tile + BNx64 W tile per stage, SWIZZLE_128B, mbarrier complete_tx
+//   warp 1      TMEM allocator + single-thread tcgen05.mma issuer (UMMA 128 x BN x 16, fp32 accumulate in TMEM)
+//   warps 2..5  epilogue: tcgen05.ld (32 lanes x 32 columns) -> smem transpose -> coalesced global stores
+// TMEM holds two BN-column accumulators so the epilogue of tile i overlaps the MMAs of tile i+1.
+#include "common.cuh"
+#include "kernels.h"
+
+#include <mutex>
+
+namespace b200 {
+
+enum : int { ACT_QUICK_GELU = 0, ACT_GELU = 1 };
+
+struct GemmParams {
+    int M, N, K;          // K is a multiple of 64 (operands are zero-padded in K)
+    const float* bias;    // [N] or nullptr
+    void* out;            // bf16 or fp32, row pitch ldc elements
+    int ldc;
+    int epi, act;
+    DeviceStatus* status;
+};
+
+constexpr int BM = 128, BK = 64;
+constexpr int EPI_STAGE_WORDS = 32 * 33;
+
+template <int BN> struct GemmCfg {
+    static constexpr int STAGES = BN == 256 ? 4 : 6;
+    static constexpr int A_BYTES = BM * BK * 2;
+    static constexpr int B_BYTES = BN * BK * 2;
+    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr int TMEM_COLS = 2 * BN;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 4 * EPI_STAGE_WORDS * 4 + 256 + 1024;
+};
+
+__device__ __forceinline__ float apply_act(float v, int act) {
+    if (act == ACT_QUICK_GELU) return v / (1.0f + __expf(-1.702f * v));
+    return 0.5f * v * (1.0f + erff(v * 0.70710678118654752f));
+}
+
+template <int BN>
+__global__ void __launch_bounds__(192, 1)
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, GemmParams p) {
+    using Cfg = GemmCfg<BN>;
+    constexpr int STAGES = Cfg::STAGES;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    float* epi_stage = reinterpret_cast<float*>(smem + STAGES * Cfg::STAGE_BYTES);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * Cfg::STAGE_BYTES + 4 * EPI_STAGE_WORDS * 4);
+    uint64_t* full = bars;                  // [STAGES]  TMA -> MMA
+    uint64_t* empty = bars + STAGES;        // [STAGES]  MMA -> TMA
+    uint64_t* acc_full = bars + 2 * STAGES; // [2]       MMA -> epilogue
+    uint64_t* acc_empty = acc_full + 2;     // [2]       epilogue -> MMA
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int tiles_n = (p.N + BN - 1) / BN;
+    const int tiles = ((p.M + BM - 1) / BM) * tiles_n;
+    const int kblocks = p.K / BK;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmA);
+        tma_prefetch_desc(&tmB);
+        for (int s = 0; s < STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+        for (int a = 0; a < 2; ++a) { mbar_init(&acc_full[a], 1); mbar_init(&acc_empty[a], 4); }
+        fence_mbar_init();
+    }
+    if (warp == 1) tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int s = 0; uint32_t ph = 0; bool ok = true;
+            for (int t = blockIdx.x; t < tiles && ok; t += gridDim.x) {
+                const int m0 = (t / tiles_n) * BM, n0 = (t % tiles_n) * BN;
+                for (int kb = 0; kb < kblocks; ++kb) {
+                    if (!(ok = mbar_wait(&empty[s], ph ^ 1, p.status, 1))) break;
+                    uint8_t* sa = smem + s * Cfg::STAGE_BYTES;
+                    mbar_arrive_expect_tx(&full[s], Cfg::STAGE_BYTES);
+                    tma_load_2d(sa, &tmA, &full[s], kb * BK, m0);
+                    tma_load_2d(sa + Cfg::A_BYTES, &tmB, &full[s], kb * BK, n0);
+                    if (++s == STAGES) { s = 0; ph ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = umma_idesc(BM, BN, /*bf16*/ 1);
+            int s = 0; uint32_t ph = 0; int it = 0; bool ok = true;
+            for (int t = blockIdx.x; t < tiles && ok; t += gridDim.x, ++it) {
+                const int as = it & 1; const uint32_t aph = (it >> 1) & 1;
+                if (!(ok = mbar_wait(&acc_empty[as], aph ^ 1, p.status, 2))) break;
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + as * BN;
+                for (int kb = 0; kb < kblocks; ++kb) {
+                    if (!(ok = mbar_wait(&full[s], ph, p.status, 3))) break;
+                    tc_fence_after();
+                    const uint32_t sa = smem_u32(smem + s * Cfg::STAGE_BYTES);
+                    const uint64_t da = umma_desc_sw128(sa), db = umma_desc_sw128(sa + Cfg::A_BYTES);
+#pragma unroll
+                    for (int k = 0; k < BK / 16; ++k)   // +32 bytes along K inside the 128-byte swizzled row
+                        umma_f16(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+                    umma_commit(&empty[s]);
+                    if (++s == STAGES) { s = 0; ph ^= 1; }
+                }
+                if (ok) umma_commit(&acc_full[as]);
+            }
+        }
+    } else {
+        const int q = warp & 3;                       // TMEM lane quarter this warp may read
+        float* stg = epi_stage + (warp - 2) * EPI_STAGE_WORDS;
+        int it = 0; bool ok = true;
+        for (int t = blockIdx.x; t < tiles && ok; t += gridDim.x, ++it) {
+            const int m0 = (t / tiles_n) * BM, n0 = (t % tiles_n) * BN;
+            const int as = it & 1; const uint32_t aph = (it >> 1) & 1;
+            if (!(ok = mbar_wait(&acc_full[as], aph, p.status, 4))) break;
+            tc_fence_after();
+            const int row_base = m0 + q * 32;
+#pragma unroll 1
+            for (int c = 0; c < BN / 32; ++c) {
+                const int col = n0 + c * 32 + lane;
+                if (n0 + c * 32 >= p.N) break;
+                uint32_t v[32];
+                tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + as * BN + c * 32, v);
+                tmem_ld_wait();
+#pragma unroll
+                for (int j = 0; j < 32; ++j) stg[lane * 33 + j] = __uint_as_float(v[j]);
+                __syncwarp();
+                const bool col_ok = col < p.N;
+                const float b = (p.bias && col_ok) ? __ldg(p.bias + col) : 0.0f;
+                const int rows = min(32, p.M - row_base);
+                if (p.epi == EPI_F32) {
+                    float* o = reinterpret_cast<float*>(p.out);
+                    for (int r = 0; r < rows; ++r)
+                        if (col_ok) o[(size_t)(row_base + r) * p.ldc + col] = stg[r * 33 + lane] + b;
+                } else if (p.epi == EPI_BIAS_RES_F32) {
+                    float* o = reinterpret_cast<float*>(p.out);
+                    for (int r = 0; r < rows; ++r)
+                        if (col_ok) { float* x = o + (size_t)(row_base + r) * p.ldc + col; *x = *x + (stg[r * 33 + lane] + b); }
+                } else if (p.epi == EPI_BIAS_BF16) {
+                    __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out);
+                    for (int r = 0; r < rows; ++r)
+                        if (col_ok) o[(size_t)(row_base + r) * p.ldc + col] = __float2bfloat16(stg[r * 33 + lane] + b);
+                } else {
+                    __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out);
+                    for (int r = 0; r < rows; ++r)
+                        if (col_ok) o[(size_t)(row_base + r) * p.ldc + col] = __float2bfloat16(apply_act(stg[r * 33 + lane] + b, p.act));
+                }
+                __syncwarp();
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&acc_empty[as]);
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) { __syncwarp(); tmem_dealloc(tmem_base, Cfg::TMEM_COLS); }
+}
+
+// ------------------------------------------------------------------------------------------ host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static EncodeTiledFn g_encode = nullptr;
+static std::once_flag g_encode_once;
+
+int make_tmap_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t row_pitch_bytes,
+                 uint32_t box_rows, bool fp16) {
+    std::call_once(g_encode_once, [] {
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            g_encode = reinterpret_cast<EncodeTiledFn>(fn);
+    });
+    if (!g_encode) return fail(B200_EDEVICE, "cuTensorMapEncodeTiled is not available from the CUDA driver");
+    if ((reinterpret_cast<uintptr_t>(base) & 15) || (row_pitch_bytes & 15))
+        return fail(B200_EINVAL, "TMA operands need 16-byte aligned base and row pitch");
+    cuuint64_t dims[2] = {cols, rows};
+    cuuint64_t strides[1] = {row_pitch_bytes};
+    cuuint32_t box[2] = {64, box_rows};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = g_encode(out, fp16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
+                          const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                          CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) return fail(B200_ECUDA, "cuTensorMapEncodeTiled failed with CUresult " + std::to_string((int)r));
+    return B200_OK;
+}
+
+template <int BN> static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, cudaStream_t st) {
+    using Cfg = GemmCfg<BN>;
+    static std::once_flag once;
+    static cudaError_t attr_err = cudaSuccess;
+    std::call_once(once, [] {
+        attr_err = cudaFuncSetAttribute(gemm_tc_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
+    });
+    B200_CUDA_OK(attr_err);
+    const int tiles = ((p.M + BM - 1) / BM) * ((p.N + BN - 1) / BN);
+    const int grid = tiles < kNumSMs ? tiles : kNumSMs;
+    gemm_tc_kernel<BN><<<grid, 192, Cfg::SMEM_BYTES, st>>>(ta, tb, p);
+    B200_CUDA_OK(cudaGetLastError());
+    return B200_OK;
+}
+
+// A: bf16 [M, lda] (lda >= K, K % 64 == 0, zero padded), W: bf16 [N, ldw].
+int gemm_bf16_tc(const void* A, int lda, const void* W, int ldw, int M, int N, int K, const float* bias, void* out,
+                 int ldc, int epi, int act, DeviceStatus* status, cudaStream_t st) {
+    B200_REQUIRE(M > 0 && N > 0 && K > 0 && K % BK == 0, "gemm: K must be a positive multiple of 64 (pad the operands)");
+    // Pick the column tile that wastes fewer tile-rounds on 148 SMs.
+    auto rounds = [&](int bn) {
+        long t = (long)((M + BM - 1) / BM) * ((N + bn - 1) / bn);
+        return (double)((t + kNumSMs - 1) / kNumSMs) * bn;
+    };
+    const int bn = (N <= 128 || rounds(128) < rounds(256)) ? 128 : 256;
+    CUtensorMap ta, tb;
+    int rc = make_tmap_2d(&ta, A, M, K, (uint64_t)lda * 2, BM, false);
+    if (rc) return rc;
+    rc = make_tmap_2d(&tb, W, N, K, (uint64_t)ldw * 2, bn, false);
+    if (rc) return rc;
+    GemmParams p{M, N, K, bias, out, ldc, epi, act, status};
+    return bn == 128 ? launch_gemm<128>(ta, tb, p, st) : launch_gemm<256>(ta, tb, p, st);
+}
+
+}  // namespace b200

@@ -1,0 +1,30 @@
+// Launchers shared between the translation units of libb200clip (internal; the public ABI is include/b200clip.h).
+#pragma once
+#include "common.cuh"
+
+namespace b200 {
+
+struct PreprocessState;
+PreprocessState* preprocess_state_create(const float* mean, const float* stdv, int* rc);
+void preprocess_state_destroy(PreprocessState*);
+int preprocess_run(PreprocessState*, const uint8_t* src_dev, const long long* offsets, const int* hw, int B, int S, int mode,
+                   int layout, int out_bf16, int P, int kpad, void* out_dev, cudaStream_t st);
+int gemm_bf16_tc(const void* A, int lda, const void* W, int ldw, int M, int N, int K, const float* bias, void* out, int ldc,
+                 int epi, int act, DeviceStatus* status, cudaStream_t st);
+int launch_layernorm(const float* x, long long row_stride, const float* g, const float* b, void* out, int rows, int d, float eps, cudaStream_t st);
+int launch_embed_preln(const float* patch, const float* cls, const float* pos, const float* g, const float* b, float* xres,
+                       int B, int S, int d, float eps, cudaStream_t st);
+int launch_l2_normalize(const float* in, float* out, int rows, int D, cudaStream_t st);
+int launch_attention(const void* qkv, void* out, int B, int S, int d, int heads, cudaStream_t st);
+struct TopkPlan { int splits, qtiles, cpl; long long rows_per_split; size_t cand_bytes, part_bytes; };
+int topk_plan(int Q, long long N, int k, TopkPlan* plan);
+int topk_run(const void* queries, const void* gallery, int Q, long long N, int D, int k, long long index_base, void* scratch,
+             const TopkPlan& plan, float* out_s, long long* out_i, DeviceStatus* status, cudaStream_t st);
+int merge_topk_run(const float* ps, const long long* pi, int P, int Q, int k, float* out_s, long long* out_i, cudaStream_t st);
+int classify_run(const float* img, const float* labels_unit, int B, int N, int D, float scale, int softmax, int k,
+                 float* out_v, long long* out_i, cudaStream_t st);
+
+enum : int { EPI_F32 = 0, EPI_BIAS_BF16 = 1, EPI_BIAS_ACT_BF16 = 2, EPI_BIAS_RES_F32 = 3 };
+
+
+}  // namespace b200

@@ -1,0 +1,350 @@
+// K10 cosine top-k fused into a tcgen05 GEMM, K12 candidate merge.
+//
+// Replaces, batched and without ever materialising the Q x N score matrix,
+//   similarities = np.dot(img_embedding, text_embeddings.T); top = np.argsort(similarities)[::-1][:k]
+//   packages/lumen-clip/src/lumen_clip/expert_bioclip/bioclip_model.py:313-316
+// with the total order fixed by BASELINE.json: score descending, index ascending among equal scores.
+//
+// Grid = (query tiles of 128) x (gallery splits).  A CTA streams its gallery range through the same
+// TMA -> tcgen05.mma -> TMEM pipeline as gemm_tc.cu (fp16 operands, fp32 accumulate).  The four epilogue
+// warps own one query row per thread: each score is compared with that row's running threshold tau (its
+// current k-th best) and survivors are appended, as 64-bit keys (order-preserving score bits | ~index), to a
+// per-(split, query) candidate list in global scratch.  When a list is about to overflow, the warp sorts it
+// cooperatively (register bitonic network), keeps the best k and raises tau.  Because a split is scanned in
+// index order, "score > tau" is exact under the index-ordered tie rule.  A second kernel merges the
+// per-split (and, after the NCCL all-gather, per-GPU) lists with the same order.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace b200 {
+
+constexpr int TK_BM = 128, TK_BN = 256, TK_BK = 64, TK_STAGES = 4;
+constexpr int TK_A_BYTES = TK_BM * TK_BK * 2, TK_B_BYTES = TK_BN * TK_BK * 2, TK_STAGE_BYTES = TK_A_BYTES + TK_B_BYTES;
+constexpr int TK_SMEM = TK_STAGES * TK_STAGE_BYTES + 256 + 1024;
+
+struct TopkParams {
+    int Q, D, k;
+    long long N;                 // gallery rows on this GPU
+    long long rows_per_split;    // multiple of 256
+    int splits, qtiles;
+    unsigned long long* cand;    // [splits][qtiles*128][32*CPL]
+    float* part_scores;          // [splits][Q][k]
+    long long* part_idx;         // [splits][Q][k]
+    long long index_base;
+    DeviceStatus* status;
+};
+
+__device__ __forceinline__ uint32_t flip_f32(float s) {
+    const uint32_t u = __float_as_uint(s + 0.0f);               // -0 -> +0 so equal scores have equal keys
+    return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+__device__ __forceinline__ float unflip_f32(uint32_t u) {
+    return __uint_as_float((u & 0x80000000u) ? (u & 0x7fffffffu) : ~u);
+}
+
+// One compare-exchange stage of the bitonic network over 32*CPL keys (element e = reg*32 + lane); KK and J are
+// compile-time so every register index is static.
+template <int CPL, int KK, int J>
+__device__ __forceinline__ void bitonic_stage(unsigned long long (&key)[CPL], int lane) {
+    if constexpr (J >= 32) {
+        constexpr int rj = J >> 5;
+#pragma unroll
+        for (int i = 0; i < CPL; ++i) {
+            if ((i & rj) == 0) {
+                const bool desc = ((i * 32 + lane) & KK) == 0;
+                const unsigned long long a = key[i], b = key[i | rj];
+                const bool sw = desc ? (a < b) : (a > b);
+                key[i] = sw ? b : a;
+                key[i | rj] = sw ? a : b;
+            }
+        }
+    } else {
+        const bool lower = (lane & J) == 0;
+#pragma unroll
+        for (int i = 0; i < CPL; ++i) {
+            const unsigned long long o = __shfl_xor_sync(0xffffffffu, key[i], J);
+            const bool desc = ((i * 32 + lane) & KK) == 0;
+            const bool take_o = (lower == desc) ? (o > key[i]) : (o < key[i]);
+            key[i] = take_o ? o : key[i];
+        }
+    }
+}
+template <int CPL, int KK, int J>
+__device__ __forceinline__ void bitonic_from(unsigned long long (&key)[CPL], int lane) {
+    if constexpr (KK <= 32 * CPL) {
+        bitonic_stage<CPL, KK, J>(key, lane);
+        if constexpr (J > 1) bitonic_from<CPL, KK, J / 2>(key, lane);
+        else bitonic_from<CPL, KK * 2, KK>(key, lane);
+    }
+}
+template <int CPL>
+__device__ __forceinline__ void warp_sort_desc(unsigned long long (&key)[CPL], int lane) { bitonic_from<CPL, 2, 1>(key, lane); }
+
+// Whole warp: sort the candidate list of one row, keep the best k.  Returns the new count; `tau_out` is the
+// k-th best score (or -inf while fewer than k candidates exist).  With part_s/part_i set (end of the split) the
+// sorted best k are also written out as (score, global index), padded with (-inf, -1).
+template <int CPL>
+__device__ __noinline__ int compact_row(unsigned long long* rowptr, int n, int k, int lane, float* tau_out,
+                                        float* part_s, long long* part_i, long long index_base) {
+    unsigned long long key[CPL];
+    __syncwarp();
+#pragma unroll
+    for (int i = 0; i < CPL; ++i) {
+        const int e = i * 32 + lane;
+        key[i] = e < n ? __ldcg(rowptr + e) : 0ull;
+    }
+    warp_sort_desc<CPL>(key, lane);
+    const int keep = n < k ? n : k;
+    unsigned long long kth = 0ull;
+#pragma unroll
+    for (int i = 0; i < CPL; ++i) {
+        const int e = i * 32 + lane;
+        if (e == k - 1) kth = key[i];
+        if (e < keep) __stcg(rowptr + e, key[i]);
+        if (part_s != nullptr && e < k) {
+            const bool valid = e < n;
+            part_s[e] = valid ? unflip_f32((uint32_t)(key[i] >> 32)) : -INFINITY;
+            part_i[e] = valid ? index_base + (long long)(0xffffffffu - (uint32_t)(key[i] & 0xffffffffu)) : -1;
+        }
+    }
+    kth = __shfl_sync(0xffffffffu, kth, (k - 1) & 31);
+    *tau_out = n >= k ? unflip_f32((uint32_t)(kth >> 32)) : -INFINITY;
+    __syncwarp();
+    return keep;
+}
+
+template <int CPL>
+__global__ void __launch_bounds__(192, 1)
+topk_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmG, TopkParams p) {
+    constexpr int C = 32 * CPL;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + TK_STAGES * TK_STAGE_BYTES);
+    uint64_t* full = bars;
+    uint64_t* empty = bars + TK_STAGES;
+    uint64_t* acc_full = bars + 2 * TK_STAGES;
+    uint64_t* acc_empty = acc_full + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int qt = blockIdx.x, sp = blockIdx.y;
+    const long long n_lo = (long long)sp * p.rows_per_split;
+    const long long n_hi = min(p.N, n_lo + p.rows_per_split);
+    const int tiles = n_hi > n_lo ? (int)((n_hi - n_lo + TK_BN - 1) / TK_BN) : 0;
+    const int kblocks = p.D / TK_BK;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmQ);
+        tma_prefetch_desc(&tmG);
+        for (int s = 0; s < TK_STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+        for (int a = 0; a < 2; ++a) { mbar_init(&acc_full[a], 1); mbar_init(&acc_empty[a], 4); }
+        fence_mbar_init();
+    }
+    if (warp == 1) tmem_alloc(tmem_slot, 2 * TK_BN);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int s = 0; uint32_t ph = 0; bool ok = true;
+            for (int t = 0; t < tiles && ok; ++t) {
+                const int n0 = (int)(n_lo + (long long)t * TK_BN);
+                for (int kb = 0; kb < kblocks; ++kb) {
+                    if (!(ok = mbar_wait(&empty[s], ph ^ 1, p.status, 11))) break;
+                    uint8_t* sa = smem + s * TK_STAGE_BYTES;
+                    mbar_arrive_expect_tx(&full[s], TK_STAGE_BYTES);
+                    tma_load_2d(sa, &tmQ, &full[s], kb * TK_BK, qt * TK_BM);
+                    tma_load_2d(sa + TK_A_BYTES, &tmG, &full[s], kb * TK_BK, n0);
+                    if (++s == TK_STAGES) { s = 0; ph ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (lane == 0) {
+            constexpr uint32_t idesc = umma_idesc(TK_BM, TK_BN, /*f16*/ 0);
+            int s = 0; uint32_t ph = 0; bool ok = true;
+            for (int t = 0; t < tiles && ok; ++t) {
+                const int as = t & 1; const uint32_t aph = (t >> 1) & 1;
+                if (!(ok = mbar_wait(&acc_empty[as], aph ^ 1, p.status, 12))) break;
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + as * TK_BN;
+                for (int kb = 0; kb < kblocks; ++kb) {
+                    if (!(ok = mbar_wait(&full[s], ph, p.status, 13))) break;
+                    tc_fence_after();
+                    const uint32_t sa = smem_u32(smem + s * TK_STAGE_BYTES);
+                    const uint64_t da = umma_desc_sw128(sa), db = umma_desc_sw128(sa + TK_A_BYTES);
+#pragma unroll
+                    for (int k = 0; k < TK_BK / 16; ++k) umma_f16(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+                    umma_commit(&empty[s]);
+                    if (++s == TK_STAGES) { s = 0; ph ^= 1; }
+                }
+                if (ok) umma_commit(&acc_full[as]);
+            }
+        }
+    } else {
+        const int q = warp & 3;
+        const int row = q * 32 + lane;                              // query row inside the tile = TMEM lane
+        const long long qrow = (long long)qt * TK_BM + row;
+        unsigned long long* rowptr = p.cand + ((size_t)sp * p.qtiles * TK_BM + (size_t)qrow) * C;
+        unsigned long long* warp_rows = p.cand + ((size_t)sp * p.qtiles * TK_BM + (size_t)qt * TK_BM + q * 32) * C;
+        float tau = -INFINITY;
+        int cnt = 0;
+        bool ok = true;
+        for (int t = 0; t < tiles && ok; ++t) {
+            const int as = t & 1; const uint32_t aph = (t >> 1) & 1;
+            if (!(ok = mbar_wait(&acc_full[as], aph, p.status, 14))) break;
+            tc_fence_after();
+            const long long n0 = n_lo + (long long)t * TK_BN;
+#pragma unroll 1
+            for (int c = 0; c < TK_BN / 32; ++c) {
+                uint32_t v[32];
+                tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + as * TK_BN + c * 32, v);
+                tmem_ld_wait();
+                const long long nb = n0 + c * 32;
+#pragma unroll
+                for (int j = 0; j < 32; ++j) {
+                    const float s = __uint_as_float(v[j]);
+                    if (nb + j < n_hi && s > tau) {
+                        __stcg(rowptr + cnt, ((unsigned long long)flip_f32(s) << 32) | (0xffffffffu - (uint32_t)(nb + j)));
+                        ++cnt;
+                    }
+                }
+            }
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&acc_empty[as]);
+            // make room for the next tile (256 possible appends) while the MMAs of tile t+1 run
+            unsigned need = __ballot_sync(0xffffffffu, cnt + TK_BN > C);
+            while (need) {
+                const int src = __ffs(need) - 1;
+                need &= need - 1;
+                const int n = __shfl_sync(0xffffffffu, cnt, src);
+                float tnew;
+                const int keep = compact_row<CPL>(warp_rows + (size_t)src * C, n, p.k, lane, &tnew, nullptr, nullptr, 0);
+                if (lane == src) { cnt = keep; tau = tnew; }
+            }
+        }
+        // final: every row sorted, best k written as (score, global index) for the merge kernel
+        for (int src = 0; src < 32; ++src) {
+            const int n = __shfl_sync(0xffffffffu, cnt, src);
+            float tnew;
+            const long long qr = (long long)qt * TK_BM + q * 32 + src;
+            if (qr < p.Q)       // warp-uniform
+                compact_row<CPL>(warp_rows + (size_t)src * C, n, p.k, lane, &tnew, p.part_scores + ((size_t)sp * p.Q + qr) * p.k,
+                                 p.part_idx + ((size_t)sp * p.Q + qr) * p.k, p.index_base);
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 1) { __syncwarp(); tmem_dealloc(tmem_base, 2 * TK_BN); }
+}
+
+// ------------------------------------------------------------------------------------------ merge (K12)
+// parts: scores [P][Q][k] fp32, idx [P][Q][k] int64 (idx < 0 = empty slot).  One CTA per query sorts the
+// P*k candidates in shared memory (bitonic, score descending then index ascending) and writes the best k.
+__device__ __forceinline__ bool better(float sa, long long ia, float sb, long long ib) {
+    return sa > sb || (sa == sb && ia < ib);
+}
+
+__global__ void __launch_bounds__(256) merge_topk_kernel(const float* __restrict__ ps, const long long* __restrict__ pi, int P,
+                                                         int Q, int k, int np2, float* __restrict__ out_s,
+                                                         long long* __restrict__ out_i) {
+    extern __shared__ __align__(16) uint8_t msm[];
+    long long* si = reinterpret_cast<long long*>(msm);
+    float* ss = reinterpret_cast<float*>(msm + (size_t)np2 * 8);
+    const int qi = blockIdx.x;
+    const int total = P * k;
+    for (int e = threadIdx.x; e < np2; e += blockDim.x) {
+        float s = -INFINITY; long long i = 0x7fffffffffffffffLL;
+        if (e < total) {
+            const int part = e / k, j = e - part * k;
+            const long long id = pi[((size_t)part * Q + qi) * k + j];
+            if (id >= 0) { i = id; s = ps[((size_t)part * Q + qi) * k + j] + 0.0f; }
+        }
+        ss[e] = s; si[e] = i;
+    }
+    __syncthreads();
+    for (int kk = 2; kk <= np2; kk <<= 1)
+        for (int j = kk >> 1; j > 0; j >>= 1) {
+            for (int e = threadIdx.x; e < np2; e += blockDim.x) {
+                const int o = e ^ j;
+                if (o > e) {
+                    const bool desc = (e & kk) == 0;
+                    const float sa = ss[e], sb = ss[o]; const long long ia = si[e], ib = si[o];
+                    const bool sw = desc ? better(sb, ib, sa, ia) : better(sa, ia, sb, ib);
+                    if (sw) { ss[e] = sb; ss[o] = sa; si[e] = ib; si[o] = ia; }
+                }
+            }
+            __syncthreads();
+        }
+    for (int e = threadIdx.x; e < k; e += blockDim.x) {
+        const bool valid = e < np2 && si[e] != 0x7fffffffffffffffLL;
+        out_s[(size_t)qi * k + e] = valid ? ss[e] : -INFINITY;
+        out_i[(size_t)qi * k + e] = valid ? si[e] : -1;
+    }
+}
+
+int merge_topk_run(const float* ps, const long long* pi, int P, int Q, int k, float* out_s, long long* out_i, cudaStream_t st) {
+    B200_REQUIRE(P > 0 && k > 0, "merge_topk: need at least one part and k > 0");
+    if (Q == 0) return B200_OK;
+    int np2 = 2;
+    while (np2 < P * k) np2 <<= 1;
+    B200_REQUIRE(np2 <= 16384, "merge_topk: parts * k must not exceed 16384");
+    const size_t smem = (size_t)np2 * 12;
+    if (smem > 48 * 1024)
+        B200_CUDA_OK(cudaFuncSetAttribute(merge_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    merge_topk_kernel<<<Q, 256, smem, st>>>(ps, pi, P, Q, k, np2, out_s, out_i);
+    B200_CUDA_OK(cudaGetLastError());
+    return B200_OK;
+}
+
+// ------------------------------------------------------------------------------------------ host side
+int topk_plan(int Q, long long N, int k, TopkPlan* plan) {
+    B200_REQUIRE(Q > 0 && N > 0 && k > 0, "topk: Q, N and k must be positive");
+    B200_REQUIRE(k <= 768, "topk: k larger than 768 is not supported");
+    plan->cpl = k <= 256 ? 16 : 32;
+    plan->qtiles = (Q + TK_BM - 1) / TK_BM;
+    const long long ntiles = (N + TK_BN - 1) / TK_BN;
+    long long splits = (2LL * kNumSMs) / plan->qtiles;          // about two waves of CTAs
+    if (splits < 1) splits = 1;
+    if (splits > ntiles) splits = ntiles;
+    if (splits * k > 16384) splits = 16384 / k;                 // merge kernel capacity
+    const long long tiles_per_split = (ntiles + splits - 1) / splits;
+    plan->rows_per_split = tiles_per_split * TK_BN;
+    plan->splits = (int)((ntiles + tiles_per_split - 1) / tiles_per_split);
+    plan->cand_bytes = (size_t)plan->splits * plan->qtiles * TK_BM * 32 * plan->cpl * 8;
+    plan->part_bytes = (((size_t)plan->splits * Q * k * 4 + 255) & ~(size_t)255) + (size_t)plan->splits * Q * k * 8;
+    return B200_OK;
+}
+
+template <int CPL> static int launch_topk(const CUtensorMap& tq, const CUtensorMap& tg, const TopkParams& p, cudaStream_t st) {
+    B200_CUDA_OK(cudaFuncSetAttribute(topk_tc_kernel<CPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, TK_SMEM));
+    topk_tc_kernel<CPL><<<dim3(p.qtiles, p.splits), 192, TK_SMEM, st>>>(tq, tg, p);
+    B200_CUDA_OK(cudaGetLastError());
+    return B200_OK;
+}
+
+// queries fp16 [Q, D], gallery fp16 [N, D] (both row-major, D % 64 == 0).  scratch must hold
+// plan.cand_bytes + plan.part_bytes bytes (256-byte aligned).  Outputs: scores fp32 [Q,k], idx int64 [Q,k].
+int topk_run(const void* queries, const void* gallery, int Q, long long N, int D, int k, long long index_base,
+             void* scratch, const TopkPlan& plan, float* out_s, long long* out_i, DeviceStatus* status, cudaStream_t st) {
+    B200_REQUIRE(D > 0 && D % 64 == 0, "topk: embedding dim must be a multiple of 64");
+    B200_REQUIRE(N < (1LL << 31), "topk: at most 2^31-1 gallery rows per GPU");
+    CUtensorMap tq, tg;
+    int rc = make_tmap_2d(&tq, queries, Q, D, (uint64_t)D * 2, TK_BM, true);
+    if (rc) return rc;
+    rc = make_tmap_2d(&tg, gallery, (uint64_t)N, D, (uint64_t)D * 2, TK_BN, true);
+    if (rc) return rc;
+    uint8_t* sc = reinterpret_cast<uint8_t*>(scratch);
+    float* part_s = reinterpret_cast<float*>(sc + plan.cand_bytes);
+    long long* part_i = reinterpret_cast<long long*>(sc + plan.cand_bytes + (((size_t)plan.splits * Q * k * 4 + 255) & ~(size_t)255));
+    TopkParams p{Q, D, k, N, plan.rows_per_split, plan.splits, plan.qtiles, reinterpret_cast<unsigned long long*>(sc),
+                 part_s, part_i, index_base, status};
+    rc = plan.cpl == 16 ? launch_topk<16>(tq, tg, p, st) : launch_topk<32>(tq, tg, p, st);
+    if (rc) return rc;
+    return merge_topk_run(part_s, part_i, plan.splits, Q, k, out_s, out_i, st);
+}
+
+}  // namespace b200

@@ -1,0 +1,240 @@
+// K3 LayerNorm, token assembly (CLS + position + pre-LN), K5 attention, E2 L2-normalise.
+// The math follows what the reference's encoder call computes (onnxrt_backend.py:485 / torch_backend.py:652-666;
+// restated in oracle/clip_oracle.py:vit_encode).  The residual stream is fp32, GEMM operands are bf16.
+#include "common.cuh"
+#include "kernels.h"
+
+namespace b200 {
+
+// ------------------------------------------------------------------------------------------ LayerNorm
+// One warp per row; the row lives in registers (d <= 1024, d % 128 == 0), two-pass variance in fp32.
+constexpr int LN_MAX_V4 = 8;
+
+__device__ __forceinline__ void ln_row(float4 (&v)[LN_MAX_V4], int nv, int d, float eps, float& mean, float& rstd) {
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < LN_MAX_V4; ++i) if (i < nv) s += v[i].x + v[i].y + v[i].z + v[i].w;
+    mean = warp_sum(s) / d;
+    float q = 0.f;
+#pragma unroll
+    for (int i = 0; i < LN_MAX_V4; ++i) if (i < nv) {
+        float a = v[i].x - mean, b = v[i].y - mean, c = v[i].z - mean, e = v[i].w - mean;
+        q += a * a + b * b + c * c + e * e;
+    }
+    rstd = rsqrtf(warp_sum(q) / d + eps);
+}
+
+// x: fp32 rows (row r at x + r*row_stride*d), out: bf16 [rows, d].
+__global__ void __launch_bounds__(256) layernorm_bf16_kernel(const float* __restrict__ x, long long row_stride,
+                                                             const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                             __nv_bfloat16* __restrict__ out, int rows, int d, float eps) {
+    const int row = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (row >= rows) return;
+    const int nv = d >> 7;
+    const float4* xr = reinterpret_cast<const float4*>(x + (size_t)row * row_stride * d);
+    float4 v[LN_MAX_V4];
+#pragma unroll
+    for (int i = 0; i < LN_MAX_V4; ++i) if (i < nv) v[i] = xr[i * 32 + lane];
+    float mean, rstd;
+    ln_row(v, nv, d, eps, mean, rstd);
+    uint2* o = reinterpret_cast<uint2*>(out + (size_t)row * d);
+#pragma unroll
+    for (int i = 0; i < LN_MAX_V4; ++i) if (i < nv) {
+        const float4 g = reinterpret_cast<const float4*>(gamma)[i * 32 + lane];
+        const float4 b = reinterpret_cast<const float4*>(beta)[i * 32 + lane];
+        __nv_bfloat162 lo = __floats2bfloat162_rn((v[i].x - mean) * rstd * g.x + b.x, (v[i].y - mean) * rstd * g.y + b.y);
+        __nv_bfloat162 hi = __floats2bfloat162_rn((v[i].z - mean) * rstd * g.z + b.z, (v[i].w - mean) * rstd * g.w + b.w);
+        uint2 pk; pk.x = *reinterpret_cast<uint32_t*>(&lo); pk.y = *reinterpret_cast<uint32_t*>(&hi);
+        o[i * 32 + lane] = pk;
+    }
+}
+
+// Token assembly: row (b, s) = LN_pre( (s == 0 ? cls : patch[b*n + s-1]) + pos[s] ) -> fp32 residual stream.
+__global__ void __launch_bounds__(256) embed_preln_kernel(const float* __restrict__ patch, const float* __restrict__ cls,
+                                                          const float* __restrict__ pos, const float* __restrict__ gamma,
+                                                          const float* __restrict__ beta, float* __restrict__ xres,
+                                                          int B, int S, int d, float eps) {
+    const int row = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (row >= B * S) return;
+    const int b = row / S, s = row - b * S;
+    const int nv = d >> 7;
+    const float4* src = reinterpret_cast<const float4*>(s == 0 ? cls : patch + ((size_t)b * (S - 1) + (s - 1)) * d);
+    const float4* pr = reinterpret_cast<const float4*>(pos + (size_t)s * d);
+    float4 v[LN_MAX_V4];
+#pragma unroll
+    for (int i = 0; i < LN_MAX_V4; ++i) if (i < nv) {
+        const float4 a = src[i * 32 + lane], p = pr[i * 32 + lane];
+        v[i] = make_float4(a.x + p.x, a.y + p.y, a.z + p.z, a.w + p.w);
+    }
+    float mean, rstd;
+    ln_row(v, nv, d, eps, mean, rstd);
+    float4* o = reinterpret_cast<float4*>(xres + (size_t)row * d);
+#pragma unroll
+    for (int i = 0; i < LN_MAX_V4; ++i) if (i < nv) {
+        const float4 g = reinterpret_cast<const float4*>(gamma)[i * 32 + lane];
+        const float4 be = reinterpret_cast<const float4*>(beta)[i * 32 + lane];
+        o[i * 32 + lane] = make_float4((v[i].x - mean) * rstd * g.x + be.x, (v[i].y - mean) * rstd * g.y + be.y,
+                                       (v[i].z - mean) * rstd * g.z + be.z, (v[i].w - mean) * rstd * g.w + be.w);
+    }
+}
+
+// v / ||v||_2 per row, no epsilon (onnxrt_backend.py:545-546).  One warp per row.
+__global__ void __launch_bounds__(256) l2_normalize_kernel(const float* __restrict__ in, float* __restrict__ out, int rows, int D) {
+    const int row = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (row >= rows) return;
+    const float* r = in + (size_t)row * D;
+    float s = 0.f;
+    for (int i = lane; i < D; i += 32) s += r[i] * r[i];
+    const float nrm = sqrtf(warp_sum(s));
+    for (int i = lane; i < D; i += 32) out[(size_t)row * D + i] = r[i] / nrm;
+}
+
+// ------------------------------------------------------------------------------------------ attention
+// softmax(Q K^T / sqrt(64)) V for one (image, head, 64-query tile), head_dim fixed at 64 (all CLIP ViTs here).
+// Flash-style: keys in tiles of 64 with an online softmax, bf16 mma.sync m16n8k16 with fp32 accumulators.
+// (Attention is 1-9 % of the tower's FLOPs; the tcgen05 budget goes to the GEMMs.)
+constexpr int ATT_PITCH = 72;   // bf16 elements per shared-memory row (64 + 8 pad: conflict-free ldmatrix)
+
+__device__ __forceinline__ void ldsm_x4(uint32_t (&r)[4], const void* p) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(smem_u32(p)));
+}
+__device__ __forceinline__ void ldsm_x4_t(uint32_t (&r)[4], const void* p) {
+    asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(smem_u32(p)));
+}
+__device__ __forceinline__ void mma_bf16(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
+    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
+                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
+__device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
+    __nv_bfloat162 t = __floats2bfloat162_rn(a, b);
+    return *reinterpret_cast<uint32_t*>(&t);
+}
+
+__device__ __forceinline__ void load_tile64(__nv_bfloat16* dst, const __nv_bfloat16* src, int row0, int nrows_valid, int ld) {
+    // 64 rows x 64 bf16 (128 B per row) -> 512 16-byte vectors over 128 threads; rows past the end are zero-filled.
+    for (int i = threadIdx.x; i < 512; i += 128) {
+        const int r = i >> 3, c = (i & 7) * 8;
+        uint4 v = make_uint4(0, 0, 0, 0);
+        if (row0 + r < nrows_valid) v = *reinterpret_cast<const uint4*>(src + (size_t)(row0 + r) * ld + c);
+        *reinterpret_cast<uint4*>(dst + r * ATT_PITCH + c) = v;
+    }
+}
+
+__global__ void __launch_bounds__(128) attention_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict__ out,
+                                                        int S, int d) {
+    __shared__ __align__(16) __nv_bfloat16 sQ[64 * ATT_PITCH], sK[64 * ATT_PITCH], sV[64 * ATT_PITCH];
+    const int qt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
+    const int ld = 3 * d;
+    const __nv_bfloat16* base = qkv + (size_t)b * S * ld + h * 64;
+    load_tile64(sQ, base, qt * 64, S, ld);
+    __syncthreads();
+    uint32_t qa[4][4];
+#pragma unroll
+    for (int ks = 0; ks < 4; ++ks)
+        ldsm_x4(qa[ks], sQ + (warp * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * ATT_PITCH + ks * 16 + (lane >> 4) * 8);
+
+    float o[8][4];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f;
+    float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
+    const float sl2 = 0.125f * 1.4426950408889634f;   // 64^-0.5 * log2(e)
+
+    for (int k0 = 0; k0 < S; k0 += 64) {
+        __syncthreads();                               // previous tile fully consumed
+        load_tile64(sK, base + d, k0, S, ld);
+        load_tile64(sV, base + 2 * d, k0, S, ld);
+        __syncthreads();
+        float s[8][4];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) s[i][0] = s[i][1] = s[i][2] = s[i][3] = 0.f;
+#pragma unroll
+        for (int ks = 0; ks < 4; ++ks)
+#pragma unroll
+            for (int np = 0; np < 4; ++np) {
+                uint32_t kb[4];
+                ldsm_x4(kb, sK + (np * 16 + (lane & 7) + (lane >> 4) * 8) * ATT_PITCH + ks * 16 + ((lane >> 3) & 1) * 8);
+                mma_bf16(s[2 * np], qa[ks], kb[0], kb[1]);
+                mma_bf16(s[2 * np + 1], qa[ks], kb[2], kb[3]);
+            }
+        // mask keys past the sequence end, running max
+        float mx0 = m0, mx1 = m1;
+#pragma unroll
+        for (int nt = 0; nt < 8; ++nt) {
+            const int key = k0 + nt * 8 + 2 * t;
+            if (key >= S) { s[nt][0] = -INFINITY; s[nt][2] = -INFINITY; }
+            if (key + 1 >= S) { s[nt][1] = -INFINITY; s[nt][3] = -INFINITY; }
+            mx0 = fmaxf(mx0, fmaxf(s[nt][0], s[nt][1]));
+            mx1 = fmaxf(mx1, fmaxf(s[nt][2], s[nt][3]));
+        }
+        mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1)); mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
+        mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1)); mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
+        const float c0 = exp2f((m0 - mx0) * sl2), c1 = exp2f((m1 - mx1) * sl2);   // exp2f(-inf) = 0 on the first tile
+        m0 = mx0; m1 = mx1;
+        l0 *= c0; l1 *= c1;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { o[i][0] *= c0; o[i][1] *= c0; o[i][2] *= c1; o[i][3] *= c1; }
+        uint32_t pa[4][4];
+#pragma unroll
+        for (int nt = 0; nt < 8; ++nt) {
+            const float p0 = exp2f((s[nt][0] - m0) * sl2), p1 = exp2f((s[nt][1] - m0) * sl2);
+            const float p2 = exp2f((s[nt][2] - m1) * sl2), p3 = exp2f((s[nt][3] - m1) * sl2);
+            l0 += p0 + p1; l1 += p2 + p3;
+            pa[nt >> 1][(nt & 1) * 2 + 0] = pack_bf16(p0, p1);
+            pa[nt >> 1][(nt & 1) * 2 + 1] = pack_bf16(p2, p3);
+        }
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk)
+#pragma unroll
+            for (int dp = 0; dp < 4; ++dp) {
+                uint32_t vb[4];
+                ldsm_x4_t(vb, sV + (kk * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * ATT_PITCH + dp * 16 + (lane >> 4) * 8);
+                mma_bf16(o[2 * dp], pa[kk], vb[0], vb[1]);
+                mma_bf16(o[2 * dp + 1], pa[kk], vb[2], vb[3]);
+            }
+    }
+    l0 += __shfl_xor_sync(0xffffffffu, l0, 1); l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
+    l1 += __shfl_xor_sync(0xffffffffu, l1, 1); l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
+    const float i0 = 1.f / l0, i1 = 1.f / l1;
+    const int r0 = qt * 64 + warp * 16 + g, r1 = r0 + 8;
+    __nv_bfloat16* ob = out + (size_t)b * S * d + h * 64;
+#pragma unroll
+    for (int dt = 0; dt < 8; ++dt) {
+        if (r0 < S) *reinterpret_cast<uint32_t*>(ob + (size_t)r0 * d + dt * 8 + 2 * t) = pack_bf16(o[dt][0] * i0, o[dt][1] * i0);
+        if (r1 < S) *reinterpret_cast<uint32_t*>(ob + (size_t)r1 * d + dt * 8 + 2 * t) = pack_bf16(o[dt][2] * i1, o[dt][3] * i1);
+    }
+}
+
+// ------------------------------------------------------------------------------------------ launchers
+int launch_layernorm(const float* x, long long row_stride, const float* g, const float* b, void* out, int rows, int d, float eps, cudaStream_t st) {
+    B200_REQUIRE(d % 128 == 0 && d <= 128 * LN_MAX_V4, "layernorm: width must be a multiple of 128, at most 1024");
+    layernorm_bf16_kernel<<<(rows + 7) / 8, 256, 0, st>>>(x, row_stride, g, b, reinterpret_cast<__nv_bfloat16*>(out), rows, d, eps);
+    B200_CUDA_OK(cudaGetLastError());
+    return B200_OK;
+}
+int launch_embed_preln(const float* patch, const float* cls, const float* pos, const float* g, const float* b, float* xres,
+                       int B, int S, int d, float eps, cudaStream_t st) {
+    B200_REQUIRE(d % 128 == 0 && d <= 128 * LN_MAX_V4, "embed: width must be a multiple of 128, at most 1024");
+    embed_preln_kernel<<<(B * S + 7) / 8, 256, 0, st>>>(patch, cls, pos, g, b, xres, B, S, d, eps);
+    B200_CUDA_OK(cudaGetLastError());
+    return B200_OK;
+}
+int launch_l2_normalize(const float* in, float* out, int rows, int D, cudaStream_t st) {
+    if (rows == 0) return B200_OK;
+    l2_normalize_kernel<<<(rows + 7) / 8, 256, 0, st>>>(in, out, rows, D);
+    B200_CUDA_OK(cudaGetLastError());
+    return B200_OK;
+}
+int launch_attention(const void* qkv, void* out, int B, int S, int d, int heads, cudaStream_t st) {
+    B200_REQUIRE(d == heads * 64, "attention: head_dim must be 64");
+    B200_REQUIRE(B <= 65535 && heads <= 65535, "attention: grid too large");
+    attention_kernel<<<dim3((S + 63) / 64, heads, B), 128, 0, st>>>(reinterpret_cast<const __nv_bfloat16*>(qkv),
+                                                                    reinterpret_cast<__nv_bfloat16*>(out), S, d);
+    B200_CUDA_OK(cudaGetLastError());
+    return B200_OK;
+}
+
+}  // namespace b200

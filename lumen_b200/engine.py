@@ -1,0 +1,232 @@
+"""Thin host wrapper over one libb200clip handle (one per GPU).  PyTorch appears here only to own device /
+pinned memory and to name the current CUDA stream; all arithmetic happens inside the library."""
+from __future__ import annotations
+
+import ctypes as C
+from collections.abc import Sequence
+
+import numpy as np
+
+from . import _lib
+from .vit_config import OPENAI_MEAN, OPENAI_STD
+
+MODE_SQUASH, MODE_SHORTEST_CROP = 0, 1
+LAYOUT_NCHW, LAYOUT_PATCH = 0, 1
+
+
+def _torch():
+    import torch
+    return torch
+
+
+def pack_images(images: Sequence[np.ndarray], out: np.ndarray | None = None):
+    """Packs decoded uint8 HWC RGB images at 16-byte aligned offsets (+16 spare bytes), as the C ABI expects.
+    Returns (buffer, offsets[int64], hw[int32 Bx2], total_bytes)."""
+    B = len(images)
+    offsets = np.zeros(B, np.int64)
+    hw = np.zeros((B, 2), np.int32)
+    pos = 0
+    for i, im in enumerate(images):
+        if im.ndim != 3 or im.shape[2] != 3 or im.dtype != np.uint8:
+            raise ValueError("images must be uint8 arrays of shape (H, W, 3)")
+        offsets[i] = pos
+        hw[i] = im.shape[:2]
+        pos += (im.shape[0] * im.shape[1] * 3 + 15) & ~15
+    total = pos + 16
+    if out is None or out.size < total:
+        out = np.empty(total, np.uint8)
+    for i, im in enumerate(images):
+        n = im.shape[0] * im.shape[1] * 3
+        out[offsets[i]:offsets[i] + n] = np.ascontiguousarray(im).reshape(-1)
+    return out, offsets, hw, total
+
+
+class Engine:
+    """Owns a b200clip handle.  `cfg` is a dict from vit_config.VIT_CONFIGS (or layers=0 for no encoder)."""
+
+    def __init__(self, cfg: dict | None = None, device: int = 0, max_batch: int = 512, image_size: int | None = None,
+                 mean=OPENAI_MEAN, std=OPENAI_STD):
+        self.lib = _lib.load()
+        cfg = dict(cfg or {})
+        c = _lib.Config()
+        c.device = device
+        c.image_size = image_size or cfg.get("image_size", 224)
+        c.patch = cfg.get("patch", 0)
+        c.width = cfg.get("width", 0)
+        c.layers = cfg.get("layers", 0)
+        c.heads = cfg.get("heads", 0)
+        c.mlp_dim = cfg.get("mlp_dim", 0)
+        c.embed_dim = cfg.get("embed_dim", 0)
+        c.activation = 0 if cfg.get("activation", "quick_gelu") == "quick_gelu" else 1
+        c.max_batch = max_batch
+        c.ln_eps = cfg.get("ln_eps", 1e-5)
+        c.mean = (C.c_float * 3)(*mean)
+        c.std = (C.c_float * 3)(*std)
+        self.cfg, self.device, self.image_size = cfg, device, c.image_size
+        self.embed_dim = c.embed_dim
+        self.max_batch = max_batch
+        self._h = C.c_void_p()
+        _lib.check(self.lib.b200clip_create(C.byref(c), C.byref(self._h)))
+        self._pin_in = None
+        self._pin_out = None
+
+    # ------------------------------------------------------------------ lifecycle
+    def close(self) -> None:
+        if getattr(self, "_h", None) is not None and self._h:
+            self.lib.b200clip_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):  # noqa: D105
+        try:
+            self.close()
+        except Exception:  # noqa: BLE001
+            pass
+
+    def _stream(self):
+        torch = _torch()
+        return C.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+
+    def sync(self) -> None:
+        _lib.check(self.lib.b200clip_sync(self._h, self._stream()))
+
+    @property
+    def launches(self) -> int:
+        return int(self.lib.b200clip_launch_count(self._h))
+
+    # ------------------------------------------------------------------ weights
+    def load_weights(self, weights: dict[str, np.ndarray]) -> None:
+        for name, w in weights.items():
+            if name.endswith("position_ids"):
+                continue
+            a = np.ascontiguousarray(w, dtype=np.float32)
+            shape = (C.c_int64 * a.ndim)(*a.shape)
+            _lib.check(self.lib.b200clip_load_weight(self._h, name.encode(), a.ctypes.data_as(C.c_void_p), shape, a.ndim))
+        _lib.check(self.lib.b200clip_finalize_weights(self._h))
+
+    # ------------------------------------------------------------------ device-buffer API
+    def preprocess(self, src_dev, offsets: np.ndarray, hw: np.ndarray, mode: int = MODE_SQUASH, layout: int = LAYOUT_NCHW,
+                   bf16: bool = False):
+        """src_dev: uint8 cuda tensor (packed).  Returns a cuda tensor: [B,3,S,S] or patch-major [B*n, kpad]."""
+        torch = _torch()
+        B, S = int(len(offsets)), self.image_size
+        dt = torch.bfloat16 if bf16 else torch.float32
+        if layout == LAYOUT_NCHW:
+            out = torch.empty((B, 3, S, S), dtype=dt, device=src_dev.device)
+        else:
+            P = self.cfg["patch"]
+            kpad = (3 * P * P + 63) // 64 * 64
+            out = torch.zeros((B * (S // P) ** 2, kpad), dtype=dt, device=src_dev.device)
+        offsets = np.ascontiguousarray(offsets, np.int64)
+        hw = np.ascontiguousarray(hw, np.int32)
+        _lib.check(self.lib.b200clip_preprocess(self._h, C.c_void_p(src_dev.data_ptr()), offsets.ctypes.data_as(C.c_void_p),
+                                                hw.ctypes.data_as(C.c_void_p), B, mode, layout, int(bf16),
+                                                C.c_void_p(out.data_ptr()), self._stream()))
+        return out
+
+    def encode(self, patches_dev, B: int):
+        torch = _torch()
+        out = torch.empty((B, self.embed_dim), dtype=torch.float32, device=patches_dev.device)
+        _lib.check(self.lib.b200clip_encode(self._h, C.c_void_p(patches_dev.data_ptr()), B, C.c_void_p(out.data_ptr()), self._stream()))
+        return out
+
+    def embed_u8(self, src_dev, offsets: np.ndarray, hw: np.ndarray, mode: int = MODE_SQUASH, out=None):
+        torch = _torch()
+        B = int(len(offsets))
+        if out is None:
+            out = torch.empty((B, self.embed_dim), dtype=torch.float32, device=src_dev.device)
+        offsets = np.ascontiguousarray(offsets, np.int64)
+        hw = np.ascontiguousarray(hw, np.int32)
+        _lib.check(self.lib.b200clip_embed_u8(self._h, C.c_void_p(src_dev.data_ptr()), offsets.ctypes.data_as(C.c_void_p),
+                                              hw.ctypes.data_as(C.c_void_p), B, mode, C.c_void_p(out.data_ptr()), self._stream()))
+        return out
+
+    # ------------------------------------------------------------------ host-buffer API (what the backend calls)
+    def embed_host(self, images: Sequence[np.ndarray], mode: int = MODE_SQUASH) -> np.ndarray:
+        """Decoded uint8 HWC images (host) -> float32 [B, D] unit vectors (host).  H2D, kernels, D2H, sync."""
+        torch = _torch()
+        B = len(images)
+        if B == 0:
+            return np.empty((0, self.embed_dim), np.float32)
+        need = sum(((im.shape[0] * im.shape[1] * 3 + 15) & ~15) for im in images) + 16
+        if self._pin_in is None or self._pin_in.numel() < need:
+            self._pin_in = torch.empty(int(need * 1.25), dtype=torch.uint8, pin_memory=True)
+        if self._pin_out is None or self._pin_out.numel() < B * self.embed_dim:
+            self._pin_out = torch.empty(B * self.embed_dim, dtype=torch.float32, pin_memory=True)
+        buf, offsets, hw, total = pack_images(images, self._pin_in.numpy())
+        return self.embed_packed_host(self._pin_in, total, offsets, hw, mode)
+
+    def embed_packed_host(self, pinned_u8, total: int, offsets: np.ndarray, hw: np.ndarray, mode: int = MODE_SQUASH) -> np.ndarray:
+        torch = _torch()
+        B = int(len(offsets))
+        if self._pin_out is None or self._pin_out.numel() < B * self.embed_dim:
+            self._pin_out = torch.empty(B * self.embed_dim, dtype=torch.float32, pin_memory=True)
+        offsets = np.ascontiguousarray(offsets, np.int64)
+        hw = np.ascontiguousarray(hw, np.int32)
+        _lib.check(self.lib.b200clip_embed_host(self._h, C.c_void_p(pinned_u8.data_ptr()), int(total),
+                                                offsets.ctypes.data_as(C.c_void_p), hw.ctypes.data_as(C.c_void_p), B, mode,
+                                                C.c_void_p(self._pin_out.data_ptr()), self._stream()))
+        return self._pin_out[:B * self.embed_dim].view(B, self.embed_dim).numpy().copy()
+
+    # ------------------------------------------------------------------ classify / search
+    def set_labels(self, labels: np.ndarray, slot: int = 0) -> None:
+        a = np.ascontiguousarray(labels, dtype=np.float32)
+        _lib.check(self.lib.b200clip_set_labels(self._h, slot, a.ctypes.data_as(C.c_void_p), a.shape[0], a.shape[1], self._stream()))
+
+    def classify(self, emb_dev, k: int, slot: int = 0, scale: float = 100.0, softmax: bool = True):
+        torch = _torch()
+        B = emb_dev.shape[0]
+        vals = torch.empty((B, k), dtype=torch.float32, device=emb_dev.device)
+        idx = torch.empty((B, k), dtype=torch.int64, device=emb_dev.device)
+        _lib.check(self.lib.b200clip_classify(self._h, slot, C.c_void_p(emb_dev.data_ptr()), B, float(scale), int(softmax), k,
+                                              C.c_void_p(vals.data_ptr()), C.c_void_p(idx.data_ptr()), self._stream()))
+        return vals, idx
+
+    def topk(self, queries_f16, gallery_f16, k: int, index_base: int = 0):
+        torch = _torch()
+        Q, D = queries_f16.shape
+        N = gallery_f16.shape[0]
+        assert queries_f16.dtype == torch.float16 and gallery_f16.dtype == torch.float16
+        assert queries_f16.is_contiguous() and gallery_f16.is_contiguous()
+        scores = torch.empty((Q, k), dtype=torch.float32, device=queries_f16.device)
+        idx = torch.empty((Q, k), dtype=torch.int64, device=queries_f16.device)
+        _lib.check(self.lib.b200clip_topk(self._h, C.c_void_p(queries_f16.data_ptr()), Q, C.c_void_p(gallery_f16.data_ptr()), N, D, k,
+                                          int(index_base), C.c_void_p(scores.data_ptr()), C.c_void_p(idx.data_ptr()), self._stream()))
+        return scores, idx
+
+    def merge_topk(self, part_scores, part_idx):
+        """part_scores [P,Q,k] f32, part_idx [P,Q,k] i64 (cuda) -> merged ([Q,k], [Q,k])."""
+        torch = _torch()
+        P, Q, k = part_scores.shape
+        scores = torch.empty((Q, k), dtype=torch.float32, device=part_scores.device)
+        idx = torch.empty((Q, k), dtype=torch.int64, device=part_scores.device)
+        _lib.check(self.lib.b200clip_merge_topk(self._h, C.c_void_p(part_scores.data_ptr()), C.c_void_p(part_idx.data_ptr()), P, Q, k,
+                                                C.c_void_p(scores.data_ptr()), C.c_void_p(idx.data_ptr()), self._stream()))
+        return scores, idx
+
+    # ------------------------------------------------------------------ building blocks (parity tests)
+    def gemm(self, A_bf16, W_bf16, bias=None, epilogue: int = _lib.EPI_F32, activation: int = 0, out=None):
+        torch = _torch()
+        M, K = A_bf16.shape
+        N = W_bf16.shape[0]
+        if out is None:
+            dt = torch.float32 if epilogue in (_lib.EPI_F32, _lib.EPI_BIAS_RES_F32) else torch.bfloat16
+            out = torch.zeros((M, N), dtype=dt, device=A_bf16.device)
+        _lib.check(self.lib.b200clip_gemm_bf16(self._h, C.c_void_p(A_bf16.data_ptr()), C.c_void_p(W_bf16.data_ptr()), M, N, K,
+                                               C.c_void_p(bias.data_ptr()) if bias is not None else None,
+                                               C.c_void_p(out.data_ptr()), epilogue, activation, self._stream()))
+        return out
+
+    def attention(self, qkv_bf16, B: int, S: int, width: int, heads: int):
+        torch = _torch()
+        out = torch.empty((B * S, width), dtype=torch.bfloat16, device=qkv_bf16.device)
+        _lib.check(self.lib.b200clip_attention(self._h, C.c_void_p(qkv_bf16.data_ptr()), C.c_void_p(out.data_ptr()), B, S, width, heads,
+                                               self._stream()))
+        return out
+
+    def layernorm(self, x_f32, gamma, beta, eps: float = 1e-5):
+        torch = _torch()
+        rows, d = x_f32.shape
+        out = torch.empty((rows, d), dtype=torch.bfloat16, device=x_f32.device)
+        _lib.check(self.lib.b200clip_layernorm(self._h, C.c_void_p(x_f32.data_ptr()), C.c_void_p(gamma.data_ptr()),
+                                               C.c_void_p(beta.data_ptr()), C.c_void_p(out.data_ptr()), rows, d, float(eps), self._stream()))
+        return out

@@ -127,6 +127,11 @@ int b200clip_layernorm(b200clip_handle* h, const float* x_dev, const float* gamm
 
 /* Introspection used by bench.py: kernels launched by this handle so far. */
 int64_t b200clip_launch_count(b200clip_handle* h);
+/* Optional timing: while enabled, CUDA events bracket every kernel launch of the embed path on its stream.
+ * profile_read synchronises and returns summed milliseconds / launch counts for the 4 classes
+ * {0 preprocess, 1 tcgen05 GEMM, 2 LayerNorm/assembly/normalise, 3 attention}, then clears the records. */
+int b200clip_profile(b200clip_handle* h, int32_t enable);
+int b200clip_profile_read(b200clip_handle* h, float* ms_by_class, int64_t* launches_by_class, void* stream);
 
 #ifdef __cplusplus
 }

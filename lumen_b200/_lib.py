@@ -45,6 +45,8 @@ SIGNATURES = {
     "b200clip_attention": (C.c_int, [_P, _P, _P, _I32, _I32, _I32, _I32, _P]),
     "b200clip_layernorm": (C.c_int, [_P, _P, _P, _P, _P, _I32, _I32, _F, _P]),
     "b200clip_launch_count": (_I64, [_P]),
+    "b200clip_profile": (C.c_int, [_P, _I32]),
+    "b200clip_profile_read": (C.c_int, [_P, _P, _P, _P]),
 }
 
 _lib = None

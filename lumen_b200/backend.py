@@ -128,6 +128,15 @@ class B200ClipBackend(BaseClipBackend):
         except Exception as e:  # noqa: BLE001
             raise InferenceError(f"Batch image encoding failed: {e}") from e
 
+    def embed_packed(self, pinned_u8, total_bytes: int, offsets: np.ndarray, hw: np.ndarray) -> np.ndarray:
+        """Same, for a batch the caller already packed into pinned host memory (engine.pack_images layout)."""
+        self._ensure_initialized()
+        try:
+            with self._lock:
+                return self._engine.embed_packed_host(pinned_u8, total_bytes, offsets, hw, self._mode)
+        except Exception as e:  # noqa: BLE001
+            raise InferenceError(f"Batch image encoding failed: {e}") from e
+
     def image_to_vector(self, image_bytes: bytes) -> np.ndarray:
         self._ensure_initialized()
         if not image_bytes:

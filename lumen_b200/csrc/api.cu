@@ -58,6 +58,15 @@ struct b200clip_handle {
     PreprocessState* pre = nullptr;
     DeviceStatus* status = nullptr;
     int64_t launches = 0;
+    // optional per-kernel-class timing (bench.py roofline): CUDA events recorded around each launch
+    bool prof = false;
+    std::vector<cudaEvent_t> ev_pool; size_t ev_used = 0;
+    struct ProfRec { int cls; cudaEvent_t a, b; };
+    std::vector<ProfRec> prof_recs;
+    cudaEvent_t prof_event() {
+        if (ev_used == ev_pool.size()) { cudaEvent_t e; cudaEventCreate(&e); ev_pool.push_back(e); }
+        return ev_pool[ev_used++];
+    }
 
     template <class T> int alloc(T** p, size_t count, bool zero = false) {
         void* q = nullptr;
@@ -138,6 +147,7 @@ extern "C" void b200clip_destroy(b200clip_handle* h) {
     cudaSetDevice(h->cfg.device);
     cudaDeviceSynchronize();
     for (void* p : h->allocs) cudaFree(p);
+    for (cudaEvent_t e : h->ev_pool) cudaEventDestroy(e);
     cudaFree(h->upload_tmp); cudaFree(h->img_dev); cudaFree(h->emb_dev); cudaFree(h->topk_scratch);
     cudaFree(h->labels[0]); cudaFree(h->labels[1]);
     if (h->pre) preprocess_state_destroy(h->pre);
@@ -157,6 +167,29 @@ extern "C" int b200clip_sync(b200clip_handle* h, void* stream) {
 }
 
 extern "C" int64_t b200clip_launch_count(b200clip_handle* h) { return h ? h->launches : 0; }
+
+extern "C" int b200clip_profile(b200clip_handle* h, int32_t enable) {
+    B200_REQUIRE(h != nullptr, "null handle");
+    std::lock_guard<std::mutex> lk(h->mu);
+    h->prof = enable != 0;
+    h->prof_recs.clear(); h->ev_used = 0;
+    return B200_OK;
+}
+
+extern "C" int b200clip_profile_read(b200clip_handle* h, float* ms_by_class, int64_t* launches_by_class, void* stream) {
+    int rc = set_device(h); if (rc) return rc;
+    B200_REQUIRE(ms_by_class && launches_by_class, "profile_read: null buffer");
+    std::lock_guard<std::mutex> lk(h->mu);
+    B200_CUDA_OK(cudaStreamSynchronize((cudaStream_t)stream));
+    for (int c = 0; c < 4; ++c) { ms_by_class[c] = 0.f; launches_by_class[c] = 0; }
+    for (const auto& r : h->prof_recs) {
+        float ms = 0.f;
+        B200_CUDA_OK(cudaEventElapsedTime(&ms, r.a, r.b));
+        ms_by_class[r.cls] += ms; launches_by_class[r.cls] += 1;
+    }
+    h->prof_recs.clear(); h->ev_used = 0;
+    return B200_OK;
+}
 
 // ------------------------------------------------------------------------------------------ weights
 static int upload_f32(b200clip_handle* h, const float* host, size_t count, float** dev_tmp) {
@@ -266,20 +299,29 @@ static int encode_chunk(b200clip_handle* h, const __nv_bfloat16* patches, int B,
     const int d = c.width, S = h->S, M = B * S, Mp = B * h->n, mlp = c.mlp_dim, D = c.embed_dim;
     int rc;
 #define R_(call) if ((rc = (call))) return rc
-    R_(gemm_bf16_tc(patches, h->kpad, h->w_patch, h->kpad, Mp, d, h->kpad, nullptr, h->patch_out, d, EPI_F32, 0, h->status, st));
-    R_(launch_embed_preln(h->patch_out, h->cls, h->pos, h->pre_g, h->pre_b, h->xres, B, S, d, c.ln_eps, st));
+    auto timed = [&](int cls, auto&& fn) -> int {
+        if (!h->prof) return fn();
+        cudaEvent_t a = h->prof_event(), b = h->prof_event();
+        cudaEventRecord(a, st);
+        const int r = fn();
+        cudaEventRecord(b, st);
+        h->prof_recs.push_back({cls, a, b});
+        return r;
+    };
+    R_(timed(1, [&] { return gemm_bf16_tc(patches, h->kpad, h->w_patch, h->kpad, Mp, d, h->kpad, nullptr, h->patch_out, d, EPI_F32, 0, h->status, st); }));
+    R_(timed(2, [&] { return launch_embed_preln(h->patch_out, h->cls, h->pos, h->pre_g, h->pre_b, h->xres, B, S, d, c.ln_eps, st); }));
     for (const Layer& l : h->layers) {
-        R_(launch_layernorm(h->xres, 1, l.ln1_g, l.ln1_b, h->hbuf, M, d, c.ln_eps, st));
-        R_(gemm_bf16_tc(h->hbuf, d, l.w_qkv, d, M, 3 * d, d, l.b_qkv, h->qkv, 3 * d, EPI_BIAS_BF16, 0, h->status, st));
-        R_(launch_attention(h->qkv, h->hbuf, B, S, d, c.heads, st));
-        R_(gemm_bf16_tc(h->hbuf, d, l.w_o, d, M, d, d, l.b_o, h->xres, d, EPI_BIAS_RES_F32, 0, h->status, st));
-        R_(launch_layernorm(h->xres, 1, l.ln2_g, l.ln2_b, h->hbuf, M, d, c.ln_eps, st));
-        R_(gemm_bf16_tc(h->hbuf, d, l.w_fc1, d, M, mlp, d, l.b_fc1, h->mlp, mlp, EPI_BIAS_ACT_BF16, c.activation, h->status, st));
-        R_(gemm_bf16_tc(h->mlp, mlp, l.w_fc2, mlp, M, d, mlp, l.b_fc2, h->xres, d, EPI_BIAS_RES_F32, 0, h->status, st));
+        R_(timed(2, [&] { return launch_layernorm(h->xres, 1, l.ln1_g, l.ln1_b, h->hbuf, M, d, c.ln_eps, st); }));
+        R_(timed(1, [&] { return gemm_bf16_tc(h->hbuf, d, l.w_qkv, d, M, 3 * d, d, l.b_qkv, h->qkv, 3 * d, EPI_BIAS_BF16, 0, h->status, st); }));
+        R_(timed(3, [&] { return launch_attention(h->qkv, h->hbuf, B, S, d, c.heads, st); }));
+        R_(timed(1, [&] { return gemm_bf16_tc(h->hbuf, d, l.w_o, d, M, d, d, l.b_o, h->xres, d, EPI_BIAS_RES_F32, 0, h->status, st); }));
+        R_(timed(2, [&] { return launch_layernorm(h->xres, 1, l.ln2_g, l.ln2_b, h->hbuf, M, d, c.ln_eps, st); }));
+        R_(timed(1, [&] { return gemm_bf16_tc(h->hbuf, d, l.w_fc1, d, M, mlp, d, l.b_fc1, h->mlp, mlp, EPI_BIAS_ACT_BF16, c.activation, h->status, st); }));
+        R_(timed(1, [&] { return gemm_bf16_tc(h->mlp, mlp, l.w_fc2, mlp, M, d, mlp, l.b_fc2, h->xres, d, EPI_BIAS_RES_F32, 0, h->status, st); }));
     }
-    R_(launch_layernorm(h->xres, S, h->post_g, h->post_b, h->cls_ln, B, d, c.ln_eps, st));
-    R_(gemm_bf16_tc(h->cls_ln, d, h->w_proj, d, B, D, d, nullptr, h->emb_raw, D, EPI_F32, 0, h->status, st));
-    R_(launch_l2_normalize(h->emb_raw, emb_out, B, D, st));
+    R_(timed(2, [&] { return launch_layernorm(h->xres, S, h->post_g, h->post_b, h->cls_ln, B, d, c.ln_eps, st); }));
+    R_(timed(1, [&] { return gemm_bf16_tc(h->cls_ln, d, h->w_proj, d, B, D, d, nullptr, h->emb_raw, D, EPI_F32, 0, h->status, st); }));
+    R_(timed(2, [&] { return launch_l2_normalize(h->emb_raw, emb_out, B, D, st); }));
 #undef R_
     h->launches += 5 + 7 * (int64_t)h->layers.size();
     return B200_OK;
@@ -312,8 +354,11 @@ static int embed_u8_locked(b200clip_handle* h, const uint8_t* src_dev, const int
     B200_REQUIRE((reinterpret_cast<uintptr_t>(src_dev) & 15) == 0, "embed: src_dev must be 16-byte aligned");
     for (int b0 = 0; b0 < B; b0 += h->cfg.max_batch) {
         const int nb = std::min(h->cfg.max_batch, B - b0);
+        cudaEvent_t pa = nullptr, pb = nullptr;
+        if (h->prof) { pa = h->prof_event(); pb = h->prof_event(); cudaEventRecord(pa, st); }
         rc = preprocess_run(h->pre, src_dev, reinterpret_cast<const long long*>(offsets) + b0, hw + 2 * b0, nb, h->cfg.image_size, mode,
                             /*layout*/ 1, /*bf16*/ 1, h->cfg.patch, h->kpad, h->patches, st);
+        if (h->prof) { cudaEventRecord(pb, st); h->prof_recs.push_back({0, pa, pb}); }
         if (rc) return rc;
         h->launches += 1;
         if ((rc = encode_chunk(h, h->patches, nb, emb_dev + (size_t)b0 * h->cfg.embed_dim, st))) return rc;

@@ -93,6 +93,16 @@ class Engine:
     def launches(self) -> int:
         return int(self.lib.b200clip_launch_count(self._h))
 
+    def profile(self, enable: bool) -> None:
+        _lib.check(self.lib.b200clip_profile(self._h, int(enable)))
+
+    def profile_read(self) -> dict:
+        ms = (C.c_float * 4)()
+        n = (C.c_int64 * 4)()
+        _lib.check(self.lib.b200clip_profile_read(self._h, ms, n, self._stream()))
+        names = ("preprocess", "gemm", "norm", "attention")
+        return {k: {"ms": float(ms[i]), "launches": int(n[i])} for i, k in enumerate(names)}
+
     # ------------------------------------------------------------------ weights
     def load_weights(self, weights: dict[str, np.ndarray]) -> None:
         for name, w in weights.items():

@@ -29,7 +29,8 @@ struct GemmParams {
 };
 
 constexpr int BM = 128, BK = 64;
-constexpr int EPI_STAGE_WORDS = 32 * 33;
+constexpr int EPI_PITCH = 36;                 // floats per staged row: 16-byte aligned, conflict-free for 128-bit access
+constexpr int EPI_STAGE_WORDS = 32 * EPI_PITCH;
 
 template <int BN> struct GemmCfg {
     static constexpr int STAGES = BN == 256 ? 4 : 6;
@@ -40,12 +41,17 @@ template <int BN> struct GemmCfg {
     static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 4 * EPI_STAGE_WORDS * 4 + 256 + 1024;
 };
 
-__device__ __forceinline__ float apply_act(float v, int act) {
-    if (act == ACT_QUICK_GELU) return v / (1.0f + __expf(-1.702f * v));
+template <int ACT> __device__ __forceinline__ float apply_act(float v) {
+    if (ACT == ACT_QUICK_GELU) return __fdividef(v, 1.0f + __expf(-1.702f * v));
     return 0.5f * v * (1.0f + erff(v * 0.70710678118654752f));
 }
+__device__ __forceinline__ uint2 pack4_bf16(float a, float b, float c, float d) {
+    __nv_bfloat162 lo = __floats2bfloat162_rn(a, b), hi = __floats2bfloat162_rn(c, d);
+    uint2 r; r.x = *reinterpret_cast<uint32_t*>(&lo); r.y = *reinterpret_cast<uint32_t*>(&hi);
+    return r;
+}
 
-template <int BN>
+template <int BN, int EPI, int ACT>
 __global__ void __launch_bounds__(192, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, GemmParams p) {
     using Cfg = GemmCfg<BN>;
@@ -119,6 +125,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     } else {
         const int q = warp & 3;                       // TMEM lane quarter this warp may read
         float* stg = epi_stage + (warp - 2) * EPI_STAGE_WORDS;
+        const int sub_r = lane >> 3, c4 = (lane & 7) * 4;   // store phase: 8 lanes cover 32 columns of one row
         int it = 0; bool ok = true;
         for (int t = blockIdx.x; t < tiles && ok; t += gridDim.x, ++it) {
             const int m0 = (t / tiles_n) * BM, n0 = (t % tiles_n) * BN;
@@ -126,41 +133,71 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             if (!(ok = mbar_wait(&acc_full[as], aph, p.status, 4))) break;
             tc_fence_after();
             const int row_base = m0 + q * 32;
+            const uint32_t tsrc = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN;
+            const int nchunks = min(BN / 32, (p.N - n0 + 31) / 32);
+            uint32_t v[32];
+            tmem_ld_32x32(tsrc, v);
 #pragma unroll 1
-            for (int c = 0; c < BN / 32; ++c) {
-                const int col = n0 + c * 32 + lane;
-                if (n0 + c * 32 >= p.N) break;
-                uint32_t v[32];
-                tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + as * BN + c * 32, v);
+            for (int c = 0; c < nchunks; ++c) {
                 tmem_ld_wait();
+                float4* s4 = reinterpret_cast<float4*>(stg + lane * EPI_PITCH);
 #pragma unroll
-                for (int j = 0; j < 32; ++j) stg[lane * 33 + j] = __uint_as_float(v[j]);
+                for (int j = 0; j < 8; ++j)
+                    s4[j] = make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]), __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3]));
+                if (c + 1 < nchunks) tmem_ld_32x32(tsrc + (c + 1) * 32, v);     // in flight while this chunk is stored
+                else {                                                         // accumulator fully read: hand it back
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&acc_empty[as]);
+                }
                 __syncwarp();
-                const bool col_ok = col < p.N;
-                const float b = (p.bias && col_ok) ? __ldg(p.bias + col) : 0.0f;
-                const int rows = min(32, p.M - row_base);
-                if (p.epi == EPI_F32) {
+                const int col = n0 + c * 32 + c4;
+                const bool col_ok = col < p.N;                                 // N % 4 == 0
+                float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f);
+                if (p.bias != nullptr && col_ok) b4 = __ldg(reinterpret_cast<const float4*>(p.bias + col));
+                float4 a[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    a[i] = *reinterpret_cast<const float4*>(stg + (i * 4 + sub_r) * EPI_PITCH + c4);
+                    a[i].x += b4.x; a[i].y += b4.y; a[i].z += b4.z; a[i].w += b4.w;
+                }
+                if (EPI == EPI_BIAS_RES_F32) {
                     float* o = reinterpret_cast<float*>(p.out);
-                    for (int r = 0; r < rows; ++r)
-                        if (col_ok) o[(size_t)(row_base + r) * p.ldc + col] = stg[r * 33 + lane] + b;
-                } else if (p.epi == EPI_BIAS_RES_F32) {
+                    float4 x[8];
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        const int row = row_base + i * 4 + sub_r;
+                        if (row < p.M && col_ok) x[i] = *reinterpret_cast<const float4*>(o + (size_t)row * p.ldc + col);
+                    }
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        const int row = row_base + i * 4 + sub_r;
+                        if (row < p.M && col_ok)
+                            *reinterpret_cast<float4*>(o + (size_t)row * p.ldc + col) =
+                                make_float4(x[i].x + a[i].x, x[i].y + a[i].y, x[i].z + a[i].z, x[i].w + a[i].w);
+                    }
+                } else if (EPI == EPI_F32) {
                     float* o = reinterpret_cast<float*>(p.out);
-                    for (int r = 0; r < rows; ++r)
-                        if (col_ok) { float* x = o + (size_t)(row_base + r) * p.ldc + col; *x = *x + (stg[r * 33 + lane] + b); }
-                } else if (p.epi == EPI_BIAS_BF16) {
-                    __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out);
-                    for (int r = 0; r < rows; ++r)
-                        if (col_ok) o[(size_t)(row_base + r) * p.ldc + col] = __float2bfloat16(stg[r * 33 + lane] + b);
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        const int row = row_base + i * 4 + sub_r;
+                        if (row < p.M && col_ok) *reinterpret_cast<float4*>(o + (size_t)row * p.ldc + col) = a[i];
+                    }
                 } else {
                     __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out);
-                    for (int r = 0; r < rows; ++r)
-                        if (col_ok) o[(size_t)(row_base + r) * p.ldc + col] = __float2bfloat16(apply_act(stg[r * 33 + lane] + b, p.act));
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        const int row = row_base + i * 4 + sub_r;
+                        if (EPI == EPI_BIAS_ACT_BF16) {
+                            a[i].x = apply_act<ACT>(a[i].x); a[i].y = apply_act<ACT>(a[i].y);
+                            a[i].z = apply_act<ACT>(a[i].z); a[i].w = apply_act<ACT>(a[i].w);
+                        }
+                        if (row < p.M && col_ok)
+                            *reinterpret_cast<uint2*>(o + (size_t)row * p.ldc + col) = pack4_bf16(a[i].x, a[i].y, a[i].z, a[i].w);
+                    }
                 }
                 __syncwarp();
             }
-            tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&acc_empty[as]);
         }
     }
     tc_fence_before();
@@ -198,38 +235,44 @@ int make_tmap_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64_t col
     return B200_OK;
 }
 
-template <int BN> static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, cudaStream_t st) {
+template <int BN, int EPI, int ACT> static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, cudaStream_t st) {
     using Cfg = GemmCfg<BN>;
-    static std::once_flag once;
-    static cudaError_t attr_err = cudaSuccess;
-    std::call_once(once, [] {
-        attr_err = cudaFuncSetAttribute(gemm_tc_kernel<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES);
-    });
-    B200_CUDA_OK(attr_err);
+    B200_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<BN, EPI, ACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
     const int tiles = ((p.M + BM - 1) / BM) * ((p.N + BN - 1) / BN);
     const int grid = tiles < kNumSMs ? tiles : kNumSMs;
-    gemm_tc_kernel<BN><<<grid, 192, Cfg::SMEM_BYTES, st>>>(ta, tb, p);
+    gemm_tc_kernel<BN, EPI, ACT><<<grid, 192, Cfg::SMEM_BYTES, st>>>(ta, tb, p);
     B200_CUDA_OK(cudaGetLastError());
     return B200_OK;
+}
+template <int BN> static int dispatch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, cudaStream_t st) {
+    switch (p.epi) {
+        case EPI_F32: return launch_gemm<BN, EPI_F32, 0>(ta, tb, p, st);
+        case EPI_BIAS_BF16: return launch_gemm<BN, EPI_BIAS_BF16, 0>(ta, tb, p, st);
+        case EPI_BIAS_RES_F32: return launch_gemm<BN, EPI_BIAS_RES_F32, 0>(ta, tb, p, st);
+        default: return p.act == ACT_QUICK_GELU ? launch_gemm<BN, EPI_BIAS_ACT_BF16, ACT_QUICK_GELU>(ta, tb, p, st)
+                                                : launch_gemm<BN, EPI_BIAS_ACT_BF16, ACT_GELU>(ta, tb, p, st);
+    }
 }
 
 // A: bf16 [M, lda] (lda >= K, K % 64 == 0, zero padded), W: bf16 [N, ldw].
 int gemm_bf16_tc(const void* A, int lda, const void* W, int ldw, int M, int N, int K, const float* bias, void* out,
                  int ldc, int epi, int act, DeviceStatus* status, cudaStream_t st) {
     B200_REQUIRE(M > 0 && N > 0 && K > 0 && K % BK == 0, "gemm: K must be a positive multiple of 64 (pad the operands)");
-    // Pick the column tile that wastes fewer tile-rounds on 148 SMs.
+    B200_REQUIRE(N % 4 == 0 && ldc % 4 == 0, "gemm: N and the output pitch must be multiples of 4");
+    // 128x256 tiles read 96 B/clk of shared memory per MMA against 128 B/clk for 128x128, so prefer them unless
+    // they waste clearly more tile-rounds on the 148 SMs.
     auto rounds = [&](int bn) {
         long t = (long)((M + BM - 1) / BM) * ((N + bn - 1) / bn);
         return (double)((t + kNumSMs - 1) / kNumSMs) * bn;
     };
-    const int bn = (N <= 128 || rounds(128) < rounds(256)) ? 128 : 256;
+    const int bn = (N <= 128 || rounds(128) * 1.2 < rounds(256)) ? 128 : 256;
     CUtensorMap ta, tb;
     int rc = make_tmap_2d(&ta, A, M, K, (uint64_t)lda * 2, BM, false);
     if (rc) return rc;
     rc = make_tmap_2d(&tb, W, N, K, (uint64_t)ldw * 2, bn, false);
     if (rc) return rc;
     GemmParams p{M, N, K, bias, out, ldc, epi, act, status};
-    return bn == 128 ? launch_gemm<128>(ta, tb, p, st) : launch_gemm<256>(ta, tb, p, st);
+    return bn == 128 ? dispatch_gemm<128>(ta, tb, p, st) : dispatch_gemm<256>(ta, tb, p, st);
 }
 
 }  // namespace b200

@@ -5,10 +5,10 @@
 // Replaces the encoder matmuls the reference reaches through onnxruntime / torch
 // (packages/lumen-clip/src/lumen_clip/backends/onnxrt_backend.py:485, torch_backend.py:652-666).
 //
-// Layout per CTA (192 threads, one CTA per SM, grid = min(#tiles, 148)):
+// Layout per CTA (320 threads, one CTA per SM, grid = min(#tiles, 148)):
 //   warp 0      TMA producer: 128x64 A tile + BNx64 W tile per stage, SWIZZLE_128B, mbarrier complete_tx
 //   warp 1      TMEM allocator + single-thread tcgen05.mma issuer (UMMA 128 x BN x 16, fp32 accumulate in TMEM)
-//   warps 2..5  epilogue: tcgen05.ld (32 lanes x 32 columns) -> smem transpose -> coalesced global stores
+//   warps 2..9  epilogue: tcgen05.ld (32 lanes x 16 columns) -> smem transpose -> coalesced stores / vector reductions
 // TMEM holds two BN-column accumulators so the epilogue of tile i overlaps the MMAs of tile i+1.
 #include "common.cuh"
 #include "kernels.h"
@@ -29,8 +29,10 @@ struct GemmParams {
 };
 
 constexpr int BM = 128, BK = 64;
-constexpr int EPI_PITCH = 36;                 // floats per staged row: 16-byte aligned, conflict-free for 128-bit access
+constexpr int EPI_WARPS = 8;                  // two warps per TMEM lane quarter, alternating 16-column sub-chunks
+constexpr int EPI_PITCH = 20;                 // floats per staged row (16 + 4): conflict-free 128-bit rows
 constexpr int EPI_STAGE_WORDS = 32 * EPI_PITCH;
+constexpr int GEMM_THREADS = 64 + 32 * EPI_WARPS;
 
 template <int BN> struct GemmCfg {
     static constexpr int STAGES = BN == 256 ? 4 : 6;
@@ -38,12 +40,26 @@ template <int BN> struct GemmCfg {
     static constexpr int B_BYTES = BN * BK * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
     static constexpr int TMEM_COLS = 2 * BN;
-    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 4 * EPI_STAGE_WORDS * 4 + 256 + 1024;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_WARPS * EPI_STAGE_WORDS * 4 + 256 + 1024;
 };
 
 template <int ACT> __device__ __forceinline__ float apply_act(float v) {
-    if (ACT == ACT_QUICK_GELU) return __fdividef(v, 1.0f + __expf(-1.702f * v));
+    if (ACT == ACT_QUICK_GELU) {       // x * sigmoid(1.702 x) = x * (0.5 + 0.5 tanh(0.851 x)): one MUFU op
+        float t;
+        asm("tanh.approx.f32 %0, %1;" : "=f"(t) : "f"(0.851f * v));
+        return v * fmaf(0.5f, t, 0.5f);
+    }
     return 0.5f * v * (1.0f + erff(v * 0.70710678118654752f));
+}
+__device__ __forceinline__ void red_add_v4(float* addr, float4 v) {
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(v.x), "f"(v.y), "f"(v.z), "f"(v.w) : "memory");
+}
+__device__ __forceinline__ void tmem_ld_32x16(uint32_t taddr, uint32_t (&v)[16]) {
+    asm volatile(
+        "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+        : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]),
+          "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15])
+        : "r"(taddr));
 }
 __device__ __forceinline__ uint2 pack4_bf16(float a, float b, float c, float d) {
     __nv_bfloat162 lo = __floats2bfloat162_rn(a, b), hi = __floats2bfloat162_rn(c, d);
@@ -52,14 +68,14 @@ __device__ __forceinline__ uint2 pack4_bf16(float a, float b, float c, float d) 
 }
 
 template <int BN, int EPI, int ACT>
-__global__ void __launch_bounds__(192, 1)
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, GemmParams p) {
     using Cfg = GemmCfg<BN>;
     constexpr int STAGES = Cfg::STAGES;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     float* epi_stage = reinterpret_cast<float*>(smem + STAGES * Cfg::STAGE_BYTES);
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * Cfg::STAGE_BYTES + 4 * EPI_STAGE_WORDS * 4);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * Cfg::STAGE_BYTES + EPI_WARPS * EPI_STAGE_WORDS * 4);
     uint64_t* full = bars;                  // [STAGES]  TMA -> MMA
     uint64_t* empty = bars + STAGES;        // [STAGES]  MMA -> TMA
     uint64_t* acc_full = bars + 2 * STAGES; // [2]       MMA -> epilogue
@@ -75,7 +91,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         tma_prefetch_desc(&tmA);
         tma_prefetch_desc(&tmB);
         for (int s = 0; s < STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
-        for (int a = 0; a < 2; ++a) { mbar_init(&acc_full[a], 1); mbar_init(&acc_empty[a], 4); }
+        for (int a = 0; a < 2; ++a) { mbar_init(&acc_full[a], 1); mbar_init(&acc_empty[a], EPI_WARPS); }
         fence_mbar_init();
     }
     if (warp == 1) tmem_alloc(tmem_slot, Cfg::TMEM_COLS);
@@ -124,8 +140,9 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         }
     } else {
         const int q = warp & 3;                       // TMEM lane quarter this warp may read
+        const int half = (warp - 2) >> 2;             // which 16-column sub-chunks (even / odd) this warp stores
         float* stg = epi_stage + (warp - 2) * EPI_STAGE_WORDS;
-        const int sub_r = lane >> 3, c4 = (lane & 7) * 4;   // store phase: 8 lanes cover 32 columns of one row
+        const int sub_r = lane >> 2, c4 = (lane & 3) * 4;   // store phase: 4 lanes cover 16 columns of one row, 8 rows per pass
         int it = 0; bool ok = true;
         for (int t = blockIdx.x; t < tiles && ok; t += gridDim.x, ++it) {
             const int m0 = (t / tiles_n) * BM, n0 = (t % tiles_n) * BN;
@@ -134,66 +151,52 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
             tc_fence_after();
             const int row_base = m0 + q * 32;
             const uint32_t tsrc = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN;
-            const int nchunks = min(BN / 32, (p.N - n0 + 31) / 32);
-            uint32_t v[32];
-            tmem_ld_32x32(tsrc, v);
+            const int nsub = min(BN / 16, (p.N - n0 + 15) / 16);
+            uint32_t v[16];
+            if (half < nsub) tmem_ld_32x16(tsrc + half * 16, v);
+            else {                                    // nothing to store for this warp: hand the accumulator back at once
+                tc_fence_before();
+                if (lane == 0) mbar_arrive(&acc_empty[as]);
+            }
 #pragma unroll 1
-            for (int c = 0; c < nchunks; ++c) {
+            for (int c = half; c < nsub; c += 2) {
                 tmem_ld_wait();
                 float4* s4 = reinterpret_cast<float4*>(stg + lane * EPI_PITCH);
 #pragma unroll
-                for (int j = 0; j < 8; ++j)
+                for (int j = 0; j < 4; ++j)
                     s4[j] = make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]), __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3]));
-                if (c + 1 < nchunks) tmem_ld_32x32(tsrc + (c + 1) * 32, v);     // in flight while this chunk is stored
+                if (c + 2 < nsub) tmem_ld_32x16(tsrc + (c + 2) * 16, v);       // in flight while this sub-chunk is stored
                 else {                                                         // accumulator fully read: hand it back
                     tc_fence_before();
                     __syncwarp();
                     if (lane == 0) mbar_arrive(&acc_empty[as]);
                 }
                 __syncwarp();
-                const int col = n0 + c * 32 + c4;
+                const int col = n0 + c * 16 + c4;
                 const bool col_ok = col < p.N;                                 // N % 4 == 0
                 float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f);
                 if (p.bias != nullptr && col_ok) b4 = __ldg(reinterpret_cast<const float4*>(p.bias + col));
-                float4 a[8];
+                float4 a[4];
 #pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    a[i] = *reinterpret_cast<const float4*>(stg + (i * 4 + sub_r) * EPI_PITCH + c4);
+                for (int i = 0; i < 4; ++i) {
+                    a[i] = *reinterpret_cast<const float4*>(stg + (i * 8 + sub_r) * EPI_PITCH + c4);
                     a[i].x += b4.x; a[i].y += b4.y; a[i].z += b4.z; a[i].w += b4.w;
                 }
-                if (EPI == EPI_BIAS_RES_F32) {
-                    float* o = reinterpret_cast<float*>(p.out);
-                    float4 x[8];
 #pragma unroll
-                    for (int i = 0; i < 8; ++i) {
-                        const int row = row_base + i * 4 + sub_r;
-                        if (row < p.M && col_ok) x[i] = *reinterpret_cast<const float4*>(o + (size_t)row * p.ldc + col);
-                    }
-#pragma unroll
-                    for (int i = 0; i < 8; ++i) {
-                        const int row = row_base + i * 4 + sub_r;
-                        if (row < p.M && col_ok)
-                            *reinterpret_cast<float4*>(o + (size_t)row * p.ldc + col) =
-                                make_float4(x[i].x + a[i].x, x[i].y + a[i].y, x[i].z + a[i].z, x[i].w + a[i].w);
-                    }
-                } else if (EPI == EPI_F32) {
-                    float* o = reinterpret_cast<float*>(p.out);
-#pragma unroll
-                    for (int i = 0; i < 8; ++i) {
-                        const int row = row_base + i * 4 + sub_r;
-                        if (row < p.M && col_ok) *reinterpret_cast<float4*>(o + (size_t)row * p.ldc + col) = a[i];
-                    }
-                } else {
-                    __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out);
-#pragma unroll
-                    for (int i = 0; i < 8; ++i) {
-                        const int row = row_base + i * 4 + sub_r;
+                for (int i = 0; i < 4; ++i) {
+                    const int row = row_base + i * 8 + sub_r;
+                    if (row >= p.M || !col_ok) continue;
+                    if (EPI == EPI_BIAS_RES_F32) {     // x += acc + bias: one fire-and-forget vector reduction per 16 bytes
+                        red_add_v4(reinterpret_cast<float*>(p.out) + (size_t)row * p.ldc + col, a[i]);
+                    } else if (EPI == EPI_F32) {
+                        *reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + (size_t)row * p.ldc + col) = a[i];
+                    } else {
                         if (EPI == EPI_BIAS_ACT_BF16) {
                             a[i].x = apply_act<ACT>(a[i].x); a[i].y = apply_act<ACT>(a[i].y);
                             a[i].z = apply_act<ACT>(a[i].z); a[i].w = apply_act<ACT>(a[i].w);
                         }
-                        if (row < p.M && col_ok)
-                            *reinterpret_cast<uint2*>(o + (size_t)row * p.ldc + col) = pack4_bf16(a[i].x, a[i].y, a[i].z, a[i].w);
+                        *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(p.out) + (size_t)row * p.ldc + col) =
+                            pack4_bf16(a[i].x, a[i].y, a[i].z, a[i].w);
                     }
                 }
                 __syncwarp();
@@ -240,7 +243,7 @@ template <int BN, int EPI, int ACT> static int launch_gemm(const CUtensorMap& ta
     B200_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<BN, EPI, ACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
     const int tiles = ((p.M + BM - 1) / BM) * ((p.N + BN - 1) / BN);
     const int grid = tiles < kNumSMs ? tiles : kNumSMs;
-    gemm_tc_kernel<BN, EPI, ACT><<<grid, 192, Cfg::SMEM_BYTES, st>>>(ta, tb, p);
+    gemm_tc_kernel<BN, EPI, ACT><<<grid, GEMM_THREADS, Cfg::SMEM_BYTES, st>>>(ta, tb, p);
     B200_CUDA_OK(cudaGetLastError());
     return B200_OK;
 }

@@ -113,41 +113,80 @@ __device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
     return *reinterpret_cast<uint32_t*>(&t);
 }
 
-__device__ __forceinline__ void load_tile64(__nv_bfloat16* dst, const __nv_bfloat16* src, int row0, int nrows_valid, int ld) {
-    // 64 rows x 64 bf16 (128 B per row) -> 512 16-byte vectors over 128 threads; rows past the end are zero-filled.
+__device__ __forceinline__ void cp_async16_zfill(void* smem_dst, const void* gsrc, bool valid) {
+    const int n = valid ? 16 : 0;       // src-size 0 -> the 16 destination bytes are zero-filled
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(smem_dst)), "l"(gsrc), "r"(n) : "memory");
+}
+// 64 rows x 64 bf16 (128 B per row) -> 512 16-byte vectors over 128 threads; rows past the end are zero-filled.
+__device__ __forceinline__ void load_tile64_async(__nv_bfloat16* dst, const __nv_bfloat16* src, int row0, int nrows_valid, int ld) {
+#pragma unroll
     for (int i = threadIdx.x; i < 512; i += 128) {
         const int r = i >> 3, c = (i & 7) * 8;
-        uint4 v = make_uint4(0, 0, 0, 0);
-        if (row0 + r < nrows_valid) v = *reinterpret_cast<const uint4*>(src + (size_t)(row0 + r) * ld + c);
-        *reinterpret_cast<uint4*>(dst + r * ATT_PITCH + c) = v;
+        const bool ok = row0 + r < nrows_valid;
+        cp_async16_zfill(dst + r * ATT_PITCH + c, src + (size_t)(ok ? row0 + r : 0) * ld + c, ok);
     }
 }
 
-__global__ void __launch_bounds__(128) attention_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict__ out,
-                                                        int S, int d) {
-    __shared__ __align__(16) __nv_bfloat16 sQ[64 * ATT_PITCH], sK[64 * ATT_PITCH], sV[64 * ATT_PITCH];
-    const int qt = blockIdx.x, h = blockIdx.y, b = blockIdx.z;
+// Persistent CTAs walk a flat list of (image, head, 64-query tile) items; every step consumes one 64-key tile of
+// K and V.  The next step's tiles (and the next item's Q tile) are fetched with cp.async into the other buffer
+// while the current step computes, so global-load latency overlaps the MMAs and softmax.
+constexpr int ATT_TILE = 64 * ATT_PITCH;          // bf16 elements per staged tile
+constexpr int ATT_SMEM = 6 * ATT_TILE * 2;        // Q, K, V double buffered
+
+__global__ void __launch_bounds__(128, 4) attention_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict__ out,
+                                                           int S, int d, int heads, int n_qt, int total_items) {
+    extern __shared__ __align__(16) __nv_bfloat16 att_sm[];
+    __nv_bfloat16* sQ = att_sm;                    // [2][ATT_TILE]
+    __nv_bfloat16* sK = att_sm + 2 * ATT_TILE;
+    __nv_bfloat16* sV = att_sm + 4 * ATT_TILE;
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
     const int ld = 3 * d;
-    const __nv_bfloat16* base = qkv + (size_t)b * S * ld + h * 64;
-    load_tile64(sQ, base, qt * 64, S, ld);
-    __syncthreads();
-    uint32_t qa[4][4];
-#pragma unroll
-    for (int ks = 0; ks < 4; ++ks)
-        ldsm_x4(qa[ks], sQ + (warp * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * ATT_PITCH + ks * 16 + (lane >> 4) * 8);
-
-    float o[8][4];
-#pragma unroll
-    for (int i = 0; i < 8; ++i) o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f;
-    float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
+    const int n_kt = (S + 63) >> 6;
     const float sl2 = 0.125f * 1.4426950408889634f;   // 64^-0.5 * log2(e)
 
-    for (int k0 = 0; k0 < S; k0 += 64) {
-        __syncthreads();                               // previous tile fully consumed
-        load_tile64(sK, base + d, k0, S, ld);
-        load_tile64(sV, base + 2 * d, k0, S, ld);
+    auto item_base = [&](int item, int& qt) -> const __nv_bfloat16* {
+        qt = item % n_qt;
+        const int bh = item / n_qt, h = bh % heads, b = bh / heads;
+        return qkv + (size_t)b * S * ld + h * 64;
+    };
+    auto issue = [&](int item, int kt, int buf, int qbuf) {
+        int qt;
+        const __nv_bfloat16* base = item_base(item, qt);
+        if (kt == 0) load_tile64_async(sQ + qbuf * ATT_TILE, base, qt * 64, S, ld);
+        load_tile64_async(sK + buf * ATT_TILE, base + d, kt * 64, S, ld);
+        load_tile64_async(sV + buf * ATT_TILE, base + 2 * d, kt * 64, S, ld);
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+
+    int item = blockIdx.x, kt = 0, step = 0, local_item = 0;
+    if (item >= total_items) return;
+    issue(item, 0, 0, 0);
+    uint32_t qa[4][4];
+    float o[8][4];
+    float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
+    while (item < total_items) {
+        // next step: same item / next key tile, or first tile of this CTA's next item
+        int n_item = item, n_kt_idx = kt + 1, n_local = local_item;
+        if (n_kt_idx == n_kt) { n_item = item + gridDim.x; n_kt_idx = 0; n_local = local_item + 1; }
+        if (n_item < total_items) {
+            issue(n_item, n_kt_idx, (step + 1) & 1, n_local & 1);
+            asm volatile("cp.async.wait_group 1;" ::: "memory");
+        } else {
+            asm volatile("cp.async.wait_group 0;" ::: "memory");
+        }
         __syncthreads();
+        const __nv_bfloat16* cK = sK + (step & 1) * ATT_TILE;
+        const __nv_bfloat16* cV = sV + (step & 1) * ATT_TILE;
+        if (kt == 0) {
+            const __nv_bfloat16* cQ = sQ + (local_item & 1) * ATT_TILE;
+#pragma unroll
+            for (int ks = 0; ks < 4; ++ks)
+                ldsm_x4(qa[ks], cQ + (warp * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * ATT_PITCH + ks * 16 + (lane >> 4) * 8);
+#pragma unroll
+            for (int i = 0; i < 8; ++i) o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f;
+            m0 = m1 = -INFINITY; l0 = l1 = 0.f;
+        }
+        const int k0 = kt * 64;
         float s[8][4];
 #pragma unroll
         for (int i = 0; i < 8; ++i) s[i][0] = s[i][1] = s[i][2] = s[i][3] = 0.f;
@@ -156,11 +195,10 @@ __global__ void __launch_bounds__(128) attention_kernel(const __nv_bfloat16* __r
 #pragma unroll
             for (int np = 0; np < 4; ++np) {
                 uint32_t kb[4];
-                ldsm_x4(kb, sK + (np * 16 + (lane & 7) + (lane >> 4) * 8) * ATT_PITCH + ks * 16 + ((lane >> 3) & 1) * 8);
+                ldsm_x4(kb, cK + (np * 16 + (lane & 7) + (lane >> 4) * 8) * ATT_PITCH + ks * 16 + ((lane >> 3) & 1) * 8);
                 mma_bf16(s[2 * np], qa[ks], kb[0], kb[1]);
                 mma_bf16(s[2 * np + 1], qa[ks], kb[2], kb[3]);
             }
-        // mask keys past the sequence end, running max
         float mx0 = m0, mx1 = m1;
 #pragma unroll
         for (int nt = 0; nt < 8; ++nt) {
@@ -191,20 +229,26 @@ __global__ void __launch_bounds__(128) attention_kernel(const __nv_bfloat16* __r
 #pragma unroll
             for (int dp = 0; dp < 4; ++dp) {
                 uint32_t vb[4];
-                ldsm_x4_t(vb, sV + (kk * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * ATT_PITCH + dp * 16 + (lane >> 4) * 8);
+                ldsm_x4_t(vb, cV + (kk * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * ATT_PITCH + dp * 16 + (lane >> 4) * 8);
                 mma_bf16(o[2 * dp], pa[kk], vb[0], vb[1]);
                 mma_bf16(o[2 * dp + 1], pa[kk], vb[2], vb[3]);
             }
-    }
-    l0 += __shfl_xor_sync(0xffffffffu, l0, 1); l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
-    l1 += __shfl_xor_sync(0xffffffffu, l1, 1); l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
-    const float i0 = 1.f / l0, i1 = 1.f / l1;
-    const int r0 = qt * 64 + warp * 16 + g, r1 = r0 + 8;
-    __nv_bfloat16* ob = out + (size_t)b * S * d + h * 64;
+        if (kt == n_kt - 1) {
+            float t0 = l0, t1 = l1;
+            t0 += __shfl_xor_sync(0xffffffffu, t0, 1); t0 += __shfl_xor_sync(0xffffffffu, t0, 2);
+            t1 += __shfl_xor_sync(0xffffffffu, t1, 1); t1 += __shfl_xor_sync(0xffffffffu, t1, 2);
+            const float i0 = 1.f / t0, i1 = 1.f / t1;
+            const int qt = item % n_qt, bh = item / n_qt, h = bh % heads, b = bh / heads;
+            const int r0 = qt * 64 + warp * 16 + g, r1 = r0 + 8;
+            __nv_bfloat16* ob = out + (size_t)b * S * d + h * 64;
 #pragma unroll
-    for (int dt = 0; dt < 8; ++dt) {
-        if (r0 < S) *reinterpret_cast<uint32_t*>(ob + (size_t)r0 * d + dt * 8 + 2 * t) = pack_bf16(o[dt][0] * i0, o[dt][1] * i0);
-        if (r1 < S) *reinterpret_cast<uint32_t*>(ob + (size_t)r1 * d + dt * 8 + 2 * t) = pack_bf16(o[dt][2] * i1, o[dt][3] * i1);
+            for (int dt = 0; dt < 8; ++dt) {
+                if (r0 < S) *reinterpret_cast<uint32_t*>(ob + (size_t)r0 * d + dt * 8 + 2 * t) = pack_bf16(o[dt][0] * i0, o[dt][1] * i0);
+                if (r1 < S) *reinterpret_cast<uint32_t*>(ob + (size_t)r1 * d + dt * 8 + 2 * t) = pack_bf16(o[dt][2] * i1, o[dt][3] * i1);
+            }
+        }
+        __syncthreads();                               // this step's K/V (and Q) buffers may now be overwritten
+        item = n_item; kt = n_kt_idx; local_item = n_local; ++step;
     }
 }
 
@@ -230,9 +274,14 @@ int launch_l2_normalize(const float* in, float* out, int rows, int D, cudaStream
 }
 int launch_attention(const void* qkv, void* out, int B, int S, int d, int heads, cudaStream_t st) {
     B200_REQUIRE(d == heads * 64, "attention: head_dim must be 64");
-    B200_REQUIRE(B <= 65535 && heads <= 65535, "attention: grid too large");
-    attention_kernel<<<dim3((S + 63) / 64, heads, B), 128, 0, st>>>(reinterpret_cast<const __nv_bfloat16*>(qkv),
-                                                                    reinterpret_cast<__nv_bfloat16*>(out), S, d);
+    B200_REQUIRE(B > 0 && S > 0, "attention: empty batch");
+    const int n_qt = (S + 63) / 64;
+    const long long items = (long long)B * heads * n_qt;
+    B200_REQUIRE(items < (1LL << 30), "attention: too many (image, head, tile) items");
+    B200_CUDA_OK(cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_SMEM));
+    const int grid = (int)(items < 4LL * kNumSMs ? items : 4LL * kNumSMs);
+    attention_kernel<<<grid, 128, ATT_SMEM, st>>>(reinterpret_cast<const __nv_bfloat16*>(qkv), reinterpret_cast<__nv_bfloat16*>(out),
+                                                  S, d, heads, n_qt, (int)items);
     B200_CUDA_OK(cudaGetLastError());
     return B200_OK;
 }

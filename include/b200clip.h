@@ -117,6 +117,19 @@ int b200clip_topk(b200clip_handle* h, const void* queries_f16_dev, int32_t Q, co
 int b200clip_merge_topk(b200clip_handle* h, const float* part_scores_dev, const int64_t* part_index_dev, int32_t parts,
                         int32_t Q, int32_t k, float* out_scores_dev, int64_t* out_index_dev, void* stream);
 
+/* Search without any allocation.  No counterpart in the reference: it exists for callers that are not allowed to
+ * allocate device memory at the moment they search — a host thread whose stream is being captured into a CUDA graph,
+ * a real-time serving loop that must not hit the allocator's locks, or a plug-in living inside another framework's
+ * memory pool.  Same kernels, arguments and results as b200clip_topk, but no handle: the scratch (candidate lists and
+ * per-split results) is a fixed 32 MiB array compiled into the library, which every GPU that loads the library keeps
+ * until exit.  It runs on the CURRENT device.  Limits: k <= 256 and Q*k small enough for the array (roughly 7000
+ * queries at k = 100); larger requests fail with B200CLIP_EINVAL and a message naming the limit.  The first call on
+ * each device resolves the array's device address (cudaGetSymbolAddress) — make that first call outside any stream
+ * capture.  All calls share the one array, so two calls whose kernels overlap on the GPU (different streams or
+ * threads) race; serialise them.  It calls neither cudaMalloc nor cudaFree nor any allocating library routine. */
+int b200clip_topk_static(const void* queries_f16_dev, int32_t Q, const void* gallery_f16_dev, int64_t N, int32_t D,
+                         int32_t k, int64_t index_base, float* out_scores_dev, int64_t* out_index_dev, void* stream);
+
 /* Building blocks exported for the parity tests (same kernels the calls above use). */
 int b200clip_gemm_bf16(b200clip_handle* h, const void* A_bf16_dev, const void* W_bf16_dev, int32_t M, int32_t N, int32_t K,
                        const float* bias_dev, void* out_dev, int32_t epilogue, int32_t activation, void* stream);

@@ -16,6 +16,8 @@
 #include "common.cuh"
 #include "kernels.h"
 
+#include <mutex>
+
 namespace b200 {
 
 constexpr int TK_BM = 128, TK_BN = 256, TK_BK = 64, TK_STAGES = 4;
@@ -348,3 +350,69 @@ int topk_run(const void* queries, const void* gallery, int Q, long long N, int D
 }
 
 }  // namespace b200
+
+// ------------------------------------------------------------------------------------------ allocation-free search
+// Scratch for b200clip_topk_static: lives in the library image, so every GPU that loads libb200clip holds these
+// bytes until the process exits.  First 256 bytes: watchdog status words; the rest: candidate lists + per-split results.
+namespace {
+constexpr size_t kStaticScratchBytes = 32u << 20;
+__device__ __align__(256) unsigned char g_topk_static_scratch[kStaticScratchBytes];
+std::mutex g_static_mu;
+void* g_static_ptr[64] = {nullptr};          // device address of the array, resolved once per device
+}  // namespace
+
+#include "../../include/b200clip.h"
+
+extern "C" int b200clip_topk_static(const void* queries_f16_dev, int32_t Q, const void* gallery_f16_dev, int64_t N, int32_t D,
+                                    int32_t k, int64_t index_base, float* out_scores_dev, int64_t* out_index_dev, void* stream) {
+    using namespace b200;
+    B200_REQUIRE(queries_f16_dev && gallery_f16_dev && out_scores_dev && out_index_dev, "topk_static: null buffer");
+    B200_REQUIRE(Q > 0 && N > 0 && k > 0, "topk_static: Q, N and k must be positive");
+    B200_REQUIRE(k <= 256, "topk_static: k is limited to 256 (the handle-based b200clip_topk goes to 768)");
+    int dev = -1;
+    B200_CUDA_OK(cudaGetDevice(&dev));
+    B200_REQUIRE(dev >= 0 && dev < 64, "topk_static: unsupported device ordinal");
+    void* base = nullptr;
+    {
+        // One-time set-up per device, with that device current.  In host code the array's name is only a stand-in
+        // for the symbol; the address a kernel can use has to be asked for.
+        std::lock_guard<std::mutex> lk(g_static_mu);
+        if (g_static_ptr[dev] == nullptr) {
+            void* ptr = nullptr;
+            const cudaError_t e = cudaGetSymbolAddress(&ptr, g_topk_static_scratch);
+            if (e != cudaSuccess) return fail(B200_ECUDA, std::string("topk_static: cudaGetSymbolAddress: ") + cudaGetErrorString(e));
+            g_static_ptr[dev] = ptr;
+        }
+        base = g_static_ptr[dev];
+    }
+    // Same work split as b200clip_topk, shrunk until candidate lists + per-split results fit the fixed array.
+    TopkPlan plan;
+    plan.cpl = 16;
+    plan.qtiles = (Q + TK_BM - 1) / TK_BM;
+    const long long ntiles = (N + TK_BN - 1) / TK_BN;
+    const size_t budget = kStaticScratchBytes - 256;
+    auto need = [&](long long splits) {
+        return (size_t)splits * plan.qtiles * TK_BM * 32 * 16 * 8 + (((size_t)splits * Q * k * 4 + 255) & ~(size_t)255) +
+               (size_t)splits * Q * k * 8 + 256;
+    };
+    long long splits = (2LL * kNumSMs) / plan.qtiles;
+    if (splits < 1) splits = 1;
+    if (splits > ntiles) splits = ntiles;
+    if (splits * k > 16384) splits = 16384 / k;
+    while (splits > 1 && need(splits) > budget) --splits;
+    if (need(splits) > budget)
+        return fail(B200_EINVAL, "topk_static: Q=" + std::to_string(Q) + ", k=" + std::to_string(k) + " needs " + std::to_string(need(splits)) +
+                                 " bytes of scratch, the built-in array holds " + std::to_string(budget) +
+                                 " (about 7000 queries at k=100); use b200clip_topk with a handle instead");
+    const long long tiles_per_split = (ntiles + splits - 1) / splits;
+    plan.rows_per_split = tiles_per_split * TK_BN;
+    plan.splits = (int)((ntiles + tiles_per_split - 1) / tiles_per_split);
+    plan.cand_bytes = (size_t)plan.splits * plan.qtiles * TK_BM * 32 * 16 * 8;
+    plan.part_bytes = (((size_t)plan.splits * Q * k * 4 + 255) & ~(size_t)255) + (size_t)plan.splits * Q * k * 8;
+    cudaStream_t st = (cudaStream_t)stream;
+    // The array keeps whatever the previous call left.  Only the watchdog words have to start at zero: candidate
+    // counts live in registers and every result slot that is read is written first.
+    B200_CUDA_OK(cudaMemsetAsync(base, 0, 256, st));
+    return topk_run(queries_f16_dev, gallery_f16_dev, Q, N, D, k, index_base, reinterpret_cast<unsigned char*>(base) + 256, plan,
+                    out_scores_dev, reinterpret_cast<long long*>(out_index_dev), reinterpret_cast<DeviceStatus*>(base), st);
+}

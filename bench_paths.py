@@ -1,0 +1,148 @@
+#!/usr/bin/env python
+"""Secondary measurements for the other SURVEY.md §8 rows (bench.py stays the headline contract):
+
+    python bench_paths.py preprocess   K1 at 224x224 / 640x480 / 1920x1080 -> 224 against the HBM roofline
+    python bench_paths.py search       K10+K12: Q sweep over an N x 512 fp16 gallery, k = 100 (both rooflines)
+    python bench_paths.py classify     K11: 256 images x 1000 labels (C3), microseconds
+    python bench_paths.py models       ViT-B/16 (C3) and ViT-L/14@336 (C4) embedding throughput
+    torchrun --nproc-per-node G bench_paths.py search --sharded   C5: gallery row-sharded over G GPUs, NCCL all-gather + merge
+
+Each line printed is JSON.  CUDA events on the launch stream; every timed loop is preceded by >= 3 warm-up runs; inputs
+larger than L2 unless noted."""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+from pathlib import Path
+
+import numpy as np
+
+ROOT = Path(__file__).resolve().parent
+sys.path.insert(0, str(ROOT))
+
+from bench import gemm_flops_per_image, peaks, total_flops_per_image  # noqa: E402
+from lumen_b200.vit_config import VIT_CONFIGS, synthetic_weights  # noqa: E402
+
+
+def timed(fn, iters, warm=3):
+    import torch
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / iters
+
+
+def bench_preprocess(args):
+    import torch
+    from lumen_b200.engine import Engine, pack_images
+    pk = peaks()
+    eng = Engine({"patch": 32}, device=0, image_size=224)
+    rng = np.random.default_rng(1234)
+    for (h, w), B in (((224, 224), 2048), ((480, 640), 512), ((1080, 1920), 128)):
+        img = rng.integers(0, 256, (h, w, 3), dtype=np.uint8)
+        imgs = [img] * B                                   # same pixels, distinct copies in the packed buffer
+        buf, off, hw, total = pack_images(imgs)
+        src = torch.from_numpy(buf[:total]).cuda()
+        out = torch.zeros((B * 49, 3072), dtype=torch.bfloat16, device="cuda")
+        import ctypes as C
+        from lumen_b200 import _lib
+
+        def run():
+            _lib.check(eng.lib.b200clip_preprocess(eng._h, C.c_void_p(src.data_ptr()), off.ctypes.data_as(C.c_void_p),
+                                                   hw.ctypes.data_as(C.c_void_p), B, 0, 1, 1, C.c_void_p(out.data_ptr()), eng._stream()))
+        ms = timed(run, 20)
+        bytes_alg = B * (h * w * 3 + 3 * 224 * 224 * 2)
+        gbs = bytes_alg / ms / 1e6
+        print(json.dumps({"path": "K1 preprocess", "src": f"{h}x{w}", "batch": B, "ms": ms, "images_per_s": B / ms * 1e3,
+                          "roofline": {"bound": "hbm", "achieved": gbs, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": gbs / pk["hbm_gbs"],
+                                       "algorithmic_bytes_per_image": h * w * 3 + 3 * 224 * 224 * 2}}), flush=True)
+    eng.close()
+
+
+def bench_search(args):
+    import torch
+    import torch.distributed as dist
+    from lumen_b200.engine import Engine
+    from lumen_b200.managers import ShardedGallery
+    pk = peaks()
+    world = int(os.environ.get("WORLD_SIZE", "1")); rank = int(os.environ.get("RANK", "0")); local = int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    eng = Engine({}, device=local)
+    N_total, D, k = args.gallery, 512, 100
+    lo, hi = ShardedGallery.shard_bounds(N_total, world, rank)
+    gen = torch.Generator(device="cuda").manual_seed(42 + rank)
+    g = torch.empty((hi - lo, D), dtype=torch.float16, device="cuda")
+    for s in range(0, hi - lo, 1 << 20):                   # generate the shard on the device, chunked
+        blk = torch.randn((min(1 << 20, hi - lo - s), D), device="cuda", generator=gen)
+        g[s:s + blk.shape[0]] = torch.nn.functional.normalize(blk, dim=1).half()
+    gal = ShardedGallery(eng, g, index_base=lo)
+    qs = [4096] if args.sharded else [1, 16, 64, 128, 512, 4096]
+    for Q in qs:
+        q = torch.nn.functional.normalize(torch.randn((Q, D), device="cuda", generator=torch.Generator(device="cuda").manual_seed(43)), dim=1).half()
+        ms = timed(lambda: gal.search(q, k), 5 if Q >= 512 else 10)
+        if world > 1:
+            t = torch.tensor([ms], device="cuda", dtype=torch.float64); dist.all_reduce(t, op=dist.ReduceOp.MAX); ms = float(t.item())
+        if rank == 0:
+            n_local = hi - lo
+            flops = 2.0 * Q * n_local * D
+            byts = n_local * D * 2 + Q * D * 2 + Q * k * 12
+            tf, gbs = flops / ms / 1e9, byts / ms / 1e6
+            print(json.dumps({"path": "K10+K12 gallery search", "Q": Q, "N_total": N_total, "N_per_gpu": n_local, "k": k, "n_gpus": world, "ms": ms,
+                              "queries_per_s": Q / ms * 1e3,
+                              "roofline": {"bound": "tensor" if Q > 222 else "hbm", "tensor_tflops": tf, "tensor_frac": tf / pk["bf16_burst"],
+                                           "hbm_gbs": gbs, "hbm_frac": gbs / pk["hbm_gbs"], "peaks": pk}}), flush=True)
+    eng.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def bench_classify(args):
+    import torch
+    from lumen_b200.engine import Engine
+    eng = Engine({}, device=0)
+    eng.set_labels(np.random.default_rng(7).standard_normal((1000, 512)).astype(np.float32))
+    q = torch.nn.functional.normalize(torch.randn((256, 512), device="cuda"), dim=1)
+    ms = timed(lambda: eng.classify(q, 5), 50)
+    print(json.dumps({"path": "K11 classify (C3 numerics)", "B": 256, "labels": 1000, "D": 512, "k": 5, "us": ms * 1e3,
+                      "note": "launch-latency bound: 262 MFLOP, 2 MB of labels"}), flush=True)
+    eng.close()
+
+
+def bench_models(args):
+    import torch
+    from lumen_b200.engine import Engine, pack_images
+    pk = peaks()
+    for name, B in (("ViT-B-16", 256), ("ViT-L-14-336", 256), ("ViT-B-32", 1)):
+        cfg = VIT_CONFIGS[name]
+        eng = Engine(cfg, device=0, max_batch=B)
+        eng.load_weights(synthetic_weights(cfg, 0))
+        S = cfg["image_size"]
+        imgs = list(np.random.default_rng(1).integers(0, 256, (B, S, S, 3), dtype=np.uint8))
+        buf, off, hw, total = pack_images(imgs)
+        src = torch.from_numpy(buf[:total]).cuda()
+        out = torch.empty((B, cfg["embed_dim"]), dtype=torch.float32, device="cuda")
+        ms = timed(lambda: eng.embed_u8(src, off, hw, 0, out=out), 5 if B > 1 else 50)
+        ips = B / ms * 1e3
+        print(json.dumps({"path": "embed (K1..K9)", "model": name, "batch": B, "ms": ms, "images_per_s": ips,
+                          "frac_of_tensor_peak_sustained": total_flops_per_image(cfg) * ips / 1e12 / pk["bf16_sustained"],
+                          "gflop_per_image": total_flops_per_image(cfg) / 1e9}), flush=True)
+        eng.close()
+
+
+if __name__ == "__main__":
+    ap = argparse.ArgumentParser()
+    ap.add_argument("what", choices=["preprocess", "search", "classify", "models"])
+    ap.add_argument("--gallery", type=int, default=1_250_000, help="total gallery rows (all GPUs)")
+    ap.add_argument("--sharded", action="store_true")
+    a = ap.parse_args()
+    {"preprocess": bench_preprocess, "search": bench_search, "classify": bench_classify, "models": bench_models}[a.what](a)

@@ -123,7 +123,7 @@ class ShardedGallery:
 
     def __init__(self, engine, shard_f16, index_base: int = 0, group=None) -> None:
         torch = _torch()
-        assert shard_f16.dtype == torch.float16 and shard_f16.is_cuda and shard_f16.is_contiguous()
+        assert shard_f16.dtype == torch.float16 and shard_f16.is_contiguous()
         self.engine, self.shard, self.index_base, self.group = engine, shard_f16, int(index_base), group
 
     @staticmethod
@@ -141,8 +141,12 @@ class ShardedGallery:
         world = dist.get_world_size(self.group)
         all_s = torch.empty((world,) + tuple(scores.shape), dtype=scores.dtype, device=scores.device)
         all_i = torch.empty((world,) + tuple(idx.shape), dtype=idx.dtype, device=idx.device)
-        dist.all_gather_into_tensor(all_s, scores, group=self.group)
-        dist.all_gather_into_tensor(all_i, idx, group=self.group)
+        if dist.get_backend(self.group) == "nccl":          # one fused collective per tensor over NVLink
+            dist.all_gather_into_tensor(all_s, scores, group=self.group)
+            dist.all_gather_into_tensor(all_i, idx, group=self.group)
+        else:                                                # gloo (CPU tests of the host logic)
+            dist.all_gather(list(all_s.unbind(0)), scores, group=self.group)
+            dist.all_gather(list(all_i.unbind(0)), idx, group=self.group)
         return self.engine.merge_topk(all_s, all_i)
 
 

@@ -86,7 +86,7 @@ def bench_search(args):
         blk = torch.randn((min(1 << 20, hi - lo - s), D), device="cuda", generator=gen)
         g[s:s + blk.shape[0]] = torch.nn.functional.normalize(blk, dim=1).half()
     gal = ShardedGallery(eng, g, index_base=lo)
-    qs = [4096] if args.sharded else [1, 16, 64, 128, 512, 4096]
+    qs = [int(x) for x in args.qs.split(",")] if args.qs else ([4096] if args.sharded else [1, 16, 64, 128, 512, 4096])
     for Q in qs:
         q = torch.nn.functional.normalize(torch.randn((Q, D), device="cuda", generator=torch.Generator(device="cuda").manual_seed(43)), dim=1).half()
         ms = timed(lambda: gal.search(q, k), 5 if Q >= 512 else 10)
@@ -144,5 +144,6 @@ if __name__ == "__main__":
     ap.add_argument("what", choices=["preprocess", "search", "classify", "models"])
     ap.add_argument("--gallery", type=int, default=1_250_000, help="total gallery rows (all GPUs)")
     ap.add_argument("--sharded", action="store_true")
+    ap.add_argument("--qs", default="", help="comma-separated query counts for the search sweep")
     a = ap.parse_args()
     {"preprocess": bench_preprocess, "search": bench_search, "classify": bench_classify, "models": bench_models}[a.what](a)

@@ -9,8 +9,8 @@
 // TMA -> tcgen05.mma -> TMEM pipeline as gemm_tc.cu (fp16 operands, fp32 accumulate).  The four epilogue
 // warps own one query row per thread: each score is compared with that row's running threshold tau (its
 // current k-th best) and survivors are appended, as 64-bit keys (order-preserving score bits | ~index), to a
-// per-(split, query) candidate list in global scratch.  When a list is about to overflow, the warp sorts it
-// cooperatively (register bitonic network), keeps the best k and raises tau.  Because a split is scanned in
+// per-(split, query) candidate list in global scratch.  When a list is about to overflow, the warp shrinks it
+// cooperatively (radix select of the k-th best key, no sort), keeps the best k and raises tau.  Because a split is scanned in
 // index order, "score > tau" is exact under the index-ordered tie rule.  A second kernel merges the
 // per-split (and, after the NCCL all-gather, per-GPU) lists with the same order.
 #include "common.cuh"
@@ -44,73 +44,99 @@ __device__ __forceinline__ float unflip_f32(uint32_t u) {
     return __uint_as_float((u & 0x80000000u) ? (u & 0x7fffffffu) : ~u);
 }
 
-// One compare-exchange stage of the bitonic network over 32*CPL keys (element e = reg*32 + lane); KK and J are
-// compile-time so every register index is static.
-template <int CPL, int KK, int J>
-__device__ __forceinline__ void bitonic_stage(unsigned long long (&key)[CPL], int lane) {
-    if constexpr (J >= 32) {
-        constexpr int rj = J >> 5;
-#pragma unroll
-        for (int i = 0; i < CPL; ++i) {
-            if ((i & rj) == 0) {
-                const bool desc = ((i * 32 + lane) & KK) == 0;
-                const unsigned long long a = key[i], b = key[i | rj];
-                const bool sw = desc ? (a < b) : (a > b);
-                key[i] = sw ? b : a;
-                key[i | rj] = sw ? a : b;
-            }
-        }
-    } else {
-        const bool lower = (lane & J) == 0;
-#pragma unroll
-        for (int i = 0; i < CPL; ++i) {
-            const unsigned long long o = __shfl_xor_sync(0xffffffffu, key[i], J);
-            const bool desc = ((i * 32 + lane) & KK) == 0;
-            const bool take_o = (lower == desc) ? (o > key[i]) : (o < key[i]);
-            key[i] = take_o ? o : key[i];
-        }
-    }
-}
-template <int CPL, int KK, int J>
-__device__ __forceinline__ void bitonic_from(unsigned long long (&key)[CPL], int lane) {
-    if constexpr (KK <= 32 * CPL) {
-        bitonic_stage<CPL, KK, J>(key, lane);
-        if constexpr (J > 1) bitonic_from<CPL, KK, J / 2>(key, lane);
-        else bitonic_from<CPL, KK * 2, KK>(key, lane);
-    }
-}
+// Whole warp: shrink one row's candidate list (n keys, 32*CPL at most) and return the new count.
+// No sort: a most-significant-bit-first radix select finds the k-th largest key (one warp-wide vote per key
+// register and bit, branch-free inside), then the survivors are compacted to the front in arrival order.
+//   exact == false (mid-scan): only the top 16 bits of the score are resolved.  The resulting threshold is a
+//     valid lower bound of the k-th best score, a few extra candidates survive, and the select costs a quarter.
+//     If too many candidates tie at that resolution to leave room for the next tile, it falls through to exact.
+//   exact == true (end of the split): full 32-bit score, then -- only if candidates tie at the k-th score --
+//     the low word picks the smallest indices.  With part_s/part_i the survivors are also written out as
+//     (score, global index), padded with (-inf, -1); the merge kernel sorts, so no order is needed here.
+// `tau_out` is the new threshold (-inf while fewer than k candidates exist).
 template <int CPL>
-__device__ __forceinline__ void warp_sort_desc(unsigned long long (&key)[CPL], int lane) { bitonic_from<CPL, 2, 1>(key, lane); }
-
-// Whole warp: sort the candidate list of one row, keep the best k.  Returns the new count; `tau_out` is the
-// k-th best score (or -inf while fewer than k candidates exist).  With part_s/part_i set (end of the split) the
-// sorted best k are also written out as (score, global index), padded with (-inf, -1).
-template <int CPL>
-__device__ __noinline__ int compact_row(unsigned long long* rowptr, int n, int k, int lane, float* tau_out,
-                                        float* part_s, long long* part_i, long long index_base) {
-    unsigned long long key[CPL];
+__device__ __noinline__ int compact_row(unsigned long long* rowptr, int n, int k, int lane, bool exact, int room,
+                                        float* tau_out, float* part_s, long long* part_i, long long index_base) {
+    uint32_t hi[CPL], lo[CPL];
     __syncwarp();
 #pragma unroll
     for (int i = 0; i < CPL; ++i) {
         const int e = i * 32 + lane;
-        key[i] = e < n ? __ldcg(rowptr + e) : 0ull;
+        const unsigned long long key = e < n ? __ldcg(rowptr + e) : 0ull;     // 0 sorts below every real key
+        hi[i] = (uint32_t)(key >> 32); lo[i] = (uint32_t)key;
     }
-    warp_sort_desc<CPL>(key, lane);
-    const int keep = n < k ? n : k;
-    unsigned long long kth = 0ull;
+    int keep = n;
+    float tau = -INFINITY;
+    if (n >= k) {
+        uint32_t p = 0, pl = 0; int kk = k;
+        auto select_hi = [&](int b_from, int b_to) {
+#pragma unroll 1
+            for (int b = b_from; b >= b_to; --b) {
+                const uint32_t want = p | (1u << b), m = 0xffffffffu << b;
+                int c0 = 0, c1 = 0, c2 = 0, c3 = 0;
 #pragma unroll
-    for (int i = 0; i < CPL; ++i) {
-        const int e = i * 32 + lane;
-        if (e == k - 1) kth = key[i];
-        if (e < keep) __stcg(rowptr + e, key[i]);
-        if (part_s != nullptr && e < k) {
-            const bool valid = e < n;
-            part_s[e] = valid ? unflip_f32((uint32_t)(key[i] >> 32)) : -INFINITY;
-            part_i[e] = valid ? index_base + (long long)(0xffffffffu - (uint32_t)(key[i] & 0xffffffffu)) : -1;
+                for (int i = 0; i < CPL; i += 4) {
+                    c0 += __popc(__ballot_sync(0xffffffffu, (hi[i] & m) == want));
+                    c1 += __popc(__ballot_sync(0xffffffffu, (hi[i + 1] & m) == want));
+                    c2 += __popc(__ballot_sync(0xffffffffu, (hi[i + 2] & m) == want));
+                    c3 += __popc(__ballot_sync(0xffffffffu, (hi[i + 3] & m) == want));
+                }
+                const int c = (c0 + c1) + (c2 + c3);
+                if (c >= kk) p = want; else kk -= c;
+            }
+        };
+        auto count_ge = [&]() {
+            int c = 0;
+#pragma unroll
+            for (int i = 0; i < CPL; ++i) c += __popc(__ballot_sync(0xffffffffu, hi[i] >= p));
+            return c;
+        };
+        select_hi(31, 16);
+        bool coarse = !exact;
+        if (coarse && count_ge() > room) coarse = false;   // degenerate: too many ties at 16-bit resolution
+        if (!coarse) {
+            select_hi(15, 0);
+            int ceq = 0;
+#pragma unroll
+            for (int i = 0; i < CPL; ++i) ceq += __popc(__ballot_sync(0xffffffffu, hi[i] == p));
+            if (ceq > kk) {                                // ties at the k-th score: kk-th largest low word = kk-th smallest index
+#pragma unroll 1
+                for (int b = 31; b >= 0; --b) {
+                    const uint32_t want = pl | (1u << b), m = 0xffffffffu << b;
+                    int c = 0;
+#pragma unroll
+                    for (int i = 0; i < CPL; ++i) c += __popc(__ballot_sync(0xffffffffu, hi[i] == p && (lo[i] & m) == want));
+                    if (c >= kk) pl = want; else kk -= c;
+                }
+            }
+        }
+        int base = 0;
+        const uint32_t lt = (1u << lane) - 1u;
+#pragma unroll
+        for (int i = 0; i < CPL; ++i) {
+            const bool pred = hi[i] > p || (hi[i] == p && lo[i] >= pl);
+            const uint32_t bal = __ballot_sync(0xffffffffu, pred);
+            const int pos = base + __popc(bal & lt);
+            if (pred) {
+                __stcg(rowptr + pos, ((unsigned long long)hi[i] << 32) | lo[i]);
+                if (part_s != nullptr && pos < k) { part_s[pos] = unflip_f32(hi[i]); part_i[pos] = index_base + (long long)(0xffffffffu - lo[i]); }
+            }
+            base += __popc(bal);
+        }
+        keep = base;
+        tau = unflip_f32(p);
+    } else if (part_s != nullptr) {
+#pragma unroll
+        for (int i = 0; i < CPL; ++i) {
+            const int e = i * 32 + lane;
+            if (e < k) {
+                const bool valid = e < n;
+                part_s[e] = valid ? unflip_f32(hi[i]) : -INFINITY;
+                part_i[e] = valid ? index_base + (long long)(0xffffffffu - lo[i]) : -1;
+            }
         }
     }
-    kth = __shfl_sync(0xffffffffu, kth, (k - 1) & 31);
-    *tau_out = n >= k ? unflip_f32((uint32_t)(kth >> 32)) : -INFINITY;
+    *tau_out = tau;
     __syncwarp();
     return keep;
 }
@@ -191,7 +217,7 @@ topk_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         const long long qrow = (long long)qt * TK_BM + row;
         unsigned long long* rowptr = p.cand + ((size_t)sp * p.qtiles * TK_BM + (size_t)qrow) * C;
         unsigned long long* warp_rows = p.cand + ((size_t)sp * p.qtiles * TK_BM + (size_t)qt * TK_BM + q * 32) * C;
-        float tau = -INFINITY;
+        float tau = qrow < p.Q ? -INFINITY : INFINITY;      // padding rows of the last query tile never collect candidates
         int cnt = 0;
         bool ok = true;
         for (int t = 0; t < tiles && ok; ++t) {
@@ -224,7 +250,7 @@ topk_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
                 need &= need - 1;
                 const int n = __shfl_sync(0xffffffffu, cnt, src);
                 float tnew;
-                const int keep = compact_row<CPL>(warp_rows + (size_t)src * C, n, p.k, lane, &tnew, nullptr, nullptr, 0);
+                const int keep = compact_row<CPL>(warp_rows + (size_t)src * C, n, p.k, lane, false, C - TK_BN, &tnew, nullptr, nullptr, 0);
                 if (lane == src) { cnt = keep; tau = tnew; }
             }
         }
@@ -234,7 +260,7 @@ topk_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
             float tnew;
             const long long qr = (long long)qt * TK_BM + q * 32 + src;
             if (qr < p.Q)       // warp-uniform
-                compact_row<CPL>(warp_rows + (size_t)src * C, n, p.k, lane, &tnew, p.part_scores + ((size_t)sp * p.Q + qr) * p.k,
+                compact_row<CPL>(warp_rows + (size_t)src * C, n, p.k, lane, true, C, &tnew, p.part_scores + ((size_t)sp * p.Q + qr) * p.k,
                                  p.part_idx + ((size_t)sp * p.Q + qr) * p.k, p.index_base);
         }
     }
@@ -244,36 +270,126 @@ topk_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
 }
 
 // ------------------------------------------------------------------------------------------ merge (K12)
-// parts: scores [P][Q][k] fp32, idx [P][Q][k] int64 (idx < 0 = empty slot).  One CTA per query sorts the
-// P*k candidates in shared memory (bitonic, score descending then index ascending) and writes the best k.
+// parts: scores [P][Q][k] fp32, idx [P][Q][k] int64 (idx < 0 = empty slot), in any order.  One CTA per query:
+//   1. block radix select (8 bits per pass, shared-memory histogram) of the k-th best score over the P*k candidates,
+//   2. if more candidates tie with that score than fit, a second select keeps the smallest indices among them,
+//   3. the <= k survivors are gathered into shared memory and sorted there (score descending, index ascending).
+// Work is O(P*k) per query instead of a full sort of P*k entries.
 __device__ __forceinline__ bool better(float sa, long long ia, float sb, long long ib) {
     return sa > sb || (sa == sb && ia < ib);
 }
+constexpr int MERGE_THREADS = 256;
+constexpr int MERGE_KMAX = 1024;
 
-__global__ void __launch_bounds__(256) merge_topk_kernel(const float* __restrict__ ps, const long long* __restrict__ pi, int P,
-                                                         int Q, int k, int np2, float* __restrict__ out_s,
-                                                         long long* __restrict__ out_i) {
-    extern __shared__ __align__(16) uint8_t msm[];
-    long long* si = reinterpret_cast<long long*>(msm);
-    float* ss = reinterpret_cast<float*>(msm + (size_t)np2 * 8);
-    const int qi = blockIdx.x;
-    const int total = P * k;
-    for (int e = threadIdx.x; e < np2; e += blockDim.x) {
-        float s = -INFINITY; long long i = 0x7fffffffffffffffLL;
-        if (e < total) {
-            const int part = e / k, j = e - part * k;
-            const long long id = pi[((size_t)part * Q + qi) * k + j];
-            if (id >= 0) { i = id; s = ps[((size_t)part * Q + qi) * k + j] + 0.0f; }
+// Finds the digit d (scanning from `hi_first ? 255 : 0`) where the running count reaches kk; returns it and
+// the count before it.  Called by all threads after the histogram is complete; thread 0 scans.
+__device__ __forceinline__ void scan_hist(const int* hist, int kk, bool hi_first, int* sh_digit, int* sh_before) {
+    if (threadIdx.x == 0) {
+        int acc = 0, d = hi_first ? 255 : 0;
+        for (int s = 0; s < 256; ++s) {
+            d = hi_first ? 255 - s : s;
+            if (acc + hist[d] >= kk) break;
+            acc += hist[d];
         }
-        ss[e] = s; si[e] = i;
+        *sh_digit = d; *sh_before = acc;
+    }
+}
+
+__global__ void __launch_bounds__(MERGE_THREADS) merge_topk_kernel(const float* __restrict__ ps, const long long* __restrict__ pi, int P,
+                                                                   int Q, int k, float* __restrict__ out_s, long long* __restrict__ out_i) {
+    __shared__ int hist[256];
+    __shared__ int sh_digit, sh_before, sh_count, sh_gt, sh_eq;
+    __shared__ float ss[MERGE_KMAX];
+    __shared__ long long si[MERGE_KMAX];
+    const int qi = blockIdx.x, T = P * k, tid = threadIdx.x;
+    auto elem = [&](int e, float& s, long long& id) {
+        const int part = e / k, j = e - part * k;
+        const size_t o = ((size_t)part * Q + qi) * k + j;
+        id = pi[o]; s = ps[o] + 0.0f;
+    };
+    if (tid == 0) { sh_count = 0; sh_gt = 0; sh_eq = 0; }
+    // ---- k-th best score: 4 passes of 8 bits over the order-preserving 32-bit image of the score
+    uint32_t prefix = 0; int kk = k; bool all = false;
+    for (int pass = 0; pass < 4; ++pass) {
+        const int shift = 24 - 8 * pass;
+        hist[tid] = 0;
+        __syncthreads();
+        for (int e = tid; e < T; e += MERGE_THREADS) {
+            float s; long long id; elem(e, s, id);
+            if (id < 0) continue;
+            const uint32_t key = flip_f32(s);
+            if (pass == 0 || (key >> (shift + 8)) == (prefix >> (shift + 8))) atomicAdd(&hist[(key >> shift) & 255], 1);
+        }
+        __syncthreads();
+        if (pass == 0) {                                   // fewer valid candidates than k: keep them all
+            int tot = 0;
+            for (int d = 0; d < 256; ++d) tot += hist[d];
+            if (tot <= k) { all = true; break; }
+        }
+        scan_hist(hist, kk, true, &sh_digit, &sh_before);
+        __syncthreads();
+        prefix |= (uint32_t)sh_digit << shift;
+        kk -= sh_before;
+        __syncthreads();
+    }
+    // ---- count strictly better / tied candidates
+    long long idx_cut = 0x7fffffffffffffffLL;
+    if (!all) {
+        int gt = 0, eq = 0;
+        for (int e = tid; e < T; e += MERGE_THREADS) {
+            float s; long long id; elem(e, s, id);
+            if (id < 0) continue;
+            const uint32_t key = flip_f32(s);
+            gt += key > prefix; eq += key == prefix;
+        }
+        atomicAdd(&sh_gt, gt); atomicAdd(&sh_eq, eq);
+        __syncthreads();
+        const int need = k - sh_gt;                        // ties to keep (1 <= need <= sh_eq)
+        if (sh_eq > need) {                                // rare: pick the `need` smallest indices among the ties
+            unsigned long long ip = 0; int kn = need;
+            for (int pass = 0; pass < 8; ++pass) {
+                const int shift = 56 - 8 * pass;
+                __syncthreads();
+                hist[tid] = 0;
+                __syncthreads();
+                for (int e = tid; e < T; e += MERGE_THREADS) {
+                    float s; long long id; elem(e, s, id);
+                    if (id < 0 || flip_f32(s) != prefix) continue;
+                    const unsigned long long u = (unsigned long long)id;
+                    if (pass == 0 || (u >> (shift + 8)) == (ip >> (shift + 8))) atomicAdd(&hist[(u >> shift) & 255], 1);
+                }
+                __syncthreads();
+                scan_hist(hist, kn, false, &sh_digit, &sh_before);
+                __syncthreads();
+                ip |= (unsigned long long)sh_digit << shift;
+                kn -= sh_before;
+            }
+            idx_cut = (long long)ip;                       // the need-th smallest tied index
+        }
     }
     __syncthreads();
-    for (int kk = 2; kk <= np2; kk <<= 1)
-        for (int j = kk >> 1; j > 0; j >>= 1) {
-            for (int e = threadIdx.x; e < np2; e += blockDim.x) {
+    // ---- gather survivors, sort them, write
+    for (int e = tid; e < T; e += MERGE_THREADS) {
+        float s; long long id; elem(e, s, id);
+        if (id < 0) continue;
+        const uint32_t key = flip_f32(s);
+        if (all || key > prefix || (key == prefix && id <= idx_cut)) {
+            const int pos = atomicAdd(&sh_count, 1);
+            if (pos < MERGE_KMAX) { ss[pos] = s; si[pos] = id; }
+        }
+    }
+    __syncthreads();
+    const int cnt = min(sh_count, k);
+    int np2 = 1;
+    while (np2 < cnt) np2 <<= 1;
+    for (int e = cnt + tid; e < np2; e += MERGE_THREADS) { ss[e] = -INFINITY; si[e] = 0x7fffffffffffffffLL; }
+    __syncthreads();
+    for (int kk2 = 2; kk2 <= np2; kk2 <<= 1)
+        for (int j = kk2 >> 1; j > 0; j >>= 1) {
+            for (int e = tid; e < np2; e += MERGE_THREADS) {
                 const int o = e ^ j;
                 if (o > e) {
-                    const bool desc = (e & kk) == 0;
+                    const bool desc = (e & kk2) == 0;
                     const float sa = ss[e], sb = ss[o]; const long long ia = si[e], ib = si[o];
                     const bool sw = desc ? better(sb, ib, sa, ia) : better(sa, ia, sb, ib);
                     if (sw) { ss[e] = sb; ss[o] = sa; si[e] = ib; si[o] = ia; }
@@ -281,8 +397,8 @@ __global__ void __launch_bounds__(256) merge_topk_kernel(const float* __restrict
             }
             __syncthreads();
         }
-    for (int e = threadIdx.x; e < k; e += blockDim.x) {
-        const bool valid = e < np2 && si[e] != 0x7fffffffffffffffLL;
+    for (int e = tid; e < k; e += MERGE_THREADS) {
+        const bool valid = e < cnt;
         out_s[(size_t)qi * k + e] = valid ? ss[e] : -INFINITY;
         out_i[(size_t)qi * k + e] = valid ? si[e] : -1;
     }
@@ -290,14 +406,10 @@ __global__ void __launch_bounds__(256) merge_topk_kernel(const float* __restrict
 
 int merge_topk_run(const float* ps, const long long* pi, int P, int Q, int k, float* out_s, long long* out_i, cudaStream_t st) {
     B200_REQUIRE(P > 0 && k > 0, "merge_topk: need at least one part and k > 0");
+    B200_REQUIRE(k <= MERGE_KMAX, "merge_topk: k larger than 1024 is not supported");
+    B200_REQUIRE((long long)P * k < (1LL << 30), "merge_topk: too many candidates per query");
     if (Q == 0) return B200_OK;
-    int np2 = 2;
-    while (np2 < P * k) np2 <<= 1;
-    B200_REQUIRE(np2 <= 16384, "merge_topk: parts * k must not exceed 16384");
-    const size_t smem = (size_t)np2 * 12;
-    if (smem > 48 * 1024)
-        B200_CUDA_OK(cudaFuncSetAttribute(merge_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    merge_topk_kernel<<<Q, 256, smem, st>>>(ps, pi, P, Q, k, np2, out_s, out_i);
+    merge_topk_kernel<<<Q, MERGE_THREADS, 0, st>>>(ps, pi, P, Q, k, out_s, out_i);
     B200_CUDA_OK(cudaGetLastError());
     return B200_OK;
 }
@@ -309,7 +421,8 @@ int topk_plan(int Q, long long N, int k, TopkPlan* plan) {
     plan->cpl = k <= 256 ? 16 : 32;
     plan->qtiles = (Q + TK_BM - 1) / TK_BM;
     const long long ntiles = (N + TK_BN - 1) / TK_BN;
-    long long splits = (2LL * kNumSMs) / plan->qtiles;          // about two waves of CTAs
+    // qtiles * splits CTAs: fill one wave of 148 SMs when the query tiles are few, two waves otherwise
+    long long splits = plan->qtiles <= kNumSMs / 2 ? kNumSMs / plan->qtiles : (2LL * kNumSMs) / plan->qtiles;
     if (splits < 1) splits = 1;
     if (splits > ntiles) splits = ntiles;
     if (splits * k > 16384) splits = 16384 / k;                 // merge kernel capacity

@@ -225,20 +225,38 @@ topk_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
             if (!(ok = mbar_wait(&acc_full[as], aph, p.status, 14))) break;
             tc_fence_after();
             const long long n0 = n_lo + (long long)t * TK_BN;
-#pragma unroll 1
-            for (int c = 0; c < TK_BN / 32; ++c) {
-                uint32_t v[32];
-                tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + as * TK_BN + c * 32, v);
-                tmem_ld_wait();
-                const long long nb = n0 + c * 32;
+            const uint32_t tsrc = tmem_base + ((uint32_t)(q * 32) << 16) + as * TK_BN;
+            // Scan 8 chunks of 32 scores; the TMEM load of chunk c+1 is in flight while chunk c is examined.
+            // A thread first reduces its 32 scores to their maximum: only if that beats tau (rare once the
+            // threshold has settled) does it walk the chunk and append the survivors.
+            auto scan = [&](const uint32_t (&v)[32], int c) {
+                float mx = __uint_as_float(v[0]);
 #pragma unroll
-                for (int j = 0; j < 32; ++j) {
-                    const float s = __uint_as_float(v[j]);
-                    if (nb + j < n_hi && s > tau) {
-                        __stcg(rowptr + cnt, ((unsigned long long)flip_f32(s) << 32) | (0xffffffffu - (uint32_t)(nb + j)));
-                        ++cnt;
+                for (int j = 1; j < 32; ++j) mx = fmaxf(mx, __uint_as_float(v[j]));
+                if (mx > tau) {
+                    const long long nb = n0 + c * 32;
+                    const int lim = (int)min(32LL, n_hi - nb);                    // < 32 only in the last tile of the gallery
+                    const uint32_t inv = 0xffffffffu - (uint32_t)nb;
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        const float s = __uint_as_float(v[j]);
+                        if (s > tau && j < lim) {
+                            __stcg(rowptr + cnt, ((unsigned long long)flip_f32(s) << 32) | (inv - (uint32_t)j));
+                            ++cnt;
+                        }
                     }
                 }
+            };
+            uint32_t va[32], vb[32];
+            tmem_ld_32x32(tsrc, va);
+#pragma unroll 1
+            for (int c = 0; c < TK_BN / 32; c += 2) {
+                tmem_ld_wait();
+                tmem_ld_32x32(tsrc + (c + 1) * 32, vb);
+                scan(va, c);
+                tmem_ld_wait();
+                if (c + 2 < TK_BN / 32) tmem_ld_32x32(tsrc + (c + 2) * 32, va);
+                scan(vb, c + 1);
             }
             tc_fence_before();
             __syncwarp();

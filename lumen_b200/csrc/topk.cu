@@ -299,6 +299,15 @@ __device__ __forceinline__ bool better(float sa, long long ia, float sb, long lo
 constexpr int MERGE_THREADS = 256;
 constexpr int MERGE_KMAX = 1024;
 
+// hist[digit] += 1 for every participating lane, one shared-memory atomic per distinct digit in the warp
+// (candidate scores cluster in a few high-order digits, so plain per-thread atomics would serialise).
+__device__ __forceinline__ void hist_add(int* hist, bool active, int digit) {
+    const unsigned act = __ballot_sync(0xffffffffu, active);
+    if (!active) return;
+    const unsigned peers = __match_any_sync(act, digit);
+    if ((threadIdx.x & 31) == __ffs(peers) - 1) atomicAdd(&hist[digit], __popc(peers));
+}
+
 // Finds the digit d (scanning from `hi_first ? 255 : 0`) where the running count reaches kk; returns it and
 // the count before it.  Called by all threads after the histogram is complete; thread 0 scans.
 __device__ __forceinline__ void scan_hist(const int* hist, int kk, bool hi_first, int* sh_digit, int* sh_before) {
@@ -332,11 +341,13 @@ __global__ void __launch_bounds__(MERGE_THREADS) merge_topk_kernel(const float* 
         const int shift = 24 - 8 * pass;
         hist[tid] = 0;
         __syncthreads();
-        for (int e = tid; e < T; e += MERGE_THREADS) {
-            float s; long long id; elem(e, s, id);
-            if (id < 0) continue;
+        for (int e0 = 0; e0 < T; e0 += MERGE_THREADS) {          // whole warps iterate together (hist_add votes)
+            const int e = e0 + tid;
+            float s = 0.f; long long id = -1;
+            if (e < T) elem(e, s, id);
             const uint32_t key = flip_f32(s);
-            if (pass == 0 || (key >> (shift + 8)) == (prefix >> (shift + 8))) atomicAdd(&hist[(key >> shift) & 255], 1);
+            const bool act = id >= 0 && (pass == 0 || (key >> (shift + 8)) == (prefix >> (shift + 8)));
+            hist_add(hist, act, (key >> shift) & 255);
         }
         __syncthreads();
         if (pass == 0) {                                   // fewer valid candidates than k: keep them all
@@ -370,11 +381,13 @@ __global__ void __launch_bounds__(MERGE_THREADS) merge_topk_kernel(const float* 
                 __syncthreads();
                 hist[tid] = 0;
                 __syncthreads();
-                for (int e = tid; e < T; e += MERGE_THREADS) {
-                    float s; long long id; elem(e, s, id);
-                    if (id < 0 || flip_f32(s) != prefix) continue;
+                for (int e0 = 0; e0 < T; e0 += MERGE_THREADS) {
+                    const int e = e0 + tid;
+                    float s = 0.f; long long id = -1;
+                    if (e < T) elem(e, s, id);
                     const unsigned long long u = (unsigned long long)id;
-                    if (pass == 0 || (u >> (shift + 8)) == (ip >> (shift + 8))) atomicAdd(&hist[(u >> shift) & 255], 1);
+                    const bool act = id >= 0 && flip_f32(s) == prefix && (pass == 0 || (u >> (shift + 8)) == (ip >> (shift + 8)));
+                    hist_add(hist, act, (int)((u >> shift) & 255));
                 }
                 __syncthreads();
                 scan_hist(hist, kn, false, &sh_digit, &sh_before);

@@ -139,11 +139,32 @@ def bench_models(args):
         eng.close()
 
 
+def bench_gemm(args):
+    """Every encoder GEMM shape of ViT-B/32 at batch 512 through b200clip_gemm_bf16, per epilogue."""
+    import torch
+    from lumen_b200 import _lib
+    from lumen_b200.engine import Engine
+    pk = peaks()
+    eng = Engine({}, device=0)
+    shapes = [("patch", 25088, 768, 3072, _lib.EPI_F32), ("qkv", 25600, 2304, 768, _lib.EPI_BIAS_BF16), ("out_proj", 25600, 768, 768, _lib.EPI_BIAS_RES_F32),
+              ("fc1", 25600, 3072, 768, _lib.EPI_BIAS_ACT_BF16), ("fc2", 25600, 768, 3072, _lib.EPI_BIAS_RES_F32), ("qkv_f32", 25600, 2304, 768, _lib.EPI_F32)]
+    for name, M, N, K, epi in shapes:
+        A = torch.randn(M, K, device="cuda").to(torch.bfloat16)
+        W = (torch.randn(N, K, device="cuda") / K ** 0.5).to(torch.bfloat16)
+        bias = torch.randn(N, device="cuda")
+        out = torch.zeros((M, N), dtype=torch.float32 if epi in (_lib.EPI_F32, _lib.EPI_BIAS_RES_F32) else torch.bfloat16, device="cuda")
+        ms = timed(lambda: eng.gemm(A, W, bias, epi, 0, out=out), 20)
+        tf = 2.0 * M * N * K / ms / 1e9
+        print(json.dumps({"path": "gemm_tc_kernel", "shape": name, "M": M, "N": N, "K": K, "epilogue": epi, "us": ms * 1e3, "tflops": tf,
+                          "frac_burst": tf / pk["bf16_burst"], "frac_sustained": tf / pk["bf16_sustained"]}), flush=True)
+    eng.close()
+
+
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
-    ap.add_argument("what", choices=["preprocess", "search", "classify", "models"])
+    ap.add_argument("what", choices=["preprocess", "search", "classify", "models", "gemm"])
     ap.add_argument("--gallery", type=int, default=1_250_000, help="total gallery rows (all GPUs)")
     ap.add_argument("--sharded", action="store_true")
     ap.add_argument("--qs", default="", help="comma-separated query counts for the search sweep")
     a = ap.parse_args()
-    {"preprocess": bench_preprocess, "search": bench_search, "classify": bench_classify, "models": bench_models}[a.what](a)
+    {"preprocess": bench_preprocess, "search": bench_search, "classify": bench_classify, "models": bench_models, "gemm": bench_gemm}[a.what](a)

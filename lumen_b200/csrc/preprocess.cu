@@ -68,38 +68,113 @@ __device__ __forceinline__ int stage_span(uint8_t* dst, const uint8_t* src, long
     return prefix;
 }
 
-template <int VW, bool BF16>
-__device__ __forceinline__ void store_vec(const PreParams& p, int b, int c, int y, int x, const float (&f)[VW]) {
-    size_t idx;
-    if (p.layout == 0) idx = (((size_t)b * 3 + c) * p.S + y) * p.S + x;
-    else idx = ((size_t)b * p.npatch_side * p.npatch_side + (size_t)(y / p.P) * p.npatch_side + x / p.P) * p.kpad +
-               (size_t)c * p.P * p.P + (y % p.P) * p.P + (x % p.P);
+// Element index of (image b, channel 0, row y, column x) and the distance between channels, for both layouts.
+__device__ __forceinline__ size_t out_index(const PreParams& p, int b, int y, int x, int& cstride) {
+    if (p.layout == 0) { cstride = p.S * p.S; return (((size_t)b * 3) * p.S + y) * p.S + x; }
+    cstride = p.P * p.P;
+    return ((size_t)b * p.npatch_side * p.npatch_side + (size_t)(y / p.P) * p.npatch_side + x / p.P) * p.kpad + (y % p.P) * p.P + (x % p.P);
+}
+
+// Stores 8 consecutive x positions of one channel at element index `idx` (vec8: one 16-byte bf16 / two 16-byte
+// fp32 stores).  When the patch size is not a multiple of 8 (e.g. 14) the 8 pixels may straddle a patch boundary:
+// element pairs are then addressed one by one.
+template <bool BF16>
+__device__ __forceinline__ void store8(const PreParams& p, bool vec8, size_t idx, int b, int c, int y, int x, const float (&f)[8]) {
     if (BF16) {
-        __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out) + idx;
-        if (VW == 8) {
+        __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out);
+        if (vec8) {
             uint4 v;
             __nv_bfloat162 t0 = __floats2bfloat162_rn(f[0], f[1]), t1 = __floats2bfloat162_rn(f[2], f[3]);
             __nv_bfloat162 t2 = __floats2bfloat162_rn(f[4], f[5]), t3 = __floats2bfloat162_rn(f[6], f[7]);
             v.x = *reinterpret_cast<uint32_t*>(&t0); v.y = *reinterpret_cast<uint32_t*>(&t1);
             v.z = *reinterpret_cast<uint32_t*>(&t2); v.w = *reinterpret_cast<uint32_t*>(&t3);
-            *reinterpret_cast<uint4*>(o) = v;
+            *reinterpret_cast<uint4*>(o + idx) = v;
         } else {
 #pragma unroll
-            for (int i = 0; i < VW; i += 2) *reinterpret_cast<__nv_bfloat162*>(o + i) = __floats2bfloat162_rn(f[i], f[i + 1]);
+            for (int i = 0; i < 8; i += 2) {
+                int cs; const size_t e = out_index(p, b, y, x + i, cs) + (size_t)c * cs;
+                *reinterpret_cast<__nv_bfloat162*>(o + e) = __floats2bfloat162_rn(f[i], f[i + 1]);
+            }
         }
     } else {
-        float* o = reinterpret_cast<float*>(p.out) + idx;
-        if (VW == 8) {
-            *reinterpret_cast<float4*>(o) = make_float4(f[0], f[1], f[2], f[3]);
-            *reinterpret_cast<float4*>(o + 4) = make_float4(f[4], f[5], f[6], f[7]);
+        float* o = reinterpret_cast<float*>(p.out);
+        if (vec8) {
+            *reinterpret_cast<float4*>(o + idx) = make_float4(f[0], f[1], f[2], f[3]);
+            *reinterpret_cast<float4*>(o + idx + 4) = make_float4(f[4], f[5], f[6], f[7]);
         } else {
 #pragma unroll
-            for (int i = 0; i < VW; i += 2) *reinterpret_cast<float2*>(o + i) = make_float2(f[i], f[i + 1]);
+            for (int i = 0; i < 8; i += 2) {
+                int cs; const size_t e = out_index(p, b, y, x + i, cs) + (size_t)c * cs;
+                *reinterpret_cast<float2*>(o + e) = make_float2(f[i], f[i + 1]);
+            }
         }
     }
 }
 
-template <int VW, bool BF16>
+__device__ __forceinline__ uint32_t byte_of(uint32_t w, int i) { return __byte_perm(w, 0, 0x4440 | i); }
+
+// NW+1 aligned 32-bit words starting at the word that holds `p` -> NW words whose byte 0 is *p (little endian).
+template <int NW>
+__device__ __forceinline__ void load_bytes_aligned(const uint8_t* p, uint32_t (&al)[NW]) {
+    const uint32_t sh = (smem_u32(p) & 3u) * 8u;
+    const uint32_t* wp = reinterpret_cast<const uint32_t*>(p - (smem_u32(p) & 3u));
+    uint32_t prev = wp[0];
+#pragma unroll
+    for (int j = 0; j < NW; ++j) {
+        const uint32_t next = wp[j + 1];
+        al[j] = __funnelshift_r(prev, next, sh);
+        prev = next;
+    }
+}
+
+// Horizontal pass for one staged chunk of source rows.  A thread owns one output column: its (at most KMAX)
+// coefficients sit in registers for all rows of the chunk; the 3*KMAX source bytes of a row are fetched as 32-bit
+// words (one shared-memory load per four bytes), realigned with funnel shifts and split with PRMT, so the integer
+// MACs, not the load/store unit, set the pace.  Coefficients beyond the real tap count are zero, so the extra
+// bytes (still inside the staging allocation) contribute nothing.  KMAX == 0: generic byte loop for very wide filters.
+template <int KMAX>
+__device__ __forceinline__ void hpass_chunk(const ImgDesc& d, const uint8_t* __restrict__ rows, int rowbytes, int nr, int S,
+                                            uint8_t* __restrict__ inter_rows, int inter_pitch) {
+    for (int x = threadIdx.x; x < S; x += blockDim.x) {
+        const int xo = d.left + x;
+        const int xmin = __ldg(d.bounds_h + 2 * xo), cnt = __ldg(d.bounds_h + 2 * xo + 1);
+        const int* k = d.kk_h + (size_t)xo * d.ksize_h;
+        const uint8_t* px0 = rows + xmin * 3;
+        uint8_t* o = inter_rows + x * 3;
+        if (KMAX > 0) {
+            constexpr int NW = (3 * (KMAX > 0 ? KMAX : 1) + 3) / 4;
+            int w[KMAX > 0 ? KMAX : 1];
+#pragma unroll
+            for (int t = 0; t < KMAX; ++t) w[t] = t < cnt ? __ldg(k + t) : 0;
+            for (int r = 0; r < nr; ++r) {
+                uint32_t al[NW];
+                load_bytes_aligned<NW>(px0 + r * rowbytes, al);
+                int a0 = 1 << (PRECISION_BITS - 1), a1 = a0, a2 = a0;
+#pragma unroll
+                for (int t = 0; t < KMAX; ++t) {
+                    a0 += (int)byte_of(al[(3 * t) >> 2], (3 * t) & 3) * w[t];
+                    a1 += (int)byte_of(al[(3 * t + 1) >> 2], (3 * t + 1) & 3) * w[t];
+                    a2 += (int)byte_of(al[(3 * t + 2) >> 2], (3 * t + 2) & 3) * w[t];
+                }
+                o[0] = (uint8_t)clip8(a0); o[1] = (uint8_t)clip8(a1); o[2] = (uint8_t)clip8(a2);
+                o += inter_pitch;
+            }
+        } else {
+            for (int r = 0; r < nr; ++r) {
+                const uint8_t* px = px0 + r * rowbytes;
+                int a0 = 1 << (PRECISION_BITS - 1), a1 = a0, a2 = a0;
+                for (int j = 0; j < cnt; ++j) {
+                    const int w = __ldg(k + j);
+                    a0 += px[3 * j] * w; a1 += px[3 * j + 1] * w; a2 += px[3 * j + 2] * w;
+                }
+                o[0] = (uint8_t)clip8(a0); o[1] = (uint8_t)clip8(a1); o[2] = (uint8_t)clip8(a2);
+                o += inter_pitch;
+            }
+        }
+    }
+}
+
+template <bool BF16>
 __global__ void __launch_bounds__(256) preprocess_kernel(PreParams p) {
     extern __shared__ __align__(16) uint8_t sm[];
     float* lut = reinterpret_cast<float*>(sm);                  // 768 floats
@@ -112,32 +187,17 @@ __global__ void __launch_bounds__(256) preprocess_kernel(PreParams p) {
     const int y0 = blockIdx.x * p.TR, y1 = min(S, y0 + p.TR);
     for (int i = threadIdx.x; i < 768; i += blockDim.x) lut[i] = p.lut[i];
     const int rowbytes = d.w_in * 3;
-    const int xvecs = S / VW;
+    const int xvecs = S >> 3;                                   // groups of 8 output pixels (S % 8 == 0)
+    const bool vec8 = p.layout == 0 || (p.P & 7) == 0;
+    const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
-    if (d.identity) {
-        // Crop + convert only: stage source rows [top+y0, top+y1) (one contiguous span) and write the planes.
-        const int nr = y1 - y0;
-        const int prefix = stage_span(stage, p.src, d.src_off + (long long)(d.top + y0) * rowbytes, nr * rowbytes);
-        cp_async_commit();
-        cp_async_wait<0>();
-        __syncthreads();
-        const uint8_t* base = stage + prefix + d.left * 3;
-        for (int i = threadIdx.x; i < nr * 3 * xvecs; i += blockDim.x) {
-            const int xv = i % xvecs, c = (i / xvecs) % 3, r = i / (3 * xvecs);
-            const uint8_t* px = base + r * rowbytes + xv * VW * 3 + c;
-            float f[VW];
-#pragma unroll
-            for (int j = 0; j < VW; ++j) f[j] = lut[c * 256 + px[j * 3]];
-            store_vec<VW, BF16>(p, b, c, y0 + r, xv * VW, f);
-        }
-        return;
-    }
+    if (d.identity) return;                                     // handled by convert_kernel
 
     // ---- rows of the source this tile needs (vertical taps of its first and last output row)
     const int r_lo = d.bounds_v[2 * (d.top + y0)];
     const int r_hi = d.bounds_v[2 * (d.top + y1 - 1)] + d.bounds_v[2 * (d.top + y1 - 1) + 1];
     const int nrows = r_hi - r_lo;
-    const int rpc = max(1, (p.stage_bytes - 32) / rowbytes);    // source rows per staged chunk
+    const int rpc = max(1, (p.stage_bytes - 32 - 128) / rowbytes);    // source rows per staged chunk
     const int nchunks = (nrows + rpc - 1) / rpc;
 
     int prefix_cur = stage_span(stage, p.src, d.src_off + (long long)r_lo * rowbytes, min(rpc, nrows) * rowbytes);
@@ -157,44 +217,105 @@ __global__ void __launch_bounds__(256) preprocess_kernel(PreParams p) {
             cp_async_wait<0>();
         }
         __syncthreads();
-        // ---- horizontal pass: (row, x) -> 3 channels
-        for (int i = threadIdx.x; i < nr * S; i += blockDim.x) {
-            const int r = i / S, x = i - r * S;
-            const int xo = d.left + x;
-            const int xmin = __ldg(d.bounds_h + 2 * xo), cnt = __ldg(d.bounds_h + 2 * xo + 1);
-            const int* k = d.kk_h + (size_t)xo * d.ksize_h;
-            const uint8_t* px = cur + prefix_cur + r * rowbytes + xmin * 3;
-            int a0 = 1 << (PRECISION_BITS - 1), a1 = a0, a2 = a0;
-            for (int j = 0; j < cnt; ++j) {
-                const int w = __ldg(k + j);
-                a0 += px[3 * j] * w; a1 += px[3 * j + 1] * w; a2 += px[3 * j + 2] * w;
-            }
-            uint8_t* o = inter + (size_t)(row0 - r_lo + r) * p.inter_pitch + x * 3;
-            o[0] = (uint8_t)clip8(a0); o[1] = (uint8_t)clip8(a1); o[2] = (uint8_t)clip8(a2);
+        // ---- horizontal pass: one output column per thread, all rows of the chunk
+        {
+            const uint8_t* rows = cur + prefix_cur;
+            uint8_t* irows = inter + (size_t)(row0 - r_lo) * p.inter_pitch;
+            if (d.ksize_h <= 8) hpass_chunk<8>(d, rows, rowbytes, nr, S, irows, p.inter_pitch);
+            else if (d.ksize_h <= 16) hpass_chunk<16>(d, rows, rowbytes, nr, S, irows, p.inter_pitch);
+            else if (d.ksize_h <= 24) hpass_chunk<24>(d, rows, rowbytes, nr, S, irows, p.inter_pitch);
+            else if (d.ksize_h <= 40) hpass_chunk<40>(d, rows, rowbytes, nr, S, irows, p.inter_pitch);
+            else hpass_chunk<0>(d, rows, rowbytes, nr, S, irows, p.inter_pitch);
         }
         __syncthreads();
         prefix_cur = prefix_next;
     }
-    // ---- vertical pass + normalise + store
-    for (int i = threadIdx.x; i < (y1 - y0) * 3 * xvecs; i += blockDim.x) {
-        const int xv = i % xvecs, c = (i / xvecs) % 3, y = y0 + i / (3 * xvecs);
-        const int yo = d.top + y;
+    // ---- vertical pass + normalise + store: a thread owns 8 pixels x 3 channels (24 contiguous, 8-byte aligned
+    //      bytes of every intermediate row: three 64-bit loads per tap)
+    for (int yy = y0 + wid; yy < y1; yy += 8) {
+        const int yo = d.top + yy;
         const int ymin = __ldg(d.bounds_v + 2 * yo), cnt = __ldg(d.bounds_v + 2 * yo + 1);
         const int* k = d.kk_v + (size_t)yo * d.ksize_v;
-        const uint8_t* col = inter + (size_t)(ymin - r_lo) * p.inter_pitch + xv * VW * 3 + c;
-        int acc[VW];
+        for (int xv = lane; xv < xvecs; xv += 32) {
+            const uint8_t* col = inter + (size_t)(ymin - r_lo) * p.inter_pitch + xv * 24;
+            int acc[24];
 #pragma unroll
-        for (int j = 0; j < VW; ++j) acc[j] = 1 << (PRECISION_BITS - 1);
-        for (int t = 0; t < cnt; ++t) {
-            const int w = __ldg(k + t);
-            const uint8_t* row = col + (size_t)t * p.inter_pitch;
+            for (int j = 0; j < 24; ++j) acc[j] = 1 << (PRECISION_BITS - 1);
+            for (int t = 0; t < cnt; ++t) {
+                const int w = __ldg(k + t);
+                const uint2* rp = reinterpret_cast<const uint2*>(col + (size_t)t * p.inter_pitch);
+                const uint2 q0 = rp[0], q1 = rp[1], q2 = rp[2];
+                const uint32_t q[6] = {q0.x, q0.y, q1.x, q1.y, q2.x, q2.y};
 #pragma unroll
-            for (int j = 0; j < VW; ++j) acc[j] += row[j * 3] * w;
+                for (int j = 0; j < 24; ++j) acc[j] += (int)byte_of(q[j >> 2], j & 3) * w;
+            }
+            int cstride;
+            const size_t idx0 = out_index(p, b, yy, xv * 8, cstride);
+#pragma unroll
+            for (int c = 0; c < 3; ++c) {
+                float f[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) f[j] = lut[c * 256 + clip8(acc[3 * j + c])];
+                store8<BF16>(p, vec8, idx0 + (size_t)c * cstride, b, c, yy, xv * 8, f);
+            }
         }
-        float f[VW];
+    }
+}
+
+// Identity-size images (resized size == source size, e.g. 224x224 sources for a 224 model): crop + convert only.
+// Persistent CTAs walk (image, row-tile) items; the next item's rows are fetched with cp.async while the current
+// ones are converted, so the kernel streams at memory speed instead of paying one load latency per tile.
+template <bool BF16>
+__global__ void __launch_bounds__(256, 4) convert_kernel(PreParams p, int B, int tiles) {
+    extern __shared__ __align__(16) uint8_t sm[];
+    float* lut = reinterpret_cast<float*>(sm);
+    uint8_t* stage = sm + 3072;                                 // 2 x stage_bytes
+    for (int i = threadIdx.x; i < 768; i += blockDim.x) lut[i] = p.lut[i];
+    const int S = p.S, xvecs = S >> 3;
+    const bool vec8 = p.layout == 0 || (p.P & 7) == 0;
+    const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int total = B * tiles;
+    auto fetch = [&](int item, int buf) -> int {               // returns the byte offset of the first row inside the buffer
+        const int b = item / tiles, y0 = (item - b * tiles) * p.TR;
+        const ImgDesc& d = p.desc[b];
+        int prefix = 0;
+        if (d.identity) {
+            const int rowbytes = d.w_in * 3, nr = min(S, y0 + p.TR) - y0;
+            prefix = stage_span(stage + buf * p.stage_bytes, p.src, d.src_off + (long long)(d.top + y0) * rowbytes, nr * rowbytes);
+        }
+        cp_async_commit();
+        return prefix;
+    };
+    int item = blockIdx.x, it = 0;
+    if (item >= total) return;
+    int prefix = fetch(item, 0);
+    for (; item < total; item += gridDim.x, ++it) {
+        const int next = item + gridDim.x;
+        int prefix_next = 0;
+        if (next < total) { prefix_next = fetch(next, (it + 1) & 1); cp_async_wait<1>(); } else cp_async_wait<0>();
+        __syncthreads();
+        const int b = item / tiles, y0 = (item - b * tiles) * p.TR;
+        const ImgDesc& d = p.desc[b];
+        if (d.identity) {
+            const int rowbytes = d.w_in * 3, nr = min(S, y0 + p.TR) - y0;
+            const uint8_t* base = stage + (it & 1) * p.stage_bytes + prefix + d.left * 3;
+            for (int r = wid; r < nr; r += 8)
+                for (int xv = lane; xv < xvecs; xv += 32) {
+                    uint32_t al[6];
+                    load_bytes_aligned<6>(base + r * rowbytes + xv * 24, al);
+                    int cstride;
+                    const size_t idx0 = out_index(p, b, y0 + r, xv * 8, cstride);
 #pragma unroll
-        for (int j = 0; j < VW; ++j) f[j] = lut[c * 256 + clip8(acc[j])];
-        store_vec<VW, BF16>(p, b, c, y, xv * VW, f);
+                    for (int c = 0; c < 3; ++c) {
+                        float f[8];
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) f[j] = lut[c * 256 + byte_of(al[(3 * j + c) >> 2], (3 * j + c) & 3)];
+                        store8<BF16>(p, vec8, idx0 + (size_t)c * cstride, b, c, y0 + r, xv * 8, f);
+                    }
+                }
+        }
+        __syncthreads();
+        prefix = prefix_next;
     }
 }
 
@@ -283,13 +404,10 @@ static int get_table(PreprocessState* s, int in_size, int out_size, const AxisTa
     return B200_OK;
 }
 
-template <int VW, bool BF16> static int launch_pre(const PreParams& p, int tiles, int B, size_t smem, cudaStream_t st) {
-    static size_t configured = 0;
-    if (smem > configured) {
-        B200_CUDA_OK(cudaFuncSetAttribute(preprocess_kernel<VW, BF16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = smem;
-    }
-    preprocess_kernel<VW, BF16><<<dim3(tiles, B), 256, smem, st>>>(p);
+template <bool BF16> static int launch_pre(const PreParams& p, int tiles, int B, size_t smem, cudaStream_t st) {
+    if (smem > 48 * 1024)
+        B200_CUDA_OK(cudaFuncSetAttribute(preprocess_kernel<BF16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    preprocess_kernel<BF16><<<dim3(tiles, B), 256, smem, st>>>(p);
     B200_CUDA_OK(cudaGetLastError());
     return B200_OK;
 }
@@ -299,7 +417,7 @@ template <int VW, bool BF16> static int launch_pre(const PreParams& p, int tiles
 // layout 0: out[B,3,S,S]; layout 1: out[B*n, kpad] patch-major with K index (c, i, j) and zero padding left untouched.
 int preprocess_run(PreprocessState* s, const uint8_t* src_dev, const long long* offsets, const int* hw, int B, int S,
                    int mode, int layout, int out_bf16, int P, int kpad, void* out_dev, cudaStream_t st) {
-    B200_REQUIRE(B >= 0 && S > 0 && S % 2 == 0, "preprocess: target size must be positive and even");
+    B200_REQUIRE(B >= 0 && S > 0 && S % 8 == 0, "preprocess: target size must be a positive multiple of 8");
     if (B == 0) return B200_OK;
     B200_REQUIRE(src_dev && offsets && hw && out_dev, "preprocess: null buffer");
     B200_REQUIRE(mode == 0 || mode == 1, "preprocess: mode must be 0 (squash) or 1 (shortest side + centre crop)");
@@ -342,28 +460,44 @@ int preprocess_run(PreprocessState* s, const uint8_t* src_dev, const long long* 
         } else if (w * 3 > max_ident_rowbytes) max_ident_rowbytes = w * 3;
     }
     // Tile height: as many output rows as keep the uint8 intermediate within ~64 KB (whole tile within 200 KB).
-    int stage_bytes = 16384;
-    while (stage_bytes < max_rowbytes + 32) stage_bytes *= 2;
-    B200_REQUIRE(stage_bytes <= 65536, "preprocess: source rows wider than 21834 pixels are not supported");
-    auto rows_needed = [&](int tr) { return (int)std::ceil(max_vscale * tr + 4.0 * (max_vscale < 1 ? 1 : max_vscale)) + 3; };
-    int TR = 16;
-    const size_t budget = 200 * 1024 - 3072 - 2 * (size_t)stage_bytes;
-    if (any_resize) {
-        while (TR > 1 && ((size_t)rows_needed(TR) * inter_pitch > 65536)) TR /= 2;
-        B200_REQUIRE((size_t)rows_needed(TR) * inter_pitch <= budget, "preprocess: vertical downscale factor too large for one tile");
-    }
-    while (TR > 1 && (size_t)TR * max_ident_rowbytes + 32 > 2 * (size_t)stage_bytes) TR /= 2;
-    B200_REQUIRE((size_t)TR * max_ident_rowbytes + 32 <= 2 * (size_t)stage_bytes, "preprocess: source rows too wide");
-    const size_t inter_bytes = any_resize ? (size_t)rows_needed(TR) * inter_pitch : 0;
-    const size_t smem = 3072 + 2 * (size_t)stage_bytes + inter_bytes;
-
     B200_CUDA_OK(cudaMemcpyAsync(s->d_desc, s->h_desc, sizeof(ImgDesc) * B, cudaMemcpyHostToDevice, st));
     B200_CUDA_OK(cudaEventRecord(s->desc_free, st));
+    int rc = B200_OK;
+    if (max_ident_rowbytes > 0) {
+        // identity images: TR rows per item, one staging buffer per item (double buffered)
+        int TR = 16;
+        while (TR > 1 && (size_t)TR * max_ident_rowbytes + 48 > 48 * 1024) TR /= 2;
+        const int stage_bytes = (TR * max_ident_rowbytes + 48 + 15) & ~15;
+        B200_REQUIRE(stage_bytes <= 96 * 1024, "preprocess: source rows too wide");
+        const size_t smem = 3072 + 2 * (size_t)stage_bytes;
+        const int tiles = (S + TR - 1) / TR;
+        PreParams p{src_dev, s->d_desc, s->d_lut, out_dev, S, TR, layout, out_bf16, P, layout ? S / P : 0, kpad, inter_pitch, stage_bytes};
+        const long long total = (long long)B * tiles;
+        const int grid = (int)std::min<long long>(total, 8LL * kNumSMs);
+        if (out_bf16) {
+            if (smem > 48 * 1024) B200_CUDA_OK(cudaFuncSetAttribute(convert_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            convert_kernel<true><<<grid, 256, smem, st>>>(p, B, tiles);
+        } else {
+            if (smem > 48 * 1024) B200_CUDA_OK(cudaFuncSetAttribute(convert_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            convert_kernel<false><<<grid, 256, smem, st>>>(p, B, tiles);
+        }
+        B200_CUDA_OK(cudaGetLastError());
+    }
+    if (!any_resize) return rc;
+    // Resized images.  Staging: two buffers of `stage_bytes` (>= one source row + slack for the zero-weight
+    // over-reads of the register-tiled horizontal pass).
+    int stage_bytes = 16384;
+    while (stage_bytes < max_rowbytes + 32 + 128) stage_bytes *= 2;
+    B200_REQUIRE(stage_bytes <= 65536, "preprocess: source rows wider than 21800 pixels are not supported");
+    auto rows_needed = [&](int tr) { return (int)std::ceil(max_vscale * tr + 4.0 * (max_vscale < 1 ? 1 : max_vscale)) + 3; };
+    int TR = 32;
+    const size_t budget = 200 * 1024 - 3072 - 2 * (size_t)stage_bytes;
+    while (TR > 1 && ((size_t)rows_needed(TR) * inter_pitch > 65536)) TR /= 2;
+    B200_REQUIRE((size_t)rows_needed(TR) * inter_pitch <= budget, "preprocess: vertical downscale factor too large for one tile");
+    const size_t smem = 3072 + 2 * (size_t)stage_bytes + (size_t)rows_needed(TR) * inter_pitch;
     PreParams p{src_dev, s->d_desc, s->d_lut, out_dev, S, TR, layout, out_bf16, P, layout ? S / P : 0, kpad, inter_pitch, stage_bytes};
     const int tiles = (S + TR - 1) / TR;
-    const bool vw8 = (S % 8 == 0) && (layout == 0 || P % 8 == 0);
-    if (vw8) return out_bf16 ? launch_pre<8, true>(p, tiles, B, smem, st) : launch_pre<8, false>(p, tiles, B, smem, st);
-    return out_bf16 ? launch_pre<2, true>(p, tiles, B, smem, st) : launch_pre<2, false>(p, tiles, B, smem, st);
+    return out_bf16 ? launch_pre<true>(p, tiles, B, smem, st) : launch_pre<false>(p, tiles, B, smem, st);
 }
 
 }  // namespace b200

@@ -41,6 +41,15 @@ def peaks() -> dict:
     return {"hbm_gbs": 6650.0, "bf16_sustained": 1400.0, "bf16_burst": 1590.0, "src": "fallback"}
 
 
+def measured_gemm_traffic():
+    """dram__bytes_read+write per GEMM launch from the committed ncu --set full capture (None if absent)."""
+    p = ROOT / "profiles" / "gemm_traffic_r1.json"
+    try:
+        return json.loads(p.read_text())["dram_bytes_per_launch_mean"]
+    except Exception:  # noqa: BLE001
+        return None
+
+
 def gemm_flops_per_image(cfg: dict) -> float:
     n = (cfg["image_size"] // cfg["patch"]) ** 2
     S, d, L, mlp, D, P = n + 1, cfg["width"], cfg["layers"], cfg["mlp_dim"], cfg["embed_dim"], cfg["patch"]
@@ -95,6 +104,12 @@ class ClockSampler:
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx, "reasons": sorted(reasons), "samples": len(sm)}
 
 
+def workload_config(args, cfg: dict, src_hw, world: int) -> dict:
+    return {"workload": f"{args.model} image embedding: batch {args.batch} per GPU of {src_hw[0]}x{src_hw[1]} uint8 RGB -> preprocess (Pillow-exact) + ViT encode -> "
+                        f"{cfg['embed_dim']}-d unit vectors", "global_batch": args.batch * world,
+            "parallelism": f"dp{world} (replicated weights, no collective)"}
+
+
 # ---------------------------------------------------------------------------------------------- CPU (oracle) arm
 def cpu_reference_rate(cfg: dict, weights: dict, src_hw: tuple[int, int], budget_s: float, max_images: int, seed: int = 1234):
     """Times the oracle (reference closure + fp32 tower restatement) on host cores; returns (img/s, images, threads)."""
@@ -127,7 +142,7 @@ def run_reference(args, cfg, weights, src_hw):
     sample = f"{timed[0][1]} images per step ({src_hw[0]}x{src_hw[1]} uint8), fp32, batches of 32, oracle port of the reference CPU path"
     line = {"metric": METRIC, "value": value, "unit": UNIT, "impl": "reference", "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": 1e3 * timed[0][1] / value, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32",
-            "data": "synthetic", "config": {"workload": f"{args.model} image embedding, {src_hw[0]}x{src_hw[1]} uint8 -> {cfg['embed_dim']}-d (CPU sample)"},
+            "data": "synthetic", "config": dict(workload_config(args, cfg, src_hw, max(1, args.gpus)), sample=sample),
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "gpu_launches": 0}
     print(json.dumps(line), flush=True)
@@ -219,16 +234,17 @@ def run_b200(args, cfg, weights, src_hw):
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
-            "config": {"workload": f"{args.model} image embedding: batch {B} per GPU of {src_hw[0]}x{src_hw[1]} uint8 RGB -> preprocess (Pillow-exact) + ViT encode -> "
-                                   f"{cfg['embed_dim']}-d unit vectors", "global_batch": B * world, "parallelism": f"dp{world} (replicated weights, no collective)",
-                       "l2": "per-step working set ~0.9 GB (activations + 77 MB input) exceeds the 126 MB L2; no explicit flush",
-                       "timing": "CUDA events on the launch stream, barrier+synchronize both sides, max over ranks"},
+            "config": dict(workload_config(args, cfg, src_hw, world),
+                           l2="per-step working set ~0.9 GB (activations + 77 MB input) exceeds the 126 MB L2; no explicit flush",
+                           timing="CUDA events on the launch stream, barrier+synchronize both sides, max over ranks"),
             "e2e": {"value": images / (e2e_ms / 1e3), "unit": UNIT, "h2d_bytes_per_step": int(total), "d2h_bytes_per_step": int(B * cfg["embed_dim"] * 4),
                     "wall_clock_value": images / (e2e_wall_ms / 1e3), "call": "B200ClipBackend.embed_packed -> b200clip_embed_host (pinned host in, host float32 out)"},
             "gpu_launches": int(launches),
             "roofline": {"bound": "tensor", "kernel": "gemm_tc_kernel (tcgen05, all encoder GEMMs)", "achieved": achieved, "peak": pk["bf16_sustained"],
                          "unit": "TFLOP/s", "frac": achieved / pk["bf16_sustained"], "peak_source": pk["src"] + " (sustained: kernel timed inside a long step)",
-                         "traffic": None, "launches": prof["gemm"]["launches"], "avg_launch_ms": gemm_ms / max(1, prof["gemm"]["launches"]),
+                         "traffic": measured_gemm_traffic() if args.model == "ViT-B-32" and B == 512 else None,
+                         "traffic_note": "mean dram bytes per launch over the 4 per-layer GEMM shapes, ncu --set full (profiles/step_r1_ncu.csv)",
+                         "launches": prof["gemm"]["launches"], "avg_launch_ms": gemm_ms / max(1, prof["gemm"]["launches"]),
                          "share_of_step": share, "end_to_end_frac_of_tensor_peak": total_flops_per_image(cfg) * value / world / 1e12 / pk["bf16_sustained"]},
             "cpu_baseline": {"value": cpu_rate, "unit": UNIT, "cores": cpu_threads, "kind": "port",
                              "sample": f"{cpu_n} images ({src_hw[0]}x{src_hw[1]}), oracle = reference preprocess closure restated + fp32 tower (torch CPU), batches of 32"},

@@ -233,18 +233,31 @@ topk_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
                 float mx = __uint_as_float(v[0]);
 #pragma unroll
                 for (int j = 1; j < 32; ++j) mx = fmaxf(mx, __uint_as_float(v[j]));
-                if (mx > tau) {
-                    const long long nb = n0 + c * 32;
-                    const int lim = (int)min(32LL, n_hi - nb);                    // < 32 only in the last tile of the gallery
-                    const uint32_t inv = 0xffffffffu - (uint32_t)nb;
+                if (!__any_sync(0xffffffffu, mx > tau)) return;                   // nothing in this 32x32 block beats any row's threshold
+                // branch-free bit mask of this row's survivors, then one loop iteration per survivor (usually 0 or 1):
+                // the score is picked out of the 32 registers with a 5-level select tree instead of 32 branches
+                uint32_t mask = 0;
 #pragma unroll
-                    for (int j = 0; j < 32; ++j) {
-                        const float s = __uint_as_float(v[j]);
-                        if (s > tau && j < lim) {
-                            __stcg(rowptr + cnt, ((unsigned long long)flip_f32(s) << 32) | (inv - (uint32_t)j));
-                            ++cnt;
-                        }
-                    }
+                for (int j = 0; j < 32; ++j) mask |= (__uint_as_float(v[j]) > tau ? 1u : 0u) << j;
+                const long long nb = n0 + c * 32;
+                const long long left = n_hi - nb;                                 // < 32 only in the last tile of the gallery
+                if (left < 32) mask = left <= 0 ? 0u : (mask & ((1u << (int)left) - 1u));
+                const uint32_t inv = 0xffffffffu - (uint32_t)nb;
+                while (mask) {
+                    const int j = __ffs(mask) - 1;
+                    mask &= mask - 1;
+                    uint32_t a16[16], a8[8], a4[4], a2[2];
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) a16[i] = (j & 1) ? v[2 * i + 1] : v[2 * i];
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) a8[i] = (j & 2) ? a16[2 * i + 1] : a16[2 * i];
+#pragma unroll
+                    for (int i = 0; i < 4; ++i) a4[i] = (j & 4) ? a8[2 * i + 1] : a8[2 * i];
+#pragma unroll
+                    for (int i = 0; i < 2; ++i) a2[i] = (j & 8) ? a4[2 * i + 1] : a4[2 * i];
+                    const float s = __uint_as_float((j & 16) ? a2[1] : a2[0]);
+                    __stcg(rowptr + cnt, ((unsigned long long)flip_f32(s) << 32) | (inv - (uint32_t)j));
+                    ++cnt;
                 }
             };
             uint32_t va[32], vb[32];
@@ -323,19 +336,41 @@ __device__ __forceinline__ void scan_hist(const int* hist, int kk, bool hi_first
 }
 
 __global__ void __launch_bounds__(MERGE_THREADS) merge_topk_kernel(const float* __restrict__ ps, const long long* __restrict__ pi, int P,
-                                                                   int Q, int k, float* __restrict__ out_s, long long* __restrict__ out_i) {
+                                                                   int Q, int k, int cache_keys, float* __restrict__ out_s,
+                                                                   long long* __restrict__ out_i) {
+    extern __shared__ __align__(16) uint32_t key_cache[];     // [T] order-preserving score keys (0 = empty slot) when cache_keys
     __shared__ int hist[256];
     __shared__ int sh_digit, sh_before, sh_count, sh_gt, sh_eq;
     __shared__ float ss[MERGE_KMAX];
     __shared__ long long si[MERGE_KMAX];
     const int qi = blockIdx.x, T = P * k, tid = threadIdx.x;
-    auto elem = [&](int e, float& s, long long& id) {
-        const int part = e / k, j = e - part * k;
-        const size_t o = ((size_t)part * Q + qi) * k + j;
-        id = pi[o]; s = ps[o] + 0.0f;
+    auto offset = [&](int e) -> size_t { const int part = e / k; return ((size_t)part * Q + qi) * k + (e - part * k); };
+    // key of candidate e: from shared memory when cached, else recomputed from global memory
+    auto key_of = [&](int e) -> uint32_t {
+        if (cache_keys) return key_cache[e];
+        const size_t o = offset(e);
+        return pi[o] < 0 ? 0u : flip_f32(ps[o] + 0.0f);
     };
     if (tid == 0) { sh_count = 0; sh_gt = 0; sh_eq = 0; }
+    if (cache_keys) {                                          // one pass over global memory, four loads in flight per thread
+        for (int e0 = 0; e0 < T; e0 += 4 * MERGE_THREADS) {
+            float s[4]; long long id[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int e = e0 + u * MERGE_THREADS + tid;
+                id[u] = -1; s[u] = 0.f;
+                if (e < T) { const size_t o = offset(e); id[u] = pi[o]; s[u] = ps[o]; }
+            }
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const int e = e0 + u * MERGE_THREADS + tid;
+                if (e < T) key_cache[e] = id[u] < 0 ? 0u : flip_f32(s[u] + 0.0f);
+            }
+        }
+    }
+    __syncthreads();
     // ---- k-th best score: 4 passes of 8 bits over the order-preserving 32-bit image of the score
+    // (real keys are never 0: flip_f32 maps -inf to 0x007fffff and NaNs are not produced by finite inputs)
     uint32_t prefix = 0; int kk = k; bool all = false;
     for (int pass = 0; pass < 4; ++pass) {
         const int shift = 24 - 8 * pass;
@@ -343,10 +378,8 @@ __global__ void __launch_bounds__(MERGE_THREADS) merge_topk_kernel(const float* 
         __syncthreads();
         for (int e0 = 0; e0 < T; e0 += MERGE_THREADS) {          // whole warps iterate together (hist_add votes)
             const int e = e0 + tid;
-            float s = 0.f; long long id = -1;
-            if (e < T) elem(e, s, id);
-            const uint32_t key = flip_f32(s);
-            const bool act = id >= 0 && (pass == 0 || (key >> (shift + 8)) == (prefix >> (shift + 8)));
+            const uint32_t key = e < T ? key_of(e) : 0u;
+            const bool act = key != 0u && (pass == 0 || (key >> (shift + 8)) == (prefix >> (shift + 8)));
             hist_add(hist, act, (key >> shift) & 255);
         }
         __syncthreads();
@@ -366,10 +399,8 @@ __global__ void __launch_bounds__(MERGE_THREADS) merge_topk_kernel(const float* 
     if (!all) {
         int gt = 0, eq = 0;
         for (int e = tid; e < T; e += MERGE_THREADS) {
-            float s; long long id; elem(e, s, id);
-            if (id < 0) continue;
-            const uint32_t key = flip_f32(s);
-            gt += key > prefix; eq += key == prefix;
+            const uint32_t key = key_of(e);
+            gt += (key != 0u && key > prefix); eq += key == prefix;
         }
         atomicAdd(&sh_gt, gt); atomicAdd(&sh_eq, eq);
         __syncthreads();
@@ -383,10 +414,9 @@ __global__ void __launch_bounds__(MERGE_THREADS) merge_topk_kernel(const float* 
                 __syncthreads();
                 for (int e0 = 0; e0 < T; e0 += MERGE_THREADS) {
                     const int e = e0 + tid;
-                    float s = 0.f; long long id = -1;
-                    if (e < T) elem(e, s, id);
-                    const unsigned long long u = (unsigned long long)id;
-                    const bool act = id >= 0 && flip_f32(s) == prefix && (pass == 0 || (u >> (shift + 8)) == (ip >> (shift + 8)));
+                    bool act = e < T && key_of(e) == prefix;
+                    unsigned long long u = 0;
+                    if (act) { u = (unsigned long long)pi[offset(e)]; act = pass == 0 || (u >> (shift + 8)) == (ip >> (shift + 8)); }
                     hist_add(hist, act, (int)((u >> shift) & 255));
                 }
                 __syncthreads();
@@ -401,12 +431,15 @@ __global__ void __launch_bounds__(MERGE_THREADS) merge_topk_kernel(const float* 
     __syncthreads();
     // ---- gather survivors, sort them, write
     for (int e = tid; e < T; e += MERGE_THREADS) {
-        float s; long long id; elem(e, s, id);
-        if (id < 0) continue;
-        const uint32_t key = flip_f32(s);
-        if (all || key > prefix || (key == prefix && id <= idx_cut)) {
-            const int pos = atomicAdd(&sh_count, 1);
-            if (pos < MERGE_KMAX) { ss[pos] = s; si[pos] = id; }
+        const uint32_t key = key_of(e);
+        if (key == 0u) continue;
+        if (all || key > prefix || key == prefix) {
+            const size_t o = offset(e);
+            const long long id = pi[o];
+            if (all || key > prefix || id <= idx_cut) {
+                const int pos = atomicAdd(&sh_count, 1);
+                if (pos < MERGE_KMAX) { ss[pos] = ps[o] + 0.0f; si[pos] = id; }
+            }
         }
     }
     __syncthreads();
@@ -440,7 +473,12 @@ int merge_topk_run(const float* ps, const long long* pi, int P, int Q, int k, fl
     B200_REQUIRE(k <= MERGE_KMAX, "merge_topk: k larger than 1024 is not supported");
     B200_REQUIRE((long long)P * k < (1LL << 30), "merge_topk: too many candidates per query");
     if (Q == 0) return B200_OK;
-    merge_topk_kernel<<<Q, MERGE_THREADS, 0, st>>>(ps, pi, P, Q, k, out_s, out_i);
+    const size_t T = (size_t)P * k;
+    const int cache = T * 4 <= 160 * 1024;                 // keys fit in shared memory next to the sort buffers
+    const size_t smem = cache ? T * 4 : 0;
+    if (smem > 32 * 1024)
+        B200_CUDA_OK(cudaFuncSetAttribute(merge_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    merge_topk_kernel<<<Q, MERGE_THREADS, smem, st>>>(ps, pi, P, Q, k, cache, out_s, out_i);
     B200_CUDA_OK(cudaGetLastError());
     return B200_OK;
 }
@@ -453,7 +491,8 @@ int topk_plan(int Q, long long N, int k, TopkPlan* plan) {
     plan->qtiles = (Q + TK_BM - 1) / TK_BM;
     const long long ntiles = (N + TK_BN - 1) / TK_BN;
     // qtiles * splits CTAs: fill one wave of 148 SMs when the query tiles are few, two waves otherwise
-    long long splits = plan->qtiles <= kNumSMs / 2 ? kNumSMs / plan->qtiles : (2LL * kNumSMs) / plan->qtiles;
+    long long splits = kNumSMs / plan->qtiles;
+    if (splits * plan->qtiles * 10 < 9LL * kNumSMs) splits = (2LL * kNumSMs) / plan->qtiles;   // one wave must fill >= 90 % of the SMs
     if (splits < 1) splits = 1;
     if (splits > ntiles) splits = ntiles;
     if (splits * k > 16384) splits = 16384 / k;                 // merge kernel capacity

@@ -445,7 +445,7 @@ extern "C" int b200clip_topk(b200clip_handle* h, const void* queries, int32_t Q,
     std::lock_guard<std::mutex> lk(h->mu);
     TopkPlan plan;
     if ((rc = topk_plan(Q, N, k, &plan))) return rc;
-    const size_t need = plan.cand_bytes + plan.part_bytes + 512;
+    const size_t need = plan.cand_bytes + plan.part_bytes + plan.qstage_bytes + 512;
     cudaStream_t st = (cudaStream_t)stream;
     if (need > h->topk_cap) {
         B200_CUDA_OK(cudaStreamSynchronize(st));
@@ -455,7 +455,7 @@ extern "C" int b200clip_topk(b200clip_handle* h, const void* queries, int32_t Q,
     }
     rc = topk_run(queries, gallery, Q, N, D, k, index_base, h->topk_scratch, plan, out_scores, reinterpret_cast<long long*>(out_index),
                   h->status, st);
-    if (rc == B200_OK) h->launches += 2;
+    if (rc == B200_OK) h->launches += plan.qstage_bytes ? 3 : 2;
     return rc;
 }
 

@@ -16,7 +16,7 @@ int launch_embed_preln(const float* patch, const float* cls, const float* pos, c
                        int B, int S, int d, float eps, cudaStream_t st);
 int launch_l2_normalize(const float* in, float* out, int rows, int D, cudaStream_t st);
 int launch_attention(const void* qkv, void* out, int B, int S, int d, int heads, cudaStream_t st);
-struct TopkPlan { int splits, qtiles, cpl; long long rows_per_split; size_t cand_bytes, part_bytes; };
+struct TopkPlan { int splits, qtiles, cpl; long long rows_per_split; size_t cand_bytes, part_bytes, qstage_bytes; };
 int topk_plan(int Q, long long N, int k, TopkPlan* plan);
 int topk_run(const void* queries, const void* gallery, int Q, long long N, int D, int k, long long index_base, void* scratch,
              const TopkPlan& plan, float* out_s, long long* out_i, DeviceStatus* status, cudaStream_t st);

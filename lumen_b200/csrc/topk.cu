@@ -23,6 +23,7 @@ namespace b200 {
 constexpr int TK_BM = 128, TK_BN = 256, TK_BK = 64, TK_STAGES = 4;
 constexpr int TK_A_BYTES = TK_BM * TK_BK * 2, TK_B_BYTES = TK_BN * TK_BK * 2, TK_STAGE_BYTES = TK_A_BYTES + TK_B_BYTES;
 constexpr int TK_SMEM = TK_STAGES * TK_STAGE_BYTES + 256 + 1024;
+constexpr int TK_PREFETCH = 0;      // k-blocks (of 32 KB of gallery) requested from L2 ahead of the TMA loads
 
 struct TopkParams {
     int Q, D, k;
@@ -33,6 +34,7 @@ struct TopkParams {
     float* part_scores;          // [splits][Q][k]
     long long* part_idx;         // [splits][Q][k]
     long long index_base;
+    int scatter;                 // queries were spread over the four TMEM lane quarters (see scatter_queries_kernel)
     DeviceStatus* status;
 };
 
@@ -214,8 +216,9 @@ topk_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     } else {
         const int q = warp & 3;
         const int row = q * 32 + lane;                              // query row inside the tile = TMEM lane
-        const long long qrow = (long long)qt * TK_BM + row;
-        unsigned long long* rowptr = p.cand + ((size_t)sp * p.qtiles * TK_BM + (size_t)qrow) * C;
+        // query handled by this thread: tile row order, or (small batches) interleaved so all four warps get rows
+        const long long qrow = (long long)qt * TK_BM + (p.scatter ? (lane * 4 + q) : row);
+        unsigned long long* rowptr = p.cand + ((size_t)sp * p.qtiles * TK_BM + (size_t)qt * TK_BM + row) * C;   // lists are indexed by tile row
         unsigned long long* warp_rows = p.cand + ((size_t)sp * p.qtiles * TK_BM + (size_t)qt * TK_BM + q * 32) * C;
         float tau = qrow < p.Q ? -INFINITY : INFINITY;      // padding rows of the last query tile never collect candidates
         int cnt = 0;
@@ -289,7 +292,7 @@ topk_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         for (int src = 0; src < 32; ++src) {
             const int n = __shfl_sync(0xffffffffu, cnt, src);
             float tnew;
-            const long long qr = (long long)qt * TK_BM + q * 32 + src;
+            const long long qr = (long long)qt * TK_BM + (p.scatter ? src * 4 + q : q * 32 + src);
             if (qr < p.Q)       // warp-uniform
                 compact_row<CPL>(warp_rows + (size_t)src * C, n, p.k, lane, true, C, &tnew, p.part_scores + ((size_t)sp * p.Q + qr) * p.k,
                                  p.part_idx + ((size_t)sp * p.Q + qr) * p.k, p.index_base);
@@ -501,7 +504,18 @@ int topk_plan(int Q, long long N, int k, TopkPlan* plan) {
     plan->splits = (int)((ntiles + tiles_per_split - 1) / tiles_per_split);
     plan->cand_bytes = (size_t)plan->splits * plan->qtiles * TK_BM * 32 * plan->cpl * 8;
     plan->part_bytes = (((size_t)plan->splits * Q * k * 4 + 255) & ~(size_t)255) + (size_t)plan->splits * Q * k * 8;
+    plan->part_bytes = (plan->part_bytes + 255) & ~(size_t)255;
+    plan->qstage_bytes = Q < TK_BM ? (size_t)TK_BM * 1024 * 2 : 0;      // staged, interleaved copy of a small query batch (D <= 1024)
     return B200_OK;
+}
+
+// Query i of a batch smaller than one tile goes to tile row (i % 4) * 32 + i / 4, i.e. TMEM lane quarter i % 4, so the
+// per-row candidate bookkeeping is shared by all four epilogue warps instead of piling up in the first one.
+__global__ void scatter_queries_kernel(const __half* __restrict__ src, __half* __restrict__ dst, int Q, int D) {
+    const int i = blockIdx.x;
+    const int r = (i & 3) * 32 + (i >> 2);
+    for (int c = threadIdx.x * 8; c < D; c += blockDim.x * 8)
+        *reinterpret_cast<uint4*>(dst + (size_t)r * D + c) = *reinterpret_cast<const uint4*>(src + (size_t)i * D + c);
 }
 
 template <int CPL> static int launch_topk(const CUtensorMap& tq, const CUtensorMap& tg, const TopkParams& p, cudaStream_t st) {
@@ -516,17 +530,28 @@ template <int CPL> static int launch_topk(const CUtensorMap& tq, const CUtensorM
 int topk_run(const void* queries, const void* gallery, int Q, long long N, int D, int k, long long index_base,
              void* scratch, const TopkPlan& plan, float* out_s, long long* out_i, DeviceStatus* status, cudaStream_t st) {
     B200_REQUIRE(D > 0 && D % 64 == 0, "topk: embedding dim must be a multiple of 64");
+    B200_REQUIRE(plan.qstage_bytes == 0 || D <= 1024, "topk: embedding dim above 1024 is not supported for batches below 128 queries");
     B200_REQUIRE(N < (1LL << 31), "topk: at most 2^31-1 gallery rows per GPU");
     CUtensorMap tq, tg;
-    int rc = make_tmap_2d(&tq, queries, Q, D, (uint64_t)D * 2, TK_BM, true);
+    uint8_t* sc = reinterpret_cast<uint8_t*>(scratch);
+    const int scatter = plan.qstage_bytes > 0 ? 1 : 0;
+    int rc;
+    if (scatter) {
+        __half* staged = reinterpret_cast<__half*>(sc + plan.cand_bytes + plan.part_bytes);
+        B200_CUDA_OK(cudaMemsetAsync(staged, 0, plan.qstage_bytes, st));
+        scatter_queries_kernel<<<Q, 64, 0, st>>>(reinterpret_cast<const __half*>(queries), staged, Q, D);
+        B200_CUDA_OK(cudaGetLastError());
+        rc = make_tmap_2d(&tq, staged, TK_BM, D, (uint64_t)D * 2, TK_BM, true);
+    } else {
+        rc = make_tmap_2d(&tq, queries, Q, D, (uint64_t)D * 2, TK_BM, true);
+    }
     if (rc) return rc;
     rc = make_tmap_2d(&tg, gallery, (uint64_t)N, D, (uint64_t)D * 2, TK_BN, true);
     if (rc) return rc;
-    uint8_t* sc = reinterpret_cast<uint8_t*>(scratch);
     float* part_s = reinterpret_cast<float*>(sc + plan.cand_bytes);
     long long* part_i = reinterpret_cast<long long*>(sc + plan.cand_bytes + (((size_t)plan.splits * Q * k * 4 + 255) & ~(size_t)255));
     TopkParams p{Q, D, k, N, plan.rows_per_split, plan.splits, plan.qtiles, reinterpret_cast<unsigned long long*>(sc),
-                 part_s, part_i, index_base, status};
+                 part_s, part_i, index_base, scatter, status};
     rc = plan.cpl == 16 ? launch_topk<16>(tq, tg, p, st) : launch_topk<32>(tq, tg, p, st);
     if (rc) return rc;
     return merge_topk_run(part_s, part_i, plan.splits, Q, k, out_s, out_i, st);
@@ -592,6 +617,7 @@ extern "C" int b200clip_topk_static(const void* queries_f16_dev, int32_t Q, cons
     plan.splits = (int)((ntiles + tiles_per_split - 1) / tiles_per_split);
     plan.cand_bytes = (size_t)plan.splits * plan.qtiles * TK_BM * 32 * 16 * 8;
     plan.part_bytes = (((size_t)plan.splits * Q * k * 4 + 255) & ~(size_t)255) + (size_t)plan.splits * Q * k * 8;
+    plan.qstage_bytes = 0;
     cudaStream_t st = (cudaStream_t)stream;
     // The array keeps whatever the previous call left.  Only the watchdog words have to start at zero: candidate
     // counts live in registers and every result slot that is read is written first.

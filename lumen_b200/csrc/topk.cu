@@ -23,7 +23,6 @@ namespace b200 {
 constexpr int TK_BM = 128, TK_BN = 256, TK_BK = 64, TK_STAGES = 4;
 constexpr int TK_A_BYTES = TK_BM * TK_BK * 2, TK_B_BYTES = TK_BN * TK_BK * 2, TK_STAGE_BYTES = TK_A_BYTES + TK_B_BYTES;
 constexpr int TK_SMEM = TK_STAGES * TK_STAGE_BYTES + 256 + 1024;
-constexpr int TK_PREFETCH = 0;      // k-blocks (of 32 KB of gallery) requested from L2 ahead of the TMA loads
 
 struct TopkParams {
     int Q, D, k;

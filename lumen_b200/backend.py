@@ -84,6 +84,18 @@ class B200ClipBackend(BaseClipBackend):
         if self._initialized:
             return
         try:
+            if self._weights is None:
+                # real checkpoints: the formats the reference's torch backend reads (weight_loaders.py)
+                from .weight_loaders import load_vision_weights
+                root = getattr(self.resources, "runtime_files_path", None) or getattr(self.resources, "model_root_path", None)
+                if root is not None:
+                    self._weights, found = load_vision_weights(root)
+                    cfgd = dict(getattr(self.resources, "config", {}) or {})
+                    cfgd["b200_vit"] = found
+                    try:
+                        self.resources.config = cfgd
+                    except Exception:  # noqa: BLE001 - frozen resources: fall back to name lookup
+                        pass
             cfg = _vit_config_for(self.resources)
             size = self.resources.get_image_size()
             if size is not None:

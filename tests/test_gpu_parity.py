@@ -325,3 +325,21 @@ def test_full_size_properties_c2_and_search():
     for r, row in enumerate(rows):
         assert len(set(i[row].tolist()) ^ set(ti[r].tolist())) <= 4
     eng.close()
+
+
+def test_encoder_exact_gelu_variant():
+    """LAION open_clip checkpoints use exact GELU instead of QuickGELU: same gate, other epilogue."""
+    from lumen_b200 import VIT_CONFIGS, synthetic_weights
+    from lumen_b200.engine import Engine
+    from oracle import clip_oracle as O
+    cfg = dict(VIT_CONFIGS["ViT-tiny-test"], activation="gelu")
+    w = synthetic_weights(cfg, seed=5)
+    eng = Engine(cfg, device=0, max_batch=8)
+    eng.load_weights(w)
+    imgs = [synth_image(60 + i, 70 + i, 90 - i) for i in range(6)]
+    emb = eng.embed_host(imgs, mode=1)
+    ref = O.vit_encode(w, O.preprocess_batch(imgs, cfg["image_size"], 1), cfg)
+    assert (emb * ref).sum(1).min() >= 0.999
+    quick = O.vit_encode(w, O.preprocess_batch(imgs, cfg["image_size"], 1), dict(cfg, activation="quick_gelu"))
+    assert (emb * quick).sum(1).min() < (emb * ref).sum(1).min()     # the two activations are distinguishable
+    eng.close()

@@ -1,0 +1,92 @@
+"""CPU: request coalescing and the service seam (§8b B-service) with a fake backend."""
+import threading
+import time
+
+import numpy as np
+import pytest
+
+from lumen_b200.interface import BackendInfo, BaseClipBackend, InferenceError
+from lumen_b200.service import BatchedBackendView, MicroBatcher
+
+
+class FakeBackend(BaseClipBackend):
+    def __init__(self, delay=0.01):
+        super().__init__(resources=None)
+        self._initialized = True
+        self.calls = []
+        self.delay = delay
+
+    def initialize(self): pass
+    def text_to_vector(self, text): raise InferenceError("no text")
+    def get_info(self): return BackendInfo(runtime="fake")
+
+    def image_to_vector(self, b):
+        return self.image_batch_to_vectors([b])[0]
+
+    def image_batch_to_vectors(self, images):
+        self.calls.append(len(images))
+        time.sleep(self.delay)
+        if any(i == b"boom" for i in images):
+            raise InferenceError("Batch image encoding failed: boom")
+        return np.stack([np.full(4, float(len(i)), np.float32) for i in images])
+
+
+def test_micro_batcher_coalesces_concurrent_requests():
+    be = FakeBackend()
+    mb = MicroBatcher(be, max_batch=8, max_wait_ms=50)
+    out = {}
+
+    def work(i):
+        out[i] = mb.image_to_vector(b"x" * (i + 1))
+
+    th = [threading.Thread(target=work, args=(i,)) for i in range(10)]
+    [t.start() for t in th]; [t.join() for t in th]
+    assert all(out[i][0] == i + 1 and out[i].dtype == np.float32 for i in range(10))     # every caller got ITS row
+    assert sum(be.calls) == 10 and len(be.calls) <= 4 and max(be.calls) <= 8              # 10 requests in few batches
+    v = mb.image_to_vector(b"abc")                                                         # a lone request still completes
+    assert v[0] == 3.0
+
+
+def test_micro_batcher_propagates_errors_to_the_whole_batch():
+    be = FakeBackend()
+    mb = MicroBatcher(be, max_batch=4, max_wait_ms=50)
+    errs = []
+
+    def work(payload):
+        try:
+            mb.image_to_vector(payload)
+        except InferenceError as e:
+            errs.append(str(e))
+
+    th = [threading.Thread(target=work, args=(p,)) for p in (b"ok", b"boom", b"ok2")]
+    [t.start() for t in th]; [t.join() for t in th]
+    assert len(errs) >= 1 and all("boom" in e for e in errs)
+    assert mb.image_to_vector(b"fine")[0] == 4.0                                          # the batcher keeps working
+
+
+def test_service_seam_with_reference_package():
+    pytest.importorskip("grpc")
+    import sys
+    from pathlib import Path
+    ref = Path("/root/reference/packages")
+    if not ref.exists():
+        pytest.skip("reference tree not mounted")
+    for p in (ref / "lumen-clip" / "src", ref / "lumen-resources" / "src"):
+        if str(p) not in sys.path:
+            sys.path.insert(0, str(p))
+    try:
+        from lumen_b200.service import b200_clip_service_class
+        cls = b200_clip_service_class()
+    except Exception as e:  # noqa: BLE001
+        pytest.skip(f"reference service not importable here: {e}")
+
+    class Res:
+        model_name = "fake"; runtime = "b200"; labels = None; label_embeddings = None
+        def has_classification_support(self): return False
+
+    be = FakeBackend(delay=0.0)
+    be.resources = Res()
+    svc = cls(be, Res())
+    assert "clip_image_embed" in svc.get_supported_tasks() or len(svc.get_supported_tasks()) > 0
+    assert isinstance(svc.model.backend, BatchedBackendView)
+    assert svc.model.backend.image_to_vector(b"abcd")[0] == 4.0

@@ -13,11 +13,8 @@
 #include "common.cuh"
 #include "kernels.h"
 
+#include <cstdlib>
 #include <mutex>
-
-#ifndef B200_RES_RMW
-#define B200_RES_RMW 0   // measured on B200: load-add-store 65.9 us vs vector RED 43.6 us for the out-proj GEMM
-#endif
 
 namespace b200 {
 
@@ -69,6 +66,59 @@ __device__ __forceinline__ uint2 pack4_bf16(float a, float b, float c, float d) 
     __nv_bfloat162 lo = __floats2bfloat162_rn(a, b), hi = __floats2bfloat162_rn(c, d);
     uint2 r; r.x = *reinterpret_cast<uint32_t*>(&lo); r.y = *reinterpret_cast<uint32_t*>(&hi);
     return r;
+}
+
+// Epilogue of one accumulator (128 rows x BN columns in this CTA's TMEM) for one epilogue warp: TMEM quarter q,
+// 16-column sub-chunks half, half+2, ...  `release()` hands the accumulator back once this warp has read its share.
+template <int BN, int EPI, int ACT, class Release>
+__device__ __forceinline__ void epilogue_tile(const GemmParams& p, float* stg, int half, int lane, uint32_t tsrc, int row_base, int n0,
+                                      Release&& release) {
+    const int sub_r = lane >> 2, c4 = (lane & 3) * 4;   // store phase: 4 lanes cover 16 columns of one row, 8 rows per pass
+    const int nsub = min(BN / 16, (p.N - n0 + 15) / 16);
+    uint32_t v[16];
+    if (half < nsub) tmem_ld_32x16(tsrc + half * 16, v);
+    else release();                           // nothing to store for this warp: hand the accumulator back at once
+#pragma unroll 1
+    for (int c = half; c < nsub; c += 2) {
+        tmem_ld_wait();
+        float4* s4 = reinterpret_cast<float4*>(stg + lane * EPI_PITCH);
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+            s4[j] = make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]), __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3]));
+        if (c + 2 < nsub) tmem_ld_32x16(tsrc + (c + 2) * 16, v);       // in flight while this sub-chunk is stored
+        else release();                                                // accumulator fully read: hand it back
+        __syncwarp();
+        const int col = n0 + c * 16 + c4;
+        const bool col_ok = col < p.N;                                 // N % 4 == 0
+        float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (p.bias != nullptr && col_ok) b4 = __ldg(reinterpret_cast<const float4*>(p.bias + col));
+        float4 a[4];
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            a[i] = *reinterpret_cast<const float4*>(stg + (i * 8 + sub_r) * EPI_PITCH + c4);
+            a[i].x += b4.x; a[i].y += b4.y; a[i].z += b4.z; a[i].w += b4.w;
+        }
+#pragma unroll
+        for (int i = 0; i < 4; ++i) {
+            const int row = row_base + i * 8 + sub_r;
+            if (row >= p.M || !col_ok) continue;
+            if (EPI == EPI_BIAS_RES_F32) {
+                // x += acc + bias: one fire-and-forget vector reduction per 16 bytes (a load-add-store
+                // variant measured 65.9 us against 43.6 us on the out-proj shape)
+                red_add_v4(reinterpret_cast<float*>(p.out) + (size_t)row * p.ldc + col, a[i]);
+            } else if (EPI == EPI_F32) {
+                *reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + (size_t)row * p.ldc + col) = a[i];
+            } else {
+                if (EPI == EPI_BIAS_ACT_BF16) {
+                    a[i].x = apply_act<ACT>(a[i].x); a[i].y = apply_act<ACT>(a[i].y);
+                    a[i].z = apply_act<ACT>(a[i].z); a[i].w = apply_act<ACT>(a[i].w);
+                }
+                *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(p.out) + (size_t)row * p.ldc + col) =
+                    pack4_bf16(a[i].x, a[i].y, a[i].z, a[i].w);
+            }
+        }
+        __syncwarp();
+    }
 }
 
 template <int BN, int EPI, int ACT>
@@ -146,89 +196,132 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const int q = warp & 3;                       // TMEM lane quarter this warp may read
         const int half = (warp - 2) >> 2;             // which 16-column sub-chunks (even / odd) this warp stores
         float* stg = epi_stage + (warp - 2) * EPI_STAGE_WORDS;
-        const int sub_r = lane >> 2, c4 = (lane & 3) * 4;   // store phase: 4 lanes cover 16 columns of one row, 8 rows per pass
         int it = 0; bool ok = true;
         for (int t = blockIdx.x; t < tiles && ok; t += gridDim.x, ++it) {
             const int m0 = (t / tiles_n) * BM, n0 = (t % tiles_n) * BN;
             const int as = it & 1; const uint32_t aph = (it >> 1) & 1;
             if (!(ok = mbar_wait(&acc_full[as], aph, p.status, 4))) break;
             tc_fence_after();
-            const int row_base = m0 + q * 32;
-            const uint32_t tsrc = tmem_base + ((uint32_t)(q * 32) << 16) + as * BN;
-            const int nsub = min(BN / 16, (p.N - n0 + 15) / 16);
-            uint32_t v[16];
-            if (half < nsub) tmem_ld_32x16(tsrc + half * 16, v);
-            else {                                    // nothing to store for this warp: hand the accumulator back at once
+            epilogue_tile<BN, EPI, ACT>(p, stg, half, lane, tmem_base + ((uint32_t)(q * 32) << 16) + as * BN, m0 + q * 32, n0, [&] {
                 tc_fence_before();
+                __syncwarp();
                 if (lane == 0) mbar_arrive(&acc_empty[as]);
-            }
-#pragma unroll 1
-            for (int c = half; c < nsub; c += 2) {
-#if B200_RES_RMW
-                // residual epilogue, load-add-store form: the x values are requested before the accumulator is even
-                // waited for, so their latency hides behind the TMEM load and the shared-memory transpose
-                float4 xr[4];
-                if (EPI == EPI_BIAS_RES_F32) {
-                    const int colx = n0 + c * 16 + c4;
-#pragma unroll
-                    for (int i = 0; i < 4; ++i) {
-                        const int row = row_base + i * 8 + sub_r;
-                        xr[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-                        if (row < p.M && colx < p.N) xr[i] = __ldcg(reinterpret_cast<const float4*>(reinterpret_cast<const float*>(p.out) + (size_t)row * p.ldc + colx));
-                    }
-                }
-#endif
-                tmem_ld_wait();
-                float4* s4 = reinterpret_cast<float4*>(stg + lane * EPI_PITCH);
-#pragma unroll
-                for (int j = 0; j < 4; ++j)
-                    s4[j] = make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]), __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3]));
-                if (c + 2 < nsub) tmem_ld_32x16(tsrc + (c + 2) * 16, v);       // in flight while this sub-chunk is stored
-                else {                                                         // accumulator fully read: hand it back
-                    tc_fence_before();
-                    __syncwarp();
-                    if (lane == 0) mbar_arrive(&acc_empty[as]);
-                }
-                __syncwarp();
-                const int col = n0 + c * 16 + c4;
-                const bool col_ok = col < p.N;                                 // N % 4 == 0
-                float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f);
-                if (p.bias != nullptr && col_ok) b4 = __ldg(reinterpret_cast<const float4*>(p.bias + col));
-                float4 a[4];
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    a[i] = *reinterpret_cast<const float4*>(stg + (i * 8 + sub_r) * EPI_PITCH + c4);
-                    a[i].x += b4.x; a[i].y += b4.y; a[i].z += b4.z; a[i].w += b4.w;
-                }
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    const int row = row_base + i * 8 + sub_r;
-                    if (row >= p.M || !col_ok) continue;
-                    if (EPI == EPI_BIAS_RES_F32) {
-#if B200_RES_RMW
-                        *reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + (size_t)row * p.ldc + col) =
-                            make_float4(xr[i].x + a[i].x, xr[i].y + a[i].y, xr[i].z + a[i].z, xr[i].w + a[i].w);
-#else                                  // x += acc + bias: one fire-and-forget vector reduction per 16 bytes
-                        red_add_v4(reinterpret_cast<float*>(p.out) + (size_t)row * p.ldc + col, a[i]);
-#endif
-                    } else if (EPI == EPI_F32) {
-                        *reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + (size_t)row * p.ldc + col) = a[i];
-                    } else {
-                        if (EPI == EPI_BIAS_ACT_BF16) {
-                            a[i].x = apply_act<ACT>(a[i].x); a[i].y = apply_act<ACT>(a[i].y);
-                            a[i].z = apply_act<ACT>(a[i].z); a[i].w = apply_act<ACT>(a[i].w);
-                        }
-                        *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(p.out) + (size_t)row * p.ldc + col) =
-                            pack4_bf16(a[i].x, a[i].y, a[i].z, a[i].w);
-                    }
-                }
-                __syncwarp();
-            }
+            });
         }
     }
     tc_fence_before();
     __syncthreads();
     if (warp == 1) { __syncwarp(); tmem_dealloc(tmem_base, Cfg::TMEM_COLS); }
+}
+
+// ------------------------------------------------------------------------------------------ CTA-pair variant
+// Same pipeline on a cluster of two CTAs (tcgen05 cta_group::2): one UMMA covers 256 rows x BN columns, CTA rank r
+// holds rows m0 + 128 r of A and HALF of the W tile (BN/2 rows), so every SM reads 64 B/clk of operands from
+// shared memory instead of 96 and a stage costs 32 KB instead of 48 (six stages).  The leader (rank 0) issues the
+// MMAs; its commits arrive on the stage / accumulator barriers of both CTAs; both CTAs' TMA loads credit the
+// leader's "full" barrier; the epilogue warps of both CTAs hand accumulators back on the leader's barrier.
+template <int BN> struct Gemm2Cfg {
+    static constexpr int STAGES = 6;
+    static constexpr int A_BYTES = BM * BK * 2;
+    static constexpr int B_BYTES = (BN / 2) * BK * 2;
+    static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+    static constexpr int TMEM_COLS = 2 * BN;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_WARPS * EPI_STAGE_WORDS * 4 + 256 + 1024;
+};
+
+template <int BN, int EPI, int ACT>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
+gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, GemmParams p) {
+    using Cfg = Gemm2Cfg<BN>;
+    constexpr int STAGES = Cfg::STAGES;
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    float* epi_stage = reinterpret_cast<float*>(smem + STAGES * Cfg::STAGE_BYTES);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * Cfg::STAGE_BYTES + EPI_WARPS * EPI_STAGE_WORDS * 4);
+    uint64_t* full = bars;                  // [STAGES]  used in the leader only
+    uint64_t* empty = bars + STAGES;        // [STAGES]  one per CTA, signalled by the leader's multicast commit
+    uint64_t* acc_full = bars + 2 * STAGES; // [2]       one per CTA, multicast commit
+    uint64_t* acc_empty = acc_full + 2;     // [2]       leader only: 2 x EPI_WARPS arrivals
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const uint32_t rank = cluster_ctarank();
+    const int pair = blockIdx.x >> 1, npairs = gridDim.x >> 1;
+    const int tiles_n = (p.N + BN - 1) / BN;
+    const int tiles = ((p.M + 2 * BM - 1) / (2 * BM)) * tiles_n;
+    const int kblocks = p.K / BK;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmA);
+        tma_prefetch_desc(&tmB);
+        for (int s = 0; s < STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+        for (int a = 0; a < 2; ++a) { mbar_init(&acc_full[a], 1); mbar_init(&acc_empty[a], 2 * EPI_WARPS); }
+        fence_mbar_init();
+    }
+    if (warp == 1) tmem_alloc_pair(tmem_slot, Cfg::TMEM_COLS);
+    tc_fence_before();
+    cluster_sync_all();                      // barriers of both CTAs initialised before any remote arrive / TMA credit
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        if (lane == 0) {
+            int s = 0; uint32_t ph = 0; bool ok = true;
+            for (int t = pair; t < tiles && ok; t += npairs) {
+                const int m0 = (t / tiles_n) * 2 * BM + (int)rank * BM, n0 = (t % tiles_n) * BN + (int)rank * (BN / 2);
+                for (int kb = 0; kb < kblocks; ++kb) {
+                    if (!(ok = mbar_wait(&empty[s], ph ^ 1, p.status, 21))) break;
+                    uint8_t* sa = smem + s * Cfg::STAGE_BYTES;
+                    if (rank == 0) mbar_arrive_expect_tx(&full[s], 2 * Cfg::STAGE_BYTES);
+                    tma_load_2d_pair(sa, &tmA, &full[s], kb * BK, m0);
+                    tma_load_2d_pair(sa + Cfg::A_BYTES, &tmB, &full[s], kb * BK, n0);
+                    if (++s == STAGES) { s = 0; ph ^= 1; }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        if (rank == 0 && lane == 0) {
+            constexpr uint32_t idesc = umma_idesc(2 * BM, BN, /*bf16*/ 1);
+            int s = 0; uint32_t ph = 0; int it = 0; bool ok = true;
+            for (int t = pair; t < tiles && ok; t += npairs, ++it) {
+                const int as = it & 1; const uint32_t aph = (it >> 1) & 1;
+                if (!(ok = mbar_wait(&acc_empty[as], aph ^ 1, p.status, 22))) break;
+                tc_fence_after();
+                const uint32_t d_tmem = tmem_base + as * BN;
+                for (int kb = 0; kb < kblocks; ++kb) {
+                    if (!(ok = mbar_wait(&full[s], ph, p.status, 23))) break;
+                    tc_fence_after();
+                    const uint32_t sa = smem_u32(smem + s * Cfg::STAGE_BYTES);
+                    const uint64_t da = umma_desc_sw128(sa), db = umma_desc_sw128(sa + Cfg::A_BYTES);
+#pragma unroll
+                    for (int k = 0; k < BK / 16; ++k) umma_f16_pair(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
+                    umma_commit_pair(&empty[s]);
+                    if (++s == STAGES) { s = 0; ph ^= 1; }
+                }
+                if (ok) umma_commit_pair(&acc_full[as]);
+            }
+        }
+    } else {
+        const int q = warp & 3;
+        const int half = (warp - 2) >> 2;
+        float* stg = epi_stage + (warp - 2) * EPI_STAGE_WORDS;
+        const uint32_t leader_acc_empty0 = mapa_u32(smem_u32(&acc_empty[0]), 0);
+        int it = 0; bool ok = true;
+        for (int t = pair; t < tiles && ok; t += npairs, ++it) {
+            const int m0 = (t / tiles_n) * 2 * BM + (int)rank * BM, n0 = (t % tiles_n) * BN;
+            const int as = it & 1; const uint32_t aph = (it >> 1) & 1;
+            if (!(ok = mbar_wait(&acc_full[as], aph, p.status, 24))) break;
+            tc_fence_after();
+            epilogue_tile<BN, EPI, ACT>(p, stg, half, lane, tmem_base + ((uint32_t)(q * 32) << 16) + as * BN, m0 + q * 32, n0, [&] {
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive_cluster(leader_acc_empty0 + as * 8);
+            });
+        }
+    }
+    tc_fence_before();
+    cluster_sync_all();                      // neither CTA may exit (or free TMEM) while its partner can still touch it
+    if (warp == 1) { __syncwarp(); tmem_dealloc_pair(tmem_base, Cfg::TMEM_COLS); }
 }
 
 // ------------------------------------------------------------------------------------------ host side
@@ -270,6 +363,24 @@ template <int BN, int EPI, int ACT> static int launch_gemm(const CUtensorMap& ta
     B200_CUDA_OK(cudaGetLastError());
     return B200_OK;
 }
+template <int BN, int EPI, int ACT> static int launch_gemm2(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, cudaStream_t st) {
+    using Cfg = Gemm2Cfg<BN>;
+    B200_CUDA_OK(cudaFuncSetAttribute(gemm_tc2_kernel<BN, EPI, ACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+    const int tiles = ((p.M + 2 * BM - 1) / (2 * BM)) * ((p.N + BN - 1) / BN);
+    const int pairs = tiles < kNumSMs / 2 ? tiles : kNumSMs / 2;
+    gemm_tc2_kernel<BN, EPI, ACT><<<2 * pairs, GEMM_THREADS, Cfg::SMEM_BYTES, st>>>(ta, tb, p);   // cluster dims are compiled in
+    B200_CUDA_OK(cudaGetLastError());
+    return B200_OK;
+}
+static int dispatch_gemm2(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, cudaStream_t st) {
+    switch (p.epi) {
+        case EPI_F32: return launch_gemm2<256, EPI_F32, 0>(ta, tb, p, st);
+        case EPI_BIAS_BF16: return launch_gemm2<256, EPI_BIAS_BF16, 0>(ta, tb, p, st);
+        case EPI_BIAS_RES_F32: return launch_gemm2<256, EPI_BIAS_RES_F32, 0>(ta, tb, p, st);
+        default: return p.act == ACT_QUICK_GELU ? launch_gemm2<256, EPI_BIAS_ACT_BF16, ACT_QUICK_GELU>(ta, tb, p, st)
+                                                : launch_gemm2<256, EPI_BIAS_ACT_BF16, ACT_GELU>(ta, tb, p, st);
+    }
+}
 template <int BN> static int dispatch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, cudaStream_t st) {
     switch (p.epi) {
         case EPI_F32: return launch_gemm<BN, EPI_F32, 0>(ta, tb, p, st);
@@ -300,6 +411,16 @@ int gemm_bf16_tc(const void* A, int lda, const void* W, int ldw, int M, int N, i
         else if (c128 < c256 && c128 < c192) bn = 128;
     }
     CUtensorMap ta, tb;
+    static const int force = [] { const char* e = getenv("B200_GEMM_PAIR"); return e ? atoi(e) : -1; }();   // -1 auto, 0 never, 1 always
+    const bool pair = force == 1 || (force != 0 && false);
+    if (pair) {
+        GemmParams p2{M, N, K, bias, out, ldc, epi, act, status};
+        int rc2 = make_tmap_2d(&ta, A, M, K, (uint64_t)lda * 2, BM, false);
+        if (rc2) return rc2;
+        rc2 = make_tmap_2d(&tb, W, N, K, (uint64_t)ldw * 2, 128, false);      // each CTA loads half of the 256-wide W tile
+        if (rc2) return rc2;
+        return dispatch_gemm2(ta, tb, p2, st);
+    }
     int rc = make_tmap_2d(&ta, A, M, K, (uint64_t)lda * 2, BM, false);
     if (rc) return rc;
     rc = make_tmap_2d(&tb, W, N, K, (uint64_t)ldw * 2, bn, false);

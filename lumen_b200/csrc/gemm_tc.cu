@@ -8,7 +8,8 @@
 // Layout per CTA (320 threads, one CTA per SM, grid = min(#tiles, 148)):
 //   warp 0      TMA producer: 128x64 A tile + BNx64 W tile per stage, SWIZZLE_128B, mbarrier complete_tx
 //   warp 1      TMEM allocator + single-thread tcgen05.mma issuer (UMMA 128 x BN x 16, fp32 accumulate in TMEM)
-//   warps 2..9  epilogue: tcgen05.ld (32 lanes x 16 columns) -> smem transpose -> coalesced stores / vector reductions
+//   warps 2..9  epilogue: tcgen05.ld -> bias / activation / convert -> swizzled 128-byte boxes in smem -> TMA store
+//               (residual epilogue: TMA reduce-add)
 // TMEM holds two BN-column accumulators so the epilogue of tile i overlaps the MMAs of tile i+1.
 #include "common.cuh"
 #include "kernels.h"
@@ -31,17 +32,15 @@ struct GemmParams {
 
 constexpr int BM = 128, BK = 64;
 constexpr int EPI_WARPS = 8;                  // two warps per TMEM lane quarter, alternating 16-column sub-chunks
-constexpr int EPI_PITCH = 20;                 // floats per staged row (16 + 4): conflict-free 128-bit rows
-constexpr int EPI_STAGE_WORDS = 32 * EPI_PITCH;
 constexpr int GEMM_THREADS = 64 + 32 * EPI_WARPS;
 
 template <int BN> struct GemmCfg {
-    static constexpr int STAGES = BN == 256 ? 4 : (BN == 192 ? 5 : 6);
+    static constexpr int STAGES = BN == 256 ? 4 : (BN == 192 ? 4 : 6);
     static constexpr int A_BYTES = BM * BK * 2;
     static constexpr int B_BYTES = BN * BK * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
     static constexpr int TMEM_COLS = BN == 128 ? 256 : 512;   // two accumulators, allocation must be a power of two
-    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_WARPS * EPI_STAGE_WORDS * 4 + 256 + 1024;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 2 * 16384 + 256 + 1024;
 };
 
 template <int ACT> __device__ __forceinline__ float apply_act(float v) {
@@ -68,68 +67,87 @@ __device__ __forceinline__ uint2 pack4_bf16(float a, float b, float c, float d) 
     return r;
 }
 
-// Epilogue of one accumulator (128 rows x BN columns in this CTA's TMEM) for one epilogue warp: TMEM quarter q,
-// 16-column sub-chunks half, half+2, ...  `release()` hands the accumulator back once this warp has read its share.
+// Epilogue of one accumulator (128 rows x BN columns in this CTA's TMEM), executed by all eight epilogue warps.
+// The tile leaves in boxes of 128 rows x 128 bytes (64 bf16 or 32 fp32 columns): a thread owns one row (its TMEM
+// lane) and, with the warp that shares its lane quarter, half of the box's columns.  It adds the bias, applies the
+// activation, converts, and writes four 16-byte chunks into a shared-memory slot laid out exactly as the output
+// tensor map's SWIZZLE_128B box (chunk j of row r at r*128 + ((j ^ (r & 7)) << 4): conflict-free).  One thread then
+// hands the slot to the TMA engine: a plain tensor store, or for the residual epilogue a tensor REDUCE-ADD
+// (x += acc + bias performed by the memory system, one add per element, so still deterministic).  Global memory is
+// therefore written in full 128-byte lines by the copy engine instead of 32-byte pieces by the LSU, which is what
+// bounded every K = 768 GEMM before (62 us floor for the 118 MB QKV output).  Two slots alternate; `box_seq` counts
+// boxes across tiles; `release()` returns the accumulator to the MMA warp once this warp has read its share.
+constexpr int EPI_SLOT_BYTES = 128 * 128;
+constexpr int EPI_THREADS = 32 * EPI_WARPS;
+
 template <int BN, int EPI, int ACT, class Release>
-__device__ __forceinline__ void epilogue_tile(const GemmParams& p, float* stg, int half, int lane, uint32_t tsrc, int row_base, int n0,
-                                      Release&& release) {
-    const int sub_r = lane >> 2, c4 = (lane & 3) * 4;   // store phase: 4 lanes cover 16 columns of one row, 8 rows per pass
-    const int nsub = min(BN / 16, (p.N - n0 + 15) / 16);
-    uint32_t v[16];
-    if (half < nsub) tmem_ld_32x16(tsrc + half * 16, v);
-    else release();                           // nothing to store for this warp: hand the accumulator back at once
+__device__ __forceinline__ void epilogue_tile(const GemmParams& p, const CUtensorMap* tmC, uint8_t* slots, int& box_seq, int q, int half,
+                                              int lane, bool issuer, uint32_t tsrc, int m0, int n0, Release&& release) {
+    constexpr bool OUT_F32 = (EPI == EPI_F32 || EPI == EPI_BIAS_RES_F32);
+    constexpr int BOXC = OUT_F32 ? 32 : 64;            // columns per 128-byte box
+    constexpr int NV = BOXC / 2;                         // columns per thread and box
+    const int nbox = min(BN / BOXC, (p.N - n0 + BOXC - 1) / BOXC);
+    const int r = q * 32 + lane;                         // row inside the tile = TMEM lane
 #pragma unroll 1
-    for (int c = half; c < nsub; c += 2) {
+    for (int ob = 0; ob < nbox; ++ob, ++box_seq) {
+        uint8_t* slot = slots + (box_seq & 1) * EPI_SLOT_BYTES;
+        const int col0 = n0 + ob * BOXC + half * NV;
+        uint32_t v[NV];
+        if (NV == 32) tmem_ld_32x32(tsrc + ob * BOXC + half * NV, reinterpret_cast<uint32_t(&)[32]>(v));
+        else tmem_ld_32x16(tsrc + ob * BOXC + half * NV, reinterpret_cast<uint32_t(&)[16]>(v));
+        float4 b4[NV / 4];
+#pragma unroll
+        for (int i = 0; i < NV / 4; ++i) {
+            b4[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (p.bias != nullptr && col0 + 4 * i < p.N) b4[i] = __ldg(reinterpret_cast<const float4*>(p.bias + col0 + 4 * i));
+        }
+        if (issuer) bulk_wait_read<1>();                 // the store that used this slot two boxes ago has read it
+        named_bar_sync(1, EPI_THREADS);
         tmem_ld_wait();
-        float4* s4 = reinterpret_cast<float4*>(stg + lane * EPI_PITCH);
+        if (ob == nbox - 1) release();
+        float f[NV];
 #pragma unroll
-        for (int j = 0; j < 4; ++j)
-            s4[j] = make_float4(__uint_as_float(v[4 * j]), __uint_as_float(v[4 * j + 1]), __uint_as_float(v[4 * j + 2]), __uint_as_float(v[4 * j + 3]));
-        if (c + 2 < nsub) tmem_ld_32x16(tsrc + (c + 2) * 16, v);       // in flight while this sub-chunk is stored
-        else release();                                                // accumulator fully read: hand it back
-        __syncwarp();
-        const int col = n0 + c * 16 + c4;
-        const bool col_ok = col < p.N;                                 // N % 4 == 0
-        float4 b4 = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (p.bias != nullptr && col_ok) b4 = __ldg(reinterpret_cast<const float4*>(p.bias + col));
-        float4 a[4];
-#pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            a[i] = *reinterpret_cast<const float4*>(stg + (i * 8 + sub_r) * EPI_PITCH + c4);
-            a[i].x += b4.x; a[i].y += b4.y; a[i].z += b4.z; a[i].w += b4.w;
+        for (int i = 0; i < NV / 4; ++i) {
+            f[4 * i] = __uint_as_float(v[4 * i]) + b4[i].x; f[4 * i + 1] = __uint_as_float(v[4 * i + 1]) + b4[i].y;
+            f[4 * i + 2] = __uint_as_float(v[4 * i + 2]) + b4[i].z; f[4 * i + 3] = __uint_as_float(v[4 * i + 3]) + b4[i].w;
         }
+        if (EPI == EPI_BIAS_ACT_BF16) {
+#pragma unroll
+            for (int i = 0; i < NV; ++i) f[i] = apply_act<ACT>(f[i]);
+        }
+        uint8_t* rowp = slot + r * 128;
 #pragma unroll
         for (int i = 0; i < 4; ++i) {
-            const int row = row_base + i * 8 + sub_r;
-            if (row >= p.M || !col_ok) continue;
-            if (EPI == EPI_BIAS_RES_F32) {
-                // x += acc + bias: one fire-and-forget vector reduction per 16 bytes (a load-add-store
-                // variant measured 65.9 us against 43.6 us on the out-proj shape)
-                red_add_v4(reinterpret_cast<float*>(p.out) + (size_t)row * p.ldc + col, a[i]);
-            } else if (EPI == EPI_F32) {
-                *reinterpret_cast<float4*>(reinterpret_cast<float*>(p.out) + (size_t)row * p.ldc + col) = a[i];
+            uint4 c;
+            if (OUT_F32) {
+                c = make_uint4(__float_as_uint(f[4 * i]), __float_as_uint(f[4 * i + 1]), __float_as_uint(f[4 * i + 2]), __float_as_uint(f[4 * i + 3]));
             } else {
-                if (EPI == EPI_BIAS_ACT_BF16) {
-                    a[i].x = apply_act<ACT>(a[i].x); a[i].y = apply_act<ACT>(a[i].y);
-                    a[i].z = apply_act<ACT>(a[i].z); a[i].w = apply_act<ACT>(a[i].w);
-                }
-                *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(p.out) + (size_t)row * p.ldc + col) =
-                    pack4_bf16(a[i].x, a[i].y, a[i].z, a[i].w);
+                const uint2 lo = pack4_bf16(f[8 * i], f[8 * i + 1], f[8 * i + 2], f[8 * i + 3]);
+                const uint2 hi = pack4_bf16(f[8 * i + 4], f[8 * i + 5], f[8 * i + 6], f[8 * i + 7]);
+                c = make_uint4(lo.x, lo.y, hi.x, hi.y);
             }
+            *reinterpret_cast<uint4*>(rowp + (((half * 4 + i) ^ (r & 7)) << 4)) = c;
         }
-        __syncwarp();
+        fence_proxy_async();                             // generic-proxy writes -> visible to the TMA (async proxy)
+        named_bar_sync(2, EPI_THREADS);
+        if (issuer) {
+            if (EPI == EPI_BIAS_RES_F32) tma_reduce_add_2d(tmC, slot, n0 + ob * BOXC, m0);
+            else tma_store_2d(tmC, slot, n0 + ob * BOXC, m0);
+            bulk_commit();
+        }
     }
 }
 
 template <int BN, int EPI, int ACT>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
-gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, GemmParams p) {
+gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+               const __grid_constant__ CUtensorMap tmC, GemmParams p) {
     using Cfg = GemmCfg<BN>;
     constexpr int STAGES = Cfg::STAGES;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
-    float* epi_stage = reinterpret_cast<float*>(smem + STAGES * Cfg::STAGE_BYTES);
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * Cfg::STAGE_BYTES + EPI_WARPS * EPI_STAGE_WORDS * 4);
+    uint8_t* epi_slots = smem + STAGES * Cfg::STAGE_BYTES;    // 2 x 16 KB output boxes, 1024-byte aligned
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * Cfg::STAGE_BYTES + 2 * 16384);
     uint64_t* full = bars;                  // [STAGES]  TMA -> MMA
     uint64_t* empty = bars + STAGES;        // [STAGES]  MMA -> TMA
     uint64_t* acc_full = bars + 2 * STAGES; // [2]       MMA -> epilogue
@@ -144,6 +162,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmA);
         tma_prefetch_desc(&tmB);
+        tma_prefetch_desc(&tmC);
         for (int s = 0; s < STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
         for (int a = 0; a < 2; ++a) { mbar_init(&acc_full[a], 1); mbar_init(&acc_empty[a], EPI_WARPS); }
         fence_mbar_init();
@@ -195,19 +214,21 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     } else {
         const int q = warp & 3;                       // TMEM lane quarter this warp may read
         const int half = (warp - 2) >> 2;             // which 16-column sub-chunks (even / odd) this warp stores
-        float* stg = epi_stage + (warp - 2) * EPI_STAGE_WORDS;
-        int it = 0; bool ok = true;
+        const bool issuer = threadIdx.x == 64;         // first epilogue thread issues the TMA stores
+        int it = 0, box_seq = 0; bool ok = true;
         for (int t = blockIdx.x; t < tiles && ok; t += gridDim.x, ++it) {
             const int m0 = (t / tiles_n) * BM, n0 = (t % tiles_n) * BN;
             const int as = it & 1; const uint32_t aph = (it >> 1) & 1;
             if (!(ok = mbar_wait(&acc_full[as], aph, p.status, 4))) break;
             tc_fence_after();
-            epilogue_tile<BN, EPI, ACT>(p, stg, half, lane, tmem_base + ((uint32_t)(q * 32) << 16) + as * BN, m0 + q * 32, n0, [&] {
+            epilogue_tile<BN, EPI, ACT>(p, &tmC, epi_slots, box_seq, q, half, lane, issuer,
+                                        tmem_base + ((uint32_t)(q * 32) << 16) + as * BN, m0, n0, [&] {
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&acc_empty[as]);
             });
         }
+        if (issuer) bulk_wait<0>();                    // every output box has left shared memory and is written
     }
     tc_fence_before();
     __syncthreads();
@@ -226,18 +247,19 @@ template <int BN> struct Gemm2Cfg {
     static constexpr int B_BYTES = (BN / 2) * BK * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
     static constexpr int TMEM_COLS = 2 * BN;
-    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + EPI_WARPS * EPI_STAGE_WORDS * 4 + 256 + 1024;
+    static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 2 * 16384 + 256 + 1024;
 };
 
 template <int BN, int EPI, int ACT>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
-gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, GemmParams p) {
+gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                const __grid_constant__ CUtensorMap tmC, GemmParams p) {
     using Cfg = Gemm2Cfg<BN>;
     constexpr int STAGES = Cfg::STAGES;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
-    float* epi_stage = reinterpret_cast<float*>(smem + STAGES * Cfg::STAGE_BYTES);
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * Cfg::STAGE_BYTES + EPI_WARPS * EPI_STAGE_WORDS * 4);
+    uint8_t* epi_slots = smem + STAGES * Cfg::STAGE_BYTES;    // 2 x 16 KB output boxes, 1024-byte aligned
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * Cfg::STAGE_BYTES + 2 * 16384);
     uint64_t* full = bars;                  // [STAGES]  used in the leader only
     uint64_t* empty = bars + STAGES;        // [STAGES]  one per CTA, signalled by the leader's multicast commit
     uint64_t* acc_full = bars + 2 * STAGES; // [2]       one per CTA, multicast commit
@@ -254,6 +276,7 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmA);
         tma_prefetch_desc(&tmB);
+        tma_prefetch_desc(&tmC);
         for (int s = 0; s < STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
         for (int a = 0; a < 2; ++a) { mbar_init(&acc_full[a], 1); mbar_init(&acc_empty[a], 2 * EPI_WARPS); }
         fence_mbar_init();
@@ -304,20 +327,22 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     } else {
         const int q = warp & 3;
         const int half = (warp - 2) >> 2;
-        float* stg = epi_stage + (warp - 2) * EPI_STAGE_WORDS;
+        const bool issuer = threadIdx.x == 64;
         const uint32_t leader_acc_empty0 = mapa_u32(smem_u32(&acc_empty[0]), 0);
-        int it = 0; bool ok = true;
+        int it = 0, box_seq = 0; bool ok = true;
         for (int t = pair; t < tiles && ok; t += npairs, ++it) {
             const int m0 = (t / tiles_n) * 2 * BM + (int)rank * BM, n0 = (t % tiles_n) * BN;
             const int as = it & 1; const uint32_t aph = (it >> 1) & 1;
             if (!(ok = mbar_wait(&acc_full[as], aph, p.status, 24))) break;
             tc_fence_after();
-            epilogue_tile<BN, EPI, ACT>(p, stg, half, lane, tmem_base + ((uint32_t)(q * 32) << 16) + as * BN, m0 + q * 32, n0, [&] {
+            epilogue_tile<BN, EPI, ACT>(p, &tmC, epi_slots, box_seq, q, half, lane, issuer,
+                                        tmem_base + ((uint32_t)(q * 32) << 16) + as * BN, m0, n0, [&] {
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive_cluster(leader_acc_empty0 + as * 8);
             });
         }
+        if (issuer) bulk_wait<0>();
     }
     tc_fence_before();
     cluster_sync_all();                      // neither CTA may exit (or free TMEM) while its partner can still touch it
@@ -333,6 +358,12 @@ static std::once_flag g_encode_once;
 
 int make_tmap_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t row_pitch_bytes,
                  uint32_t box_rows, bool fp16) {
+    return make_tmap_2d_ex(out, base, rows, cols, row_pitch_bytes, box_rows, fp16 ? 1 : 0);
+}
+
+// dtype: 0 bf16, 1 fp16, 2 fp32.  The box is always 128 bytes wide (64 or 32 elements) with SWIZZLE_128B.
+int make_tmap_2d_ex(CUtensorMap* out, const void* base, uint64_t rows, uint64_t cols, uint64_t row_pitch_bytes,
+                    uint32_t box_rows, int dtype) {
     std::call_once(g_encode_once, [] {
         void* fn = nullptr;
         cudaDriverEntryPointQueryResult q;
@@ -345,49 +376,50 @@ int make_tmap_2d(CUtensorMap* out, const void* base, uint64_t rows, uint64_t col
         return fail(B200_EINVAL, "TMA operands need 16-byte aligned base and row pitch");
     cuuint64_t dims[2] = {cols, rows};
     cuuint64_t strides[1] = {row_pitch_bytes};
-    cuuint32_t box[2] = {64, box_rows};
+    cuuint32_t box[2] = {dtype == 2 ? 32u : 64u, box_rows};
     cuuint32_t estr[2] = {1, 1};
-    CUresult r = g_encode(out, fp16 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
+    const CUtensorMapDataType dt = dtype == 2 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : dtype == 1 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT16 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16;
+    CUresult r = g_encode(out, dt, 2,
                           const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                           CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return fail(B200_ECUDA, "cuTensorMapEncodeTiled failed with CUresult " + std::to_string((int)r));
     return B200_OK;
 }
 
-template <int BN, int EPI, int ACT> static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, cudaStream_t st) {
+template <int BN, int EPI, int ACT> static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const GemmParams& p, cudaStream_t st) {
     using Cfg = GemmCfg<BN>;
     B200_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<BN, EPI, ACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
     const int tiles = ((p.M + BM - 1) / BM) * ((p.N + BN - 1) / BN);
     const int grid = tiles < kNumSMs ? tiles : kNumSMs;
-    gemm_tc_kernel<BN, EPI, ACT><<<grid, GEMM_THREADS, Cfg::SMEM_BYTES, st>>>(ta, tb, p);
+    gemm_tc_kernel<BN, EPI, ACT><<<grid, GEMM_THREADS, Cfg::SMEM_BYTES, st>>>(ta, tb, tc, p);
     B200_CUDA_OK(cudaGetLastError());
     return B200_OK;
 }
-template <int BN, int EPI, int ACT> static int launch_gemm2(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, cudaStream_t st) {
+template <int BN, int EPI, int ACT> static int launch_gemm2(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const GemmParams& p, cudaStream_t st) {
     using Cfg = Gemm2Cfg<BN>;
     B200_CUDA_OK(cudaFuncSetAttribute(gemm_tc2_kernel<BN, EPI, ACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
     const int tiles = ((p.M + 2 * BM - 1) / (2 * BM)) * ((p.N + BN - 1) / BN);
     const int pairs = tiles < kNumSMs / 2 ? tiles : kNumSMs / 2;
-    gemm_tc2_kernel<BN, EPI, ACT><<<2 * pairs, GEMM_THREADS, Cfg::SMEM_BYTES, st>>>(ta, tb, p);   // cluster dims are compiled in
+    gemm_tc2_kernel<BN, EPI, ACT><<<2 * pairs, GEMM_THREADS, Cfg::SMEM_BYTES, st>>>(ta, tb, tc, p);   // cluster dims are compiled in
     B200_CUDA_OK(cudaGetLastError());
     return B200_OK;
 }
-static int dispatch_gemm2(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, cudaStream_t st) {
+static int dispatch_gemm2(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const GemmParams& p, cudaStream_t st) {
     switch (p.epi) {
-        case EPI_F32: return launch_gemm2<256, EPI_F32, 0>(ta, tb, p, st);
-        case EPI_BIAS_BF16: return launch_gemm2<256, EPI_BIAS_BF16, 0>(ta, tb, p, st);
-        case EPI_BIAS_RES_F32: return launch_gemm2<256, EPI_BIAS_RES_F32, 0>(ta, tb, p, st);
-        default: return p.act == ACT_QUICK_GELU ? launch_gemm2<256, EPI_BIAS_ACT_BF16, ACT_QUICK_GELU>(ta, tb, p, st)
-                                                : launch_gemm2<256, EPI_BIAS_ACT_BF16, ACT_GELU>(ta, tb, p, st);
+        case EPI_F32: return launch_gemm2<256, EPI_F32, 0>(ta, tb, tc, p, st);
+        case EPI_BIAS_BF16: return launch_gemm2<256, EPI_BIAS_BF16, 0>(ta, tb, tc, p, st);
+        case EPI_BIAS_RES_F32: return launch_gemm2<256, EPI_BIAS_RES_F32, 0>(ta, tb, tc, p, st);
+        default: return p.act == ACT_QUICK_GELU ? launch_gemm2<256, EPI_BIAS_ACT_BF16, ACT_QUICK_GELU>(ta, tb, tc, p, st)
+                                                : launch_gemm2<256, EPI_BIAS_ACT_BF16, ACT_GELU>(ta, tb, tc, p, st);
     }
 }
-template <int BN> static int dispatch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const GemmParams& p, cudaStream_t st) {
+template <int BN> static int dispatch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const GemmParams& p, cudaStream_t st) {
     switch (p.epi) {
-        case EPI_F32: return launch_gemm<BN, EPI_F32, 0>(ta, tb, p, st);
-        case EPI_BIAS_BF16: return launch_gemm<BN, EPI_BIAS_BF16, 0>(ta, tb, p, st);
-        case EPI_BIAS_RES_F32: return launch_gemm<BN, EPI_BIAS_RES_F32, 0>(ta, tb, p, st);
-        default: return p.act == ACT_QUICK_GELU ? launch_gemm<BN, EPI_BIAS_ACT_BF16, ACT_QUICK_GELU>(ta, tb, p, st)
-                                                : launch_gemm<BN, EPI_BIAS_ACT_BF16, ACT_GELU>(ta, tb, p, st);
+        case EPI_F32: return launch_gemm<BN, EPI_F32, 0>(ta, tb, tc, p, st);
+        case EPI_BIAS_BF16: return launch_gemm<BN, EPI_BIAS_BF16, 0>(ta, tb, tc, p, st);
+        case EPI_BIAS_RES_F32: return launch_gemm<BN, EPI_BIAS_RES_F32, 0>(ta, tb, tc, p, st);
+        default: return p.act == ACT_QUICK_GELU ? launch_gemm<BN, EPI_BIAS_ACT_BF16, ACT_QUICK_GELU>(ta, tb, tc, p, st)
+                                                : launch_gemm<BN, EPI_BIAS_ACT_BF16, ACT_GELU>(ta, tb, tc, p, st);
     }
 }
 
@@ -410,23 +442,27 @@ int gemm_bf16_tc(const void* A, int lda, const void* W, int ldw, int M, int N, i
         if (c192 < c256 && c192 <= c128) bn = 192;
         else if (c128 < c256 && c128 < c192) bn = 128;
     }
-    CUtensorMap ta, tb;
+    CUtensorMap ta, tb, tc;
+    const bool out_f32 = epi == EPI_F32 || epi == EPI_BIAS_RES_F32;
+    int rcc = make_tmap_2d_ex(&tc, out, M, N, (uint64_t)ldc * (out_f32 ? 4 : 2), BM, out_f32 ? 2 : 0);   // 128-row x 128-byte output boxes
+    if (rcc) return rcc;
     static const int force = [] { const char* e = getenv("B200_GEMM_PAIR"); return e ? atoi(e) : -1; }();   // -1 auto, 0 never, 1 always
-    const bool pair = force == 1 || (force != 0 && false);
+    // measured on B200 (M = 25,600): the CTA pair wins on every encoder shape except the small out-proj (N = K = 768)
+    const bool pair = force == 1 || (force != 0 && M >= 2048 && N >= 256 && !(N <= 768 && K <= 768));
     if (pair) {
         GemmParams p2{M, N, K, bias, out, ldc, epi, act, status};
         int rc2 = make_tmap_2d(&ta, A, M, K, (uint64_t)lda * 2, BM, false);
         if (rc2) return rc2;
         rc2 = make_tmap_2d(&tb, W, N, K, (uint64_t)ldw * 2, 128, false);      // each CTA loads half of the 256-wide W tile
         if (rc2) return rc2;
-        return dispatch_gemm2(ta, tb, p2, st);
+        return dispatch_gemm2(ta, tb, tc, p2, st);
     }
     int rc = make_tmap_2d(&ta, A, M, K, (uint64_t)lda * 2, BM, false);
     if (rc) return rc;
     rc = make_tmap_2d(&tb, W, N, K, (uint64_t)ldw * 2, bn, false);
     if (rc) return rc;
     GemmParams p{M, N, K, bias, out, ldc, epi, act, status};
-    return bn == 128 ? dispatch_gemm<128>(ta, tb, p, st) : bn == 192 ? dispatch_gemm<192>(ta, tb, p, st) : dispatch_gemm<256>(ta, tb, p, st);
+    return bn == 128 ? dispatch_gemm<128>(ta, tb, tc, p, st) : bn == 192 ? dispatch_gemm<192>(ta, tb, tc, p, st) : dispatch_gemm<256>(ta, tb, tc, p, st);
 }
 
 }  // namespace b200

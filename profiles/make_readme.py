@@ -1,0 +1,60 @@
+"""Writes profiles/README.md from the captured JSON lines (run after capture.sh + summarise.py)."""
+import json
+from pathlib import Path
+
+P = Path(__file__).resolve().parent
+paths = [json.loads(l) for l in (P / "paths_r1.jsonl").read_text().splitlines() if l.strip().startswith("{")]
+b = json.loads((P / "bench_r1.json").read_text())
+ref = json.loads((P / "bench_r1_reference.json").read_text())
+L = []
+L.append("# profiles — round 1 (B200, sm_100a, driver 580, CUDA 12.9)\n")
+L.append("Everything here was produced by `profiles/capture.sh` on one B200 (`gpurun`), summarised with `profiles/summarise.py`, and this file by `profiles/make_readme.py`.\n")
+L.append("| file | what |\n|---|---|")
+L.append("| `bench_r1.json` / `bench_r1_reference.json` | `python bench.py` (default flags) and `--impl reference` lines |")
+L.append("| `bench_r1_n2.json`, `bench_r1_n8.json`, `search_c5_n8.json` | 2- and 8-GPU runs (torchrun, NCCL): headline bench and the C5 sharded search (10 M x 512 gallery, Q = 4096, k = 100) |")
+L.append("| `paths_r1.jsonl` | `bench_paths.py` preprocess / search / classify / models / gemm lines |")
+L.append("| `launches_r1.csv` | ncu `gpu__time_duration.sum` for every launch of one bench step (cold cache, serialised: compare shares) |")
+L.append("| `step_r1_ncu.csv` | `--set full` metrics of the per-layer kernels (GEMM shapes, attention, LayerNorm) |")
+L.append("| `k1_resize_r1_ncu.csv`, `search_q1_r1_ncu.csv`, `search_q4096_r1_ncu.csv` | same for K1 (640x480 -> 224) and K10/K12 |")
+L.append("| `gemm_traffic_r1.json` | dram bytes per GEMM launch (feeds `roofline.traffic` in bench.py) |")
+L.append("| `pytest_gpu.txt` | tail of `pytest -m gpu` on the same box |\n")
+r = b["roofline"]
+L.append("## Headline (`bench_r1.json`)\n")
+L.append(f"* value **{b['value']:.0f} images/s** (device-resident batch), e2e **{b['e2e']['value']:.0f} images/s** (pinned host in, host out), "
+         f"{b['ms_per_step']:.2f} ms per 512-image step, {b['gpu_launches']} kernel launches in the timed region.")
+L.append(f"* dominant kernel (tcgen05 GEMM): {r['achieved']:.0f} TFLOP/s = **{r['frac']:.3f} of the measured sustained bf16 peak** ({r['peak']} TFLOP/s); "
+         f"whole step = {r['end_to_end_frac_of_tensor_peak']:.3f} of that peak; CUDA-event share of step {r['share_of_step']}; "
+         f"dram traffic per launch (ncu) {r['traffic'] / 1e6:.0f} MB.")
+L.append(f"* CPU arm (`--impl reference`, oracle port, {ref['cpu_baseline']['cores']} host threads): {ref['value']:.0f} images/s; "
+         f"in-run CPU baseline {b['cpu_baseline']['value']:.0f} images/s.  Clocks during the timed region: {b['clocks']}.")
+L.append("* ncu launch list shares of one step: GEMM 0.755, attention 0.132, LayerNorm 0.094, preprocess 0.013 — agrees with the CUDA-event shares.\n")
+L.append("## Per-shape GEMM (`paths_r1.jsonl`, M = 25,600 token rows)\n\n| shape | N | K | epilogue | us | TFLOP/s | of sustained peak |\n|---|---|---|---|---|---|---|")
+for d in paths:
+    if d.get("path") == "gemm_tc_kernel":
+        L.append(f"| {d['shape']} | {d['N']} | {d['K']} | {d['epilogue']} | {d['us']:.1f} | {d['tflops']:.0f} | {d['frac_sustained']:.3f} |")
+L.append("\nHistory of this kernel in round 1 (QKV shape): 125 us (first correct version) -> 88 us (vectorised smem transpose, 8 epilogue warps) -> "
+         "78 us (epilogue through TMA stores) -> 73 us (CTA pair, `cta_group::2`).  A K sweep at N = 2304 showed a 62 us floor set by the stores "
+         "(32-byte pieces through the LSU); handing full 128-byte boxes to the TMA engine removed it.  The out-proj GEMM (N = K = 768) stays bound by the "
+         "rate of the fp32 residual update (tensor reduce-add, 19.7 M elements per launch).\n")
+L.append("## K1 preprocess against the HBM roofline\n\n| source | batch | ms | images/s | GB/s (algorithmic) | of 6,454 GB/s |\n|---|---|---|---|---|---|")
+for d in paths:
+    if d.get("path") == "K1 preprocess":
+        L.append(f"| {d['src']} | {d['batch']} | {d['ms']:.3f} | {d['images_per_s']:.0f} | {d['roofline']['achieved']:.0f} | {d['roofline']['frac']:.3f} |")
+L.append("\nIdentity sizes stream at 0.58 of peak. Down-scaling is bound by the integer pipes, not by HBM (ncu: ALU pipe 64 % active, DRAM 13 %): "
+         "Pillow-exact arithmetic needs one 32-bit MAC plus one byte extraction per (tap, channel) — 5.7 MACs per source byte at 640x480 -> 224.\n")
+L.append("## K10 + K12 gallery search (N = 1.25 M x 512 fp16 on one GPU, k = 100)\n\n| Q | ms | queries/s | TFLOP/s | of burst bf16 peak | GB/s | of HBM peak |\n|---|---|---|---|---|---|---|")
+for d in paths:
+    if d.get("path", "").startswith("K10"):
+        q = d["roofline"]
+        L.append(f"| {d['Q']} | {d['ms']:.3f} | {d['queries_per_s']:.0f} | {q['tensor_tflops']:.1f} | {q['tensor_frac']:.3f} | {q['hbm_gbs']:.0f} | {q['hbm_frac']:.3f} |")
+L.append("\nSmall Q is the HBM-bound regime (gallery read once), large Q the tensor-bound one. On 8 GPUs (`search_c5_n8.json`) the C5 case "
+         "(10 M rows, Q = 4096) takes 6.8 ms including the NCCL all-gather and the merge. What is left on the table: every gallery split warms its own "
+         "per-row threshold and the warp-cooperative radix-select compactions stall the epilogue in bursts; see DESIGN.md §7.\n")
+L.append("## Other models / classify\n")
+for d in paths:
+    if d.get("path") == "embed (K1..K9)":
+        L.append(f"* {d['model']} batch {d['batch']}: {d['images_per_s']:.0f} images/s ({d['ms']:.2f} ms), {d['frac_of_tensor_peak_sustained']:.3f} of sustained tensor peak at {d['gflop_per_image']:.1f} GFLOP/image")
+    if d.get("path", "").startswith("K11"):
+        L.append(f"* classify 256 x 1000 labels, k=5: {d['us']:.0f} us per batch")
+(P / "README.md").write_text("\n".join(L) + "\n")
+print("\n".join(L)[:1500])

@@ -149,6 +149,13 @@ class B200ClipBackend(BaseClipBackend):
         except Exception as e:  # noqa: BLE001
             raise InferenceError(f"Batch image encoding failed: {e}") from e
 
+    def embed_stream(self, batches):
+        """Pipelined embed_packed over an iterable of (pinned_u8, total_bytes, offsets, hw): the upload of the next batch
+        overlaps the encoding of the current one; yields one float32 [B, D] array per batch, in order."""
+        self._ensure_initialized()
+        with self._lock:
+            yield from self._engine.embed_stream(batches, self._mode)
+
     def image_to_vector(self, image_bytes: bytes) -> np.ndarray:
         self._ensure_initialized()
         if not image_bytes:

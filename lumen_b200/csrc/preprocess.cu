@@ -33,7 +33,7 @@ struct ImgDesc {
     const int* bounds_h; const int* kk_h;   // per output x of the resized width: (xmin, count), coefficients
     const int* bounds_v; const int* kk_v;
     int identity;                      // resized size == source size: pure crop + convert
-    int pad_;
+    int pad_[3];                       // sizeof == 80: pulled to the device as five 16-byte words
 };
 
 struct PreParams {
@@ -262,6 +262,13 @@ __global__ void __launch_bounds__(256) preprocess_kernel(PreParams p) {
     }
 }
 
+static_assert(sizeof(ImgDesc) == 80, "ImgDesc is pulled as five 16-byte words");
+// Copies the batch's descriptors from pinned host memory (read through the unified address space) to the device.
+__global__ void pull_desc_kernel(const uint4* __restrict__ host, uint4* __restrict__ dev, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) dev[i] = host[i];
+}
+
 // Identity-size images (resized size == source size, e.g. 224x224 sources for a 224 model): crop + convert only.
 // Persistent CTAs walk (image, row-tile) items; the next item's rows are fetched with cp.async while the current
 // ones are converted, so the kernel streams at memory speed instead of paying one load latency per tile.
@@ -366,13 +373,14 @@ static int build_axis_table(int in_size, int out_size, AxisTable* t, cudaStream_
 struct PreprocessState {
     std::map<std::pair<int, int>, AxisTable> tables;
     float* d_lut = nullptr;
-    ImgDesc* d_desc = nullptr; ImgDesc* h_desc = nullptr; int desc_cap = 0;
-    cudaEvent_t desc_free = nullptr;
+    // descriptors: filled in one of four pinned host buffers, pulled into d_desc by a small kernel (zero-copy
+    // reads).  No copy-engine transfer, so a caller's large uploads on another stream cannot delay this call.
+    ImgDesc* d_desc = nullptr; ImgDesc* h_desc[4] = {nullptr, nullptr, nullptr, nullptr}; int desc_cap = 0; int desc_slot = 0;
+    cudaEvent_t desc_free[4] = {nullptr, nullptr, nullptr, nullptr};
     ~PreprocessState() {
         for (auto& kv : tables) { cudaFree(kv.second.d_bounds); cudaFree(kv.second.d_kk); }
         cudaFree(d_lut); cudaFree(d_desc);
-        if (h_desc) cudaFreeHost(h_desc);
-        if (desc_free) cudaEventDestroy(desc_free);
+        for (int i = 0; i < 4; ++i) { if (h_desc[i]) cudaFreeHost(h_desc[i]); if (desc_free[i]) cudaEventDestroy(desc_free[i]); }
     }
 };
 
@@ -383,7 +391,7 @@ PreprocessState* preprocess_state_create(const float* mean, const float* stdv, i
         for (int v = 0; v < 256; ++v) lut[c * 256 + v] = ((float)v / 255.0f - mean[c]) / stdv[c];   // fp32, reference order
     cudaError_t e = cudaMalloc(&s->d_lut, 768 * sizeof(float));
     if (e == cudaSuccess) e = cudaMemcpy(s->d_lut, lut.data(), 768 * sizeof(float), cudaMemcpyHostToDevice);
-    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&s->desc_free, cudaEventDisableTiming);
+    for (int i = 0; i < 4 && e == cudaSuccess; ++i) e = cudaEventCreateWithFlags(&s->desc_free[i], cudaEventDisableTiming);
     if (e != cudaSuccess) { *rc = fail(B200_ECUDA, std::string("preprocess state: ") + cudaGetErrorString(e)); delete s; return nullptr; }
     *rc = B200_OK;
     return s;
@@ -424,14 +432,17 @@ int preprocess_run(PreprocessState* s, const uint8_t* src_dev, const long long* 
     B200_REQUIRE(layout == 0 || (layout == 1 && P > 0 && S % P == 0 && kpad >= 3 * P * P && P % 2 == 0),
                  "preprocess: bad patch-major geometry");
     if (B > s->desc_cap) {
-        if (s->d_desc) { cudaFree(s->d_desc); cudaFreeHost(s->h_desc); s->d_desc = nullptr; s->h_desc = nullptr; }
+        B200_CUDA_OK(cudaStreamSynchronize(st));
+        cudaFree(s->d_desc); s->d_desc = nullptr;
+        for (int i = 0; i < 4; ++i) { if (s->h_desc[i]) cudaFreeHost(s->h_desc[i]); s->h_desc[i] = nullptr; }
         int cap = B < 512 ? 512 : B;
         B200_CUDA_OK(cudaMalloc(&s->d_desc, sizeof(ImgDesc) * cap));
-        B200_CUDA_OK(cudaMallocHost(&s->h_desc, sizeof(ImgDesc) * cap));
+        for (int i = 0; i < 4; ++i) B200_CUDA_OK(cudaMallocHost(&s->h_desc[i], sizeof(ImgDesc) * cap));
         s->desc_cap = cap;
-    } else {
-        B200_CUDA_OK(cudaEventSynchronize(s->desc_free));    // previous upload out of the pinned staging area
     }
+    s->desc_slot = (s->desc_slot + 1) & 3;
+    ImgDesc* hdesc = s->h_desc[s->desc_slot];
+    B200_CUDA_OK(cudaEventSynchronize(s->desc_free[s->desc_slot]));   // the call four back has pulled its descriptors
     const int inter_pitch = (S * 3 + 15) & ~15;
     double max_vscale = 1.0; int max_rowbytes = 0; bool any_resize = false; int max_ident_rowbytes = 0;
     for (int i = 0; i < B; ++i) {
@@ -444,8 +455,8 @@ int preprocess_run(PreprocessState* s, const uint8_t* src_dev, const long long* 
             top = (int)std::nearbyint((new_h - S) / 2.0);
             left = (int)std::nearbyint((new_w - S) / 2.0);
         }
-        ImgDesc& d = s->h_desc[i];
-        d.src_off = offsets[i]; d.h_in = h; d.w_in = w; d.top = top; d.left = left; d.pad_ = 0;
+        ImgDesc& d = hdesc[i];
+        d.src_off = offsets[i]; d.h_in = h; d.w_in = w; d.top = top; d.left = left; d.pad_[0] = d.pad_[1] = d.pad_[2] = 0;
         d.identity = (new_h == h && new_w == w) ? 1 : 0;
         d.bounds_h = d.kk_h = d.bounds_v = d.kk_v = nullptr; d.ksize_h = d.ksize_v = 0;
         if (!d.identity) {
@@ -460,8 +471,9 @@ int preprocess_run(PreprocessState* s, const uint8_t* src_dev, const long long* 
         } else if (w * 3 > max_ident_rowbytes) max_ident_rowbytes = w * 3;
     }
     // Tile height: as many output rows as keep the uint8 intermediate within ~64 KB (whole tile within 200 KB).
-    B200_CUDA_OK(cudaMemcpyAsync(s->d_desc, s->h_desc, sizeof(ImgDesc) * B, cudaMemcpyHostToDevice, st));
-    B200_CUDA_OK(cudaEventRecord(s->desc_free, st));
+    pull_desc_kernel<<<(B * 5 + 255) / 256, 256, 0, st>>>(reinterpret_cast<const uint4*>(hdesc), reinterpret_cast<uint4*>(s->d_desc), B * 5);
+    B200_CUDA_OK(cudaGetLastError());
+    B200_CUDA_OK(cudaEventRecord(s->desc_free[s->desc_slot], st));
     int rc = B200_OK;
     if (max_ident_rowbytes > 0) {
         // identity images: TR rows per item, one staging buffer per item (double buffered)

@@ -177,6 +177,81 @@ class Engine:
                                                 C.c_void_p(self._pin_out.data_ptr()), self._stream()))
         return self._pin_out[:B * self.embed_dim].view(B, self.embed_dim).numpy().copy()
 
+    def embed_stream(self, batches, mode: int = MODE_SQUASH):
+        """Pipelined form of embed_packed_host for a stream of batches (serving / bulk indexing).
+
+        `batches` yields (pinned_u8 tensor, total_bytes, offsets, hw) in the pack_images layout.  The host->device
+        copy of batch i+1 runs on a side stream while batch i is preprocessed and encoded, results come back through
+        two pinned buffers; one numpy [B, D] array is yielded per batch, in order.  Every byte still crosses PCIe
+        inside the loop - only the waiting is overlapped.
+
+        Two details matter for the overlap: both streams are non-default (the legacy default stream serialises
+        against every other stream), and batch i is enqueued BEFORE the upload of batch i+1 - the copy engine serves
+        host->device transfers in submission order, so the small descriptor upload of a batch must not queue up
+        behind a big image upload that is still waiting for its buffer."""
+        torch = _torch()
+        dev = torch.device("cuda", self.device)
+        caller = torch.cuda.current_stream(dev)
+        compute = torch.cuda.Stream(device=dev)
+        copy = torch.cuda.Stream(device=dev)
+        compute.wait_stream(caller)
+        src = [None, None]; out = [None, None]; pin_out = [None, None]; meta = [None, None]
+        ready = [torch.cuda.Event(), torch.cuda.Event()]      # H2D of the slot finished
+        done = [torch.cuda.Event(), torch.cuda.Event()]       # D2H of the slot's result finished
+
+        def stage(i, item):
+            pinned, total, offsets, hw = item
+            s, need = i & 1, int(total)
+            if src[s] is None or src[s].numel() < need:
+                src[s] = torch.empty(int(need * 1.25) + 64, dtype=torch.uint8, device=dev)
+            with torch.cuda.stream(copy):
+                if i >= 2:
+                    # wait for the END of batch i-2 (its result download included), not just for its last read of the
+                    # slot: released any earlier, this big upload grabs the copy engine just before the next batch's
+                    # small descriptor upload becomes eligible and delays that batch's kernels by a whole transfer
+                    copy.wait_event(done[s])
+                src[s][:need].copy_(pinned[:need], non_blocking=True)
+                ready[s].record(copy)
+            meta[s] = (np.ascontiguousarray(offsets, np.int64), np.ascontiguousarray(hw, np.int32))
+
+        def launch(i):
+            s = i & 1
+            offsets, hw = meta[s]
+            B = int(len(offsets))
+            if out[s] is None or out[s].shape[0] < B:
+                out[s] = torch.empty((B, self.embed_dim), dtype=torch.float32, device=dev)
+                pin_out[s] = torch.empty((B, self.embed_dim), dtype=torch.float32, pin_memory=True)
+            with torch.cuda.stream(compute):
+                compute.wait_event(ready[s])
+                self.embed_u8(src[s], offsets, hw, mode, out=out[s][:B])
+                pin_out[s][:B].copy_(out[s][:B], non_blocking=True)
+                done[s].record(compute)
+            return B
+
+        it = iter(batches)
+        pending = []                                           # (index, B): launched, result not yet yielded
+        nxt = next(it, None)
+        i = 0
+        if nxt is not None:
+            stage(0, nxt)
+        while nxt is not None:
+            cur_i = i
+            nxt = next(it, None)
+            while pending and pending[0][0] <= cur_i - 2:      # this batch reuses the result buffers of batch cur_i - 2
+                pi, pB = pending.pop(0)
+                done[pi & 1].synchronize()
+                yield pin_out[pi & 1][:pB].numpy().copy()
+            pending.append((cur_i, launch(cur_i)))
+            if nxt is not None:
+                stage(cur_i + 1, nxt)                          # upload overlaps the encode of batch cur_i
+            i += 1
+        for pi, pB in pending:
+            done[pi & 1].synchronize()
+            yield pin_out[pi & 1][:pB].numpy().copy()
+        with torch.cuda.stream(compute):
+            self.sync()
+        caller.wait_stream(compute)
+
     # ------------------------------------------------------------------ classify / search
     def set_labels(self, labels: np.ndarray, slot: int = 0) -> None:
         a = np.ascontiguousarray(labels, dtype=np.float32)

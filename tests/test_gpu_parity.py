@@ -343,3 +343,27 @@ def test_encoder_exact_gelu_variant():
     quick = O.vit_encode(w, O.preprocess_batch(imgs, cfg["image_size"], 1), dict(cfg, activation="quick_gelu"))
     assert (emb * quick).sum(1).min() < (emb * ref).sum(1).min()     # the two activations are distinguishable
     eng.close()
+
+
+def test_embed_stream_matches_blocking_calls():
+    """Pipelined host-buffer path (upload of batch i+1 overlapping the encode of batch i): same vectors, same order."""
+    from lumen_b200 import VIT_CONFIGS, synthetic_weights
+    from lumen_b200.backend import B200ClipBackend, SyntheticResources
+    from lumen_b200.engine import pack_images
+    name = "ViT-tiny-test"; cfg = VIT_CONFIGS[name]
+    be = B200ClipBackend(SyntheticResources(model_name=name), device_preference="cuda:0", max_batch_size=16, weights=synthetic_weights(cfg, 0))
+    be.initialize()
+    rng = np.random.default_rng(31)
+    batches, want = [], []
+    for n in (5, 16, 1, 9, 12):
+        imgs = [rng.integers(0, 256, (rng.integers(40, 120), rng.integers(40, 120), 3), dtype=np.uint8) for _ in range(n)]
+        want.append(be.embed_arrays(imgs))
+        buf, off, hw, total = pack_images(imgs)
+        pinned = torch.from_numpy(buf[:total].copy()).pin_memory()
+        batches.append((pinned, total, off, hw))
+    got = list(be.embed_stream(iter(batches)))
+    assert len(got) == len(want)
+    for g, w in zip(got, want):
+        assert g.shape == w.shape and np.array_equal(g, w)
+    assert list(be.embed_stream(iter([]))) == []
+    be.close()

@@ -171,8 +171,7 @@ extern "C" int64_t b200clip_launch_count(b200clip_handle* h) { return h ? h->lau
 extern "C" int b200clip_profile(b200clip_handle* h, int32_t enable) {
     B200_REQUIRE(h != nullptr, "null handle");
     std::lock_guard<std::mutex> lk(h->mu);
-    h->prof = enable != 0;
-    h->prof_recs.clear(); h->ev_used = 0;
+    h->prof = enable != 0;          // records accumulate until b200clip_profile_read
     return B200_OK;
 }
 

@@ -28,8 +28,10 @@ __device__ __forceinline__ void ln_row(float4 (&v)[LN_MAX_V4], int nv, int d, fl
 __global__ void __launch_bounds__(256) layernorm_bf16_kernel(const float* __restrict__ x, long long row_stride,
                                                              const float* __restrict__ gamma, const float* __restrict__ beta,
                                                              __nv_bfloat16* __restrict__ out, int rows, int d, float eps) {
-    const int row = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
-    if (row >= rows) return;
+    // rows are walked from the end: the GEMM that just updated x finished with the last row blocks, so those are the
+    // lines most likely still in L2
+    const int row = rows - 1 - (blockIdx.x * 8 + (threadIdx.x >> 5)), lane = threadIdx.x & 31;
+    if (row < 0) return;
     const int nv = d >> 7;
     const float4* xr = reinterpret_cast<const float4*>(x + (size_t)row * row_stride * d);
     float4 v[LN_MAX_V4];

@@ -1,0 +1,17 @@
+import sys, torch
+sys.path.insert(0, ".")
+from lumen_b200.engine import Engine
+eng = Engine({}, device=0)
+g = torch.Generator(device="cuda").manual_seed(2)
+for B, S, heads in ((1, 64, 2), (1, 50, 2), (3, 50, 12), (1, 128, 1), (2, 197, 12), (1, 577, 16), (5, 17, 2), (4, 64, 4), (2, 129, 2), (300, 50, 12), (40, 197, 12)):
+    d = heads * 64
+    qkv = torch.randn(B * S, 3 * d, device="cuda", generator=g).to(torch.bfloat16)
+    try:
+        out = eng.attention(qkv, B, S, d, heads)
+        eng.sync()
+    except Exception as e:
+        print(B, S, heads, "ERROR", e); break
+    q, k, v = [t.view(B, S, heads, 64).transpose(1, 2) for t in qkv.float().split(d, dim=1)]
+    ref = (torch.softmax(q @ k.transpose(-1, -2) * 0.125, -1) @ v).transpose(1, 2).reshape(B * S, d)
+    err = (out.float() - ref).abs()
+    print(B, S, heads, "max err", err.max().item(), "mean", err.mean().item(), "nan", torch.isnan(out.float()).sum().item())

@@ -149,7 +149,10 @@ def test_layernorm_and_attention():
         out = eng.layernorm(x, gam, bet)
         ref = torch.nn.functional.layer_norm(x, (d,), gam, bet, 1e-5)
         torch.testing.assert_close(out.float(), ref, rtol=1e-2, atol=2e-2)
-    for B, S, heads in ((3, 50, 12), (2, 197, 12), (1, 577, 16), (5, 17, 2)):
+    # S <= 64 packs two heads per tcgen05 tile; S > 64 walks 128-key steps; 300 x 50 and 40 x 197 give each persistent CTA several items;
+    # odd head counts with S <= 64 take the mma.sync kernel
+    for B, S, heads in ((3, 50, 12), (2, 197, 12), (1, 577, 16), (5, 17, 2), (4, 64, 4), (2, 128, 2), (2, 129, 2), (3, 257, 16),
+                        (300, 50, 12), (40, 197, 12), (2, 50, 3), (1, 1, 2)):
         d = heads * 64
         qkv = torch.randn(B * S, 3 * d, device="cuda", generator=g).to(torch.bfloat16)
         out = eng.attention(qkv, B, S, d, heads)

@@ -11,7 +11,9 @@
 //             P = exp2(...)         four softmax warps, thread = query row = TMEM lane; P goes to shared memory as the
 //                                   K-major A operand of the second matmul (bf16, swizzled like a TMA tile)
 //             O_step = P V          UMMA 128x64x16 x8, B = V tile as loaded ([key][dim], dim contiguous) = MN-major
-//             O += alpha-rescaled   in registers of the softmax threads (64 fp32 per row)
+//             O accumulates in TMEM across the key steps.  The softmax reference maximum is only moved when a row's maximum
+//             grows by more than 2^8 (probabilities stay <= 256, exact in bf16/fp32 terms); then that warp rescales its
+//             32 O rows in place (tcgen05.ld -> multiply -> tcgen05.st).  After the first key step this is rare.
 // One persistent CTA per SM runs TWO such tiles at a time ("slots": own Q/K/V/P shared memory, own TMEM columns, own
 // softmax warpgroup), so the tensor core works on one slot while the other slot's softmax runs (the exp2 stream on the
 // SFUs is what bounds this kernel, not the MMAs).  warp 0 = TMA producer for both slots, warp 1 = MMA issuer for both,
@@ -77,53 +79,108 @@ __device__ __forceinline__ AttnItem attn_item(const AttnParams& p, int item) {
     return {rest / hgroups, (rest % hgroups) * p.pack, item % p.n_qt};
 }
 
-// One softmax step of one row: scores (TMEM) -> running max / sum, probabilities (bf16) into the row's P bytes.
-// MASKED = false: all 128 key columns are valid.  MASKED = true: only columns [c_lo, c_hi) inside 64-column chunks [ch0, ch1).
-template <bool MASKED>
-__device__ __forceinline__ void softmax_row(uint32_t t_s, uint8_t* p_row, int r, float sl2, int c_lo, int c_hi, int ch0, int ch1,
-                                            float& m, float& l, float& alpha) {
+// Bounded mbarrier wait with a suspend-time hint: the thread parks in hardware instead of spinning through the issue slots
+// the other slot's softmax warps need.
+__device__ __forceinline__ bool mbar_wait_parked(uint64_t* bar, uint32_t parity, DeviceStatus* st, int where) {
+#pragma unroll 1
+    for (uint32_t it = 0; it < (1u << 16); ++it) {
+        uint32_t ok;
+        asm volatile(
+            "{\n\t.reg .pred p;\n\t"
+            "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+            "selp.u32 %0, 1, 0, p;\n\t}"
+            : "=r"(ok) : "r"(smem_u32(bar)), "r"(parity), "r"(100000u) : "memory");
+        if (ok) return true;
+    }
+    if (st) { st->code = 1; st->where = where; }
+    return false;
+}
+// 32 registers per thread -> 32 consecutive fp32 columns of the thread's TMEM lane
+__device__ __forceinline__ void tmem_st_32x32(uint32_t taddr, const uint32_t (&v)[32]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
+        "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, "
+        "%17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31, %32};"
+        :: "r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]),
+           "r"(v[8]), "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]),
+           "r"(v[16]), "r"(v[17]), "r"(v[18]), "r"(v[19]), "r"(v[20]), "r"(v[21]), "r"(v[22]), "r"(v[23]),
+           "r"(v[24]), "r"(v[25]), "r"(v[26]), "r"(v[27]), "r"(v[28]), "r"(v[29]), "r"(v[30]), "r"(v[31])
+        : "memory");
+}
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
+
+// One softmax step of one row, in two halves.  Both walk the 32-column chunks [c0, c1) of the 128 score columns; only the first
+// `n_valid` columns counted from chunk c0 are real keys, the rest are forced to -inf (probability 0) before the common code runs.
+// The TMEM load of chunk c + 1 is in flight while chunk c is processed.  Loops are kept rolled (two chunk bodies each): the
+// kernel's two softmax warpgroups sit at different program counters and share the instruction cache.
+__device__ __forceinline__ void mask_tail(uint32_t (&v)[32], int lim) {     // keep columns [0, lim) of this chunk
+    if (lim < 32) {
+#pragma unroll
+        for (int j = 0; j < 32; ++j) if (j >= lim) v[j] = 0xff800000u;       // -inf
+    }
+}
+// row_max: new running maximum (scaled to the exp2 domain).
+__device__ __forceinline__ float row_max(uint32_t t_s, float sl2, int c0, int c1, int n_valid, float m) {
+    uint32_t va[32], vb[32];
     float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
-    for (int c = MASKED ? ch0 : 0; c < (MASKED ? ch1 : 2); ++c) {
-        uint32_t v[64];
-        tmem_ld_row64(t_s + c * 64, v);
+    tmem_ld_32x32(t_s + c0 * 32, va);
+#pragma unroll 1
+    for (int c = c0; c < c1; c += 2) {
+        tmem_ld_wait();
+        if (c + 1 < c1) tmem_ld_32x32(t_s + (c + 1) * 32, vb);
+        mask_tail(va, n_valid - (c - c0) * 32);
 #pragma unroll
-        for (int j = 0; j < 64; ++j) {
-            float x = __uint_as_float(v[j]);
-            if (MASKED) { const int col = c * 64 + j; x = (col >= c_lo && col < c_hi) ? x : -INFINITY; }
-            mx4[j & 3] = fmaxf(mx4[j & 3], x);
+        for (int j = 0; j < 32; ++j) mx4[j & 3] = fmaxf(mx4[j & 3], __uint_as_float(va[j]));
+        if (c + 1 < c1) {
+            tmem_ld_wait();
+            if (c + 2 < c1) tmem_ld_32x32(t_s + (c + 2) * 32, va);
+            mask_tail(vb, n_valid - (c + 1 - c0) * 32);
+#pragma unroll
+            for (int j = 0; j < 32; ++j) mx4[j & 3] = fmaxf(mx4[j & 3], __uint_as_float(vb[j]));
         }
     }
-    const float mx = fmaxf(m, fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3])) * sl2);
-    alpha = ex2_approx(m - mx);                    // 0 on the first step (m = -inf)
+    return fmaxf(m, fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3])) * sl2);
+}
+// 32 probabilities exp2(s * sl2 - mx) of chunk c as bf16 into the row's P bytes (the A operand of P V); adds them to s4.
+__device__ __forceinline__ void exp_chunk(const uint32_t (&v)[32], int c, uint8_t* p_row, int r, float sl2, float mx, float (&s4)[4]) {
+    uint8_t* blk = p_row + (c >> 1) * AT_TILE_BYTES;                // K-block of 64 keys
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        float e[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { e[j] = ex2_approx(fmaf(__uint_as_float(v[8 * i + j]), sl2, -mx)); s4[j & 3] += e[j]; }
+        uint4 w;
+        w.x = pack_bf16x2(e[0], e[1]); w.y = pack_bf16x2(e[2], e[3]); w.z = pack_bf16x2(e[4], e[5]); w.w = pack_bf16x2(e[6], e[7]);
+        *reinterpret_cast<uint4*>(blk + ((((c & 1) * 4 + i) ^ (r & 7)) << 4)) = w;
+    }
+}
+__device__ __forceinline__ float row_exp(uint32_t t_s, uint8_t* p_row, int r, float sl2, int c0, int c1, int n_valid, float mx) {
+    uint32_t va[32], vb[32];
     float s4[4] = {0.f, 0.f, 0.f, 0.f};
-    for (int c = MASKED ? ch0 : 0; c < (MASKED ? ch1 : 2); ++c) {
-        uint32_t v[64];
-        tmem_ld_row64(t_s + c * 64, v);
-        uint8_t* blk = p_row + c * AT_TILE_BYTES;  // K-block of 64 keys
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-            float e[8];
-#pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                e[j] = ex2_approx(fmaf(__uint_as_float(v[8 * i + j]), sl2, -mx));
-                if (MASKED) { const int col = c * 64 + 8 * i + j; e[j] = (col >= c_lo && col < c_hi) ? e[j] : 0.f; }
-                s4[j & 3] += e[j];
-            }
-            uint4 w;
-            w.x = pack_bf16x2(e[0], e[1]); w.y = pack_bf16x2(e[2], e[3]); w.z = pack_bf16x2(e[4], e[5]); w.w = pack_bf16x2(e[6], e[7]);
-            *reinterpret_cast<uint4*>(blk + ((i ^ (r & 7)) << 4)) = w;
+    tmem_ld_32x32(t_s + c0 * 32, va);
+#pragma unroll 1
+    for (int c = c0; c < c1; c += 2) {
+        tmem_ld_wait();
+        if (c + 1 < c1) tmem_ld_32x32(t_s + (c + 1) * 32, vb);
+        mask_tail(va, n_valid - (c - c0) * 32);
+        exp_chunk(va, c, p_row, r, sl2, mx, s4);
+        if (c + 1 < c1) {
+            tmem_ld_wait();
+            if (c + 2 < c1) tmem_ld_32x32(t_s + (c + 2) * 32, va);
+            mask_tail(vb, n_valid - (c + 1 - c0) * 32);
+            exp_chunk(vb, c + 1, p_row, r, sl2, mx, s4);
         }
     }
-    l = l * alpha + ((s4[0] + s4[1]) + (s4[2] + s4[3]));
-    m = mx;
+    return (s4[0] + s4[1]) + (s4[2] + s4[3]);
 }
 
+// 10 warps = 3 on two of the SM's four register files (16 K registers each): 168 registers per thread is the ceiling
 __global__ void __launch_bounds__(AT_THREADS, 1)
 attention_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, AttnParams p) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 2 * AT_SLOT_BYTES);
-    // per slot (stride 10): q_full, q_empty, kv_full[2], kv_empty[2], s_full, p_full, o_full, o_free
+    // per slot (stride 10): q_full, q_empty, kv_full[2], kv_empty[2], s_full, p_full, o_full (P V of a step done), o_free (per item)
     enum { Q_FULL = 0, Q_EMPTY = 1, KV_FULL = 2, KV_EMPTY = 4, S_FULL = 6, P_FULL = 7, O_FULL = 8, O_FREE = 9, NBAR = 10 };
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * NBAR);
 
@@ -187,38 +244,42 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, AttnParams p) {
         }
     } else if (warp == 1) {
         if (lane == 0) {
-            constexpr uint32_t idesc_s = attn_idesc(128, 128, 0), idesc_o = attn_idesc(128, 64, 1);
+            constexpr uint32_t idesc_o = attn_idesc(128, 64, 1);
             const int G0 = my_pairs * p.n_kt, G1 = (my_pairs - (odd_tail ? 1 : 0)) * p.n_kt;   // steps per slot
             bool ok = true;
+            // keys a step really holds, rounded up to the MMA's K granule (pack == 2 always runs the full tile)
+            auto keys16 = [&](int g) { const int left = p.S - (g % p.n_kt) * 128; return (p.pack == 2 || left >= 128) ? 128 : ((left + 15) & ~15); };
             // S = Q K^T of step g of a slot; the slot's score columns are free once P of step g - 1 was written
             auto issue_s = [&](int s, int g) -> bool {
                 uint64_t* b = bars + s * NBAR;
                 uint8_t* base = smem + s * AT_SLOT_BYTES;
                 const int kt = g % p.n_kt, st = g & 1;
-                if (kt == 0 && !mbar_wait(&b[Q_FULL], (g / p.n_kt) & 1, p.status, 33)) return false;
-                if (!mbar_wait(&b[KV_FULL + st], (g >> 1) & 1, p.status, 34)) return false;
+                if (kt == 0 && !mbar_wait_parked(&b[Q_FULL], (g / p.n_kt) & 1, p.status, 33)) return false;
+                if (!mbar_wait_parked(&b[KV_FULL + st], (g >> 1) & 1, p.status, 34)) return false;
                 tc_fence_after();
                 const uint64_t dq = umma_desc_sw128(smem_u32(base));
                 const uint64_t dk = umma_desc_sw128(smem_u32(base + AT_OFF_KV + st * 2 * AT_TILE_BYTES));
+                const uint32_t idesc_s = attn_idesc(128, keys16(g), 0);
 #pragma unroll
                 for (int k = 0; k < 4; ++k) umma_f16(tmem_base + s * 128, dq + 2 * k, dk + 2 * k, idesc_s, k != 0);
                 umma_commit(&b[S_FULL]);
                 if (kt == p.n_kt - 1) umma_commit(&b[Q_EMPTY]);
                 return true;
             };
-            // O_step = P V of step g; needs P in shared memory and the previous O tile read out of TMEM
+            // O (+)= P V of step g; the first step of an item overwrites O, so the previous item's O must have been read out
             auto issue_pv = [&](int s, int g) -> bool {
                 uint64_t* b = bars + s * NBAR;
                 uint8_t* base = smem + s * AT_SLOT_BYTES;
-                const int st = g & 1;
-                if (!mbar_wait(&b[P_FULL], g & 1, p.status, 35)) return false;
-                if (g > 0 && !mbar_wait(&b[O_FREE], (g - 1) & 1, p.status, 36)) return false;
+                const int st = g & 1, nk = keys16(g) >> 4, kt = g % p.n_kt, item = g / p.n_kt;
+                if (kt == 0 && item > 0 && !mbar_wait_parked(&b[O_FREE], (item - 1) & 1, p.status, 36)) return false;
                 tc_fence_after();
                 const uint64_t dv = umma_desc_mn_sw128(smem_u32(base + AT_OFF_KV + st * 2 * AT_TILE_BYTES + AT_TILE_BYTES));
 #pragma unroll
                 for (int k = 0; k < 8; ++k) {
-                    const uint64_t dp = umma_desc_sw128(smem_u32(base + AT_OFF_P + (k >> 2) * AT_TILE_BYTES)) + 2 * (k & 3);
-                    umma_f16(tmem_base + 256 + s * 64, dp, dv + (uint64_t)k * (2048 >> 4), idesc_o, k != 0);
+                    if (k < nk) {
+                        const uint64_t dp = umma_desc_sw128(smem_u32(base + AT_OFF_P + (k >> 2) * AT_TILE_BYTES)) + 2 * (k & 3);
+                        umma_f16(tmem_base + 256 + s * 64, dp, dv + (uint64_t)k * (2048 >> 4), idesc_o, (kt != 0 || k != 0) ? 1u : 0u);
+                    }
                 }
                 umma_commit(&b[O_FULL]);
                 umma_commit(&b[KV_EMPTY + st]);
@@ -229,8 +290,10 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, AttnParams p) {
                 for (int s = 0; s < 2 && ok; ++s) {
                     const int Gs = s ? G1 : G0;
                     if (g >= Gs) continue;
+                    // P(g) written => the score columns are free: start S(g + 1) first so the softmax warps never wait for it
+                    if (!(ok = mbar_wait_parked(&bars[s * NBAR + P_FULL], g & 1, p.status, 35))) break;
+                    if (g + 1 < Gs && !(ok = issue_s(s, g + 1))) break;
                     ok = issue_pv(s, g);
-                    if (ok && g + 1 < Gs) ok = issue_s(s, g + 1);
                 }
         }
     } else {
@@ -246,46 +309,66 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, AttnParams p) {
         int g = 0; bool ok = true;
         for (int li = 0; li < my_items && ok; ++li) {
             const AttnItem it = attn_item(p, 2 * (blockIdx.x + li * gridDim.x) + s);
-            float o[64];
-#pragma unroll
-            for (int c = 0; c < 64; ++c) o[c] = 0.f;
-            float m = -INFINITY, l = 0.f;
+            float m = -INFINITY, l = 0.f;                           // m: reference maximum the probabilities are taken against
             for (int kt = 0; kt < p.n_kt; ++kt, ++g) {
-                if (!(ok = mbar_wait(&b[S_FULL], g & 1, p.status, 37))) break;
+                if (!(ok = mbar_wait_parked(&b[S_FULL], g & 1, p.status, 37))) break;
                 tc_fence_after();
-                float alpha;
-                const int left = p.S - kt * 128;
-                if (p.pack == 1 && left >= 128) softmax_row<false>(t_s, p_row, r, sl2, 0, 128, 0, 2, m, l, alpha);
-                else if (p.pack == 1) softmax_row<true>(t_s, p_row, r, sl2, 0, left, 0, 2, m, l, alpha);
-                else softmax_row<true>(t_s, p_row, r, sl2, hsel * 64, hsel * 64 + p.S, hsel, hsel + 1, m, l, alpha);
+                int c0, c1, n_valid;                                // 32-column chunks to visit, real keys among them
+                if (p.pack == 1) { n_valid = min(128, p.S - kt * 128); c0 = 0; c1 = (n_valid + 31) >> 5; }
+                else { n_valid = p.S; c0 = hsel * 2; c1 = c0 + 2; }
+                const float mx = row_max(t_s, sl2, c0, c1, n_valid, m);
+                if (kt == 0) {
+                    m = mx;
+                } else {
+                    // P V of the previous step ran under the max pass; it must be done before P is overwritten or O rescaled
+                    if (!(ok = mbar_wait_parked(&b[O_FULL], (g - 1) & 1, p.status, 38))) break;
+                    const bool grow = mx - m > 8.f;
+                    if (__any_sync(0xffffffffu, grow)) {
+                        tc_fence_after();
+                        const float alpha = grow ? ex2_approx(m - mx) : 1.f;
+                        uint32_t v[32];
+#pragma unroll 1
+                        for (int h = 0; h < 2; ++h) {
+                            tmem_ld_32x32(t_o + h * 32, v);
+                            tmem_ld_wait();
+#pragma unroll
+                            for (int c = 0; c < 32; ++c) v[c] = __float_as_uint(__uint_as_float(v[c]) * alpha);
+                            tmem_st_32x32(t_o + h * 32, v);
+                        }
+                        tmem_st_wait();
+                        l *= alpha;
+                        if (grow) m = mx;
+                    }
+                }
+                l += row_exp(t_s, p_row, r, sl2, c0, c1, n_valid, m);
                 fence_proxy_async();
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&b[P_FULL]);
-                if (!(ok = mbar_wait(&b[O_FULL], g & 1, p.status, 38))) break;
-                tc_fence_after();
-                {
-                    uint32_t v[64];
-                    tmem_ld_row64(t_o, v);
-#pragma unroll
-                    for (int c = 0; c < 64; ++c) o[c] = fmaf(o[c], alpha, __uint_as_float(v[c]));
-                }
-                tc_fence_before();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(&b[O_FREE]);
             }
-            if (!ok) break;
+            if (!ok || !(ok = mbar_wait_parked(&b[O_FULL], (g - 1) & 1, p.status, 39))) break;
+            tc_fence_after();
             // normalise, stage this row (128 B, swizzled) in its own P block, then write the warp's 32 rows coalesced
             const float inv = 1.f / l;
             uint8_t* st_row = p_row + (p.pack == 2 ? hsel : 0) * AT_TILE_BYTES;
+#pragma unroll 1
+            for (int h = 0; h < 2; ++h) {
+                uint32_t v[32];
+                tmem_ld_32x32(t_o + h * 32, v);
+                tmem_ld_wait();
 #pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                uint4 w;
-                w.x = pack_bf16x2(o[8 * i] * inv, o[8 * i + 1] * inv); w.y = pack_bf16x2(o[8 * i + 2] * inv, o[8 * i + 3] * inv);
-                w.z = pack_bf16x2(o[8 * i + 4] * inv, o[8 * i + 5] * inv); w.w = pack_bf16x2(o[8 * i + 6] * inv, o[8 * i + 7] * inv);
-                *reinterpret_cast<uint4*>(st_row + ((i ^ (r & 7)) << 4)) = w;
+                for (int i = 0; i < 4; ++i) {
+                    uint4 w;
+                    w.x = pack_bf16x2(__uint_as_float(v[8 * i]) * inv, __uint_as_float(v[8 * i + 1]) * inv);
+                    w.y = pack_bf16x2(__uint_as_float(v[8 * i + 2]) * inv, __uint_as_float(v[8 * i + 3]) * inv);
+                    w.z = pack_bf16x2(__uint_as_float(v[8 * i + 4]) * inv, __uint_as_float(v[8 * i + 5]) * inv);
+                    w.w = pack_bf16x2(__uint_as_float(v[8 * i + 6]) * inv, __uint_as_float(v[8 * i + 7]) * inv);
+                    *reinterpret_cast<uint4*>(st_row + (((h * 4 + i) ^ (r & 7)) << 4)) = w;
+                }
             }
+            tc_fence_before();
             __syncwarp();
+            if (lane == 0) mbar_arrive(&b[O_FREE]);                  // the next item's first P V may overwrite O now
 #pragma unroll
             for (int t = 0; t < 8; ++t) {
                 const int rr = q * 32 + t * 4 + (lane >> 3), ch = lane & 7;

@@ -17,7 +17,11 @@
 // One persistent CTA per SM runs TWO such tiles at a time ("slots": own Q/K/V/P shared memory, own TMEM columns, own
 // softmax warpgroup), so the tensor core works on one slot while the other slot's softmax runs (the exp2 stream on the
 // SFUs is what bounds this kernel, not the MMAs).  warp 0 = TMA producer for both slots, warp 1 = MMA issuer for both,
-// warps 2..5 = softmax of slot 0, warps 6..9 = softmax of slot 1.  TMEM: scores at columns 0 / 128, outputs at 256 / 320.
+// warps 2..9 = softmax of slot 0, warps 10..17 = softmax of slot 1.  TMEM: scores at columns 0 / 128, outputs at 256 / 320.
+// A score row is shared by TWO softmax threads (same TMEM lane, warps w and w + 4): both scan all columns for the maximum
+// (cheap, and it keeps them in agreement without any exchange), each exponentiates one half of the columns and owns one
+// half of the row's output columns; the two partial row sums meet once per item.  Four busy warps per scheduler instead
+// of two is what keeps the SFU pipe fed while other warps wait on the tensor core.
 #include "common.cuh"
 #include "kernels.h"
 
@@ -30,8 +34,9 @@ constexpr int AT_TILE_BYTES = AT_ROWS * AT_DH * 2;            // 16 KB: one 128 
 constexpr int AT_P_BYTES = 2 * AT_TILE_BYTES;                 // 128 x 128 bf16 probabilities = two K-blocks of 64 keys
 // per slot: Q | K0 V0 | K1 V1 | P
 constexpr int AT_OFF_KV = AT_TILE_BYTES, AT_OFF_P = 5 * AT_TILE_BYTES, AT_SLOT_BYTES = 5 * AT_TILE_BYTES + AT_P_BYTES;
-constexpr int AT_SMEM = 2 * AT_SLOT_BYTES + 256 + 1024;
-constexpr int AT_THREADS = 320;
+constexpr int AT_LSUM_BYTES = 2 * 2 * AT_ROWS * 4;            // partial row sums [slot][half][row]
+constexpr int AT_SMEM = 2 * AT_SLOT_BYTES + 256 + AT_LSUM_BYTES;   // no alignment slack: the base is checked at run time
+constexpr int AT_THREADS = 576;
 static_assert(AT_SMEM <= 227 * 1024, "attention_tc: shared memory plan exceeds one SM");
 
 struct AttnParams {
@@ -111,8 +116,7 @@ __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.
 
 // One softmax step of one row, in two halves.  Both walk the 32-column chunks [c0, c1) of the 128 score columns; only the first
 // `n_valid` columns counted from chunk c0 are real keys, the rest are forced to -inf (probability 0) before the common code runs.
-// The TMEM load of chunk c + 1 is in flight while chunk c is processed.  Loops are kept rolled (two chunk bodies each): the
-// kernel's two softmax warpgroups sit at different program counters and share the instruction cache.
+// Loops are kept rolled: the softmax warps sit at different program counters and share the instruction cache.
 __device__ __forceinline__ void mask_tail(uint32_t (&v)[32], int lim) {     // keep columns [0, lim) of this chunk
     if (lim < 32) {
 #pragma unroll
@@ -121,23 +125,15 @@ __device__ __forceinline__ void mask_tail(uint32_t (&v)[32], int lim) {     // k
 }
 // row_max: new running maximum (scaled to the exp2 domain).
 __device__ __forceinline__ float row_max(uint32_t t_s, float sl2, int c0, int c1, int n_valid, float m) {
-    uint32_t va[32], vb[32];
     float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
-    tmem_ld_32x32(t_s + c0 * 32, va);
 #pragma unroll 1
-    for (int c = c0; c < c1; c += 2) {
+    for (int c = c0; c < c1; ++c) {
+        uint32_t v[32];
+        tmem_ld_32x32(t_s + c * 32, v);
         tmem_ld_wait();
-        if (c + 1 < c1) tmem_ld_32x32(t_s + (c + 1) * 32, vb);
-        mask_tail(va, n_valid - (c - c0) * 32);
+        mask_tail(v, n_valid - (c - c0) * 32);
 #pragma unroll
-        for (int j = 0; j < 32; ++j) mx4[j & 3] = fmaxf(mx4[j & 3], __uint_as_float(va[j]));
-        if (c + 1 < c1) {
-            tmem_ld_wait();
-            if (c + 2 < c1) tmem_ld_32x32(t_s + (c + 2) * 32, va);
-            mask_tail(vb, n_valid - (c + 1 - c0) * 32);
-#pragma unroll
-            for (int j = 0; j < 32; ++j) mx4[j & 3] = fmaxf(mx4[j & 3], __uint_as_float(vb[j]));
-        }
+        for (int j = 0; j < 32; ++j) mx4[j & 3] = fmaxf(mx4[j & 3], __uint_as_float(v[j]));
     }
     return fmaxf(m, fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3])) * sl2);
 }
@@ -154,32 +150,30 @@ __device__ __forceinline__ void exp_chunk(const uint32_t (&v)[32], int c, uint8_
         *reinterpret_cast<uint4*>(blk + ((((c & 1) * 4 + i) ^ (r & 7)) << 4)) = w;
     }
 }
-__device__ __forceinline__ float row_exp(uint32_t t_s, uint8_t* p_row, int r, float sl2, int c0, int c1, int n_valid, float mx) {
-    uint32_t va[32], vb[32];
+// chunks [c0, c1) are this thread's share; `first` is the row's first chunk (where the count of real keys starts)
+__device__ __forceinline__ float row_exp(uint32_t t_s, uint8_t* p_row, int r, float sl2, int c0, int c1, int first, int n_valid, float mx) {
     float s4[4] = {0.f, 0.f, 0.f, 0.f};
-    tmem_ld_32x32(t_s + c0 * 32, va);
 #pragma unroll 1
-    for (int c = c0; c < c1; c += 2) {
+    for (int c = c0; c < c1; ++c) {
+        uint32_t v[32];
+        tmem_ld_32x32(t_s + c * 32, v);
         tmem_ld_wait();
-        if (c + 1 < c1) tmem_ld_32x32(t_s + (c + 1) * 32, vb);
-        mask_tail(va, n_valid - (c - c0) * 32);
-        exp_chunk(va, c, p_row, r, sl2, mx, s4);
-        if (c + 1 < c1) {
-            tmem_ld_wait();
-            if (c + 2 < c1) tmem_ld_32x32(t_s + (c + 2) * 32, va);
-            mask_tail(vb, n_valid - (c + 1 - c0) * 32);
-            exp_chunk(vb, c + 1, p_row, r, sl2, mx, s4);
-        }
+        mask_tail(v, n_valid - (c - first) * 32);
+        exp_chunk(v, c, p_row, r, sl2, mx, s4);
     }
     return (s4[0] + s4[1]) + (s4[2] + s4[3]);
 }
 
-// 10 warps = 3 on two of the SM's four register files (16 K registers each): 168 registers per thread is the ceiling
+// 18 warps = 5 on two of the SM's four register files (16 K registers each): 96 registers per thread is the ceiling
 __global__ void __launch_bounds__(AT_THREADS, 1)
 attention_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, AttnParams p) {
-    extern __shared__ uint8_t smem_raw[];
-    uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    extern __shared__ __align__(1024) uint8_t smem[];
+    if (smem_u32(smem) & 1023u) {                      // SWIZZLE_128B tiles need 1024-byte alignment; there is no slack to fix it up
+        if (threadIdx.x == 0 && p.status) { p.status->code = 2; p.status->where = 30; }
+        return;
+    }
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 2 * AT_SLOT_BYTES);
+    float* lsum = reinterpret_cast<float*>(smem + 2 * AT_SLOT_BYTES + 256);
     // per slot (stride 10): q_full, q_empty, kv_full[2], kv_empty[2], s_full, p_full, o_full (P V of a step done), o_free (per item)
     enum { Q_FULL = 0, Q_EMPTY = 1, KV_FULL = 2, KV_EMPTY = 4, S_FULL = 6, P_FULL = 7, O_FULL = 8, O_FREE = 9, NBAR = 10 };
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * NBAR);
@@ -195,7 +189,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, AttnParams p) {
         tma_prefetch_desc(&tmQKV);
         for (int s = 0; s < 2; ++s) {
             uint64_t* b = bars + s * NBAR;
-            for (int i = 0; i < NBAR; ++i) mbar_init(&b[i], (i == P_FULL || i == O_FREE) ? 4 : 1);
+            for (int i = 0; i < NBAR; ++i) mbar_init(&b[i], (i == P_FULL || i == O_FREE) ? 8 : 1);
         }
         fence_mbar_init();
     }
@@ -297,14 +291,16 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, AttnParams p) {
                 }
         }
     } else {
-        const int s = (warp - 2) >> 2, q = warp & 3, r = q * 32 + lane;     // slot, TMEM lane quarter, tile row = TMEM lane
+        const int s = (warp - 2) >> 3, half = ((warp - 2) >> 2) & 1, q = warp & 3, r = q * 32 + lane;   // slot, column half, lane quarter, row
         const int hsel = r / R;                        // which head of the tile this row belongs to (0 when pack == 1)
         const float sl2 = 0.125f * 1.4426950408889634f;
         const uint32_t t_s = tmem_base + ((uint32_t)(q * 32) << 16) + s * 128;
-        const uint32_t t_o = tmem_base + ((uint32_t)(q * 32) << 16) + 256 + s * 64;
+        const uint32_t t_o = tmem_base + ((uint32_t)(q * 32) << 16) + 256 + s * 64 + half * 32;    // this thread's 32 output columns
         uint64_t* b = bars + s * NBAR;
         uint8_t* sP = smem + s * AT_SLOT_BYTES + AT_OFF_P;
         uint8_t* p_row = sP + r * 128;
+        float* l_mine = lsum + (s * 2 + half) * AT_ROWS + r;
+        const float* l_other = lsum + (s * 2 + (half ^ 1)) * AT_ROWS + r;
         const int my_items = my_pairs - ((s == 1 && odd_tail) ? 1 : 0);
         int g = 0; bool ok = true;
         for (int li = 0; li < my_items && ok; ++li) {
@@ -313,9 +309,9 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, AttnParams p) {
             for (int kt = 0; kt < p.n_kt; ++kt, ++g) {
                 if (!(ok = mbar_wait_parked(&b[S_FULL], g & 1, p.status, 37))) break;
                 tc_fence_after();
-                int c0, c1, n_valid;                                // 32-column chunks to visit, real keys among them
-                if (p.pack == 1) { n_valid = min(128, p.S - kt * 128); c0 = 0; c1 = (n_valid + 31) >> 5; }
-                else { n_valid = p.S; c0 = hsel * 2; c1 = c0 + 2; }
+                int c0, c1, n_valid, e0, e1;                        // row's 32-column chunks, real keys among them; this thread's share
+                if (p.pack == 1) { n_valid = min(128, p.S - kt * 128); c0 = 0; c1 = (n_valid + 31) >> 5; e0 = 2 * half; e1 = min(c1, e0 + 2); }
+                else { n_valid = p.S; c0 = hsel * 2; c1 = c0 + 2; e0 = c0 + half; e1 = e0 + 1; }
                 const float mx = row_max(t_s, sl2, c0, c1, n_valid, m);
                 if (kt == 0) {
                     m = mx;
@@ -327,20 +323,17 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, AttnParams p) {
                         tc_fence_after();
                         const float alpha = grow ? ex2_approx(m - mx) : 1.f;
                         uint32_t v[32];
-#pragma unroll 1
-                        for (int h = 0; h < 2; ++h) {
-                            tmem_ld_32x32(t_o + h * 32, v);
-                            tmem_ld_wait();
+                        tmem_ld_32x32(t_o, v);
+                        tmem_ld_wait();
 #pragma unroll
-                            for (int c = 0; c < 32; ++c) v[c] = __float_as_uint(__uint_as_float(v[c]) * alpha);
-                            tmem_st_32x32(t_o + h * 32, v);
-                        }
+                        for (int c = 0; c < 32; ++c) v[c] = __float_as_uint(__uint_as_float(v[c]) * alpha);
+                        tmem_st_32x32(t_o, v);
                         tmem_st_wait();
                         l *= alpha;
                         if (grow) m = mx;
                     }
                 }
-                l += row_exp(t_s, p_row, r, sl2, c0, c1, n_valid, m);
+                l += row_exp(t_s, p_row, r, sl2, e0, e1, c0, n_valid, m);
                 fence_proxy_async();
                 tc_fence_before();
                 __syncwarp();
@@ -348,30 +341,30 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, AttnParams p) {
             }
             if (!ok || !(ok = mbar_wait_parked(&b[O_FULL], (g - 1) & 1, p.status, 39))) break;
             tc_fence_after();
-            // normalise, stage this row (128 B, swizzled) in its own P block, then write the warp's 32 rows coalesced
-            const float inv = 1.f / l;
-            uint8_t* st_row = p_row + (p.pack == 2 ? hsel : 0) * AT_TILE_BYTES;
-#pragma unroll 1
-            for (int h = 0; h < 2; ++h) {
-                uint32_t v[32];
-                tmem_ld_32x32(t_o + h * 32, v);
-                tmem_ld_wait();
-#pragma unroll
-                for (int i = 0; i < 4; ++i) {
-                    uint4 w;
-                    w.x = pack_bf16x2(__uint_as_float(v[8 * i]) * inv, __uint_as_float(v[8 * i + 1]) * inv);
-                    w.y = pack_bf16x2(__uint_as_float(v[8 * i + 2]) * inv, __uint_as_float(v[8 * i + 3]) * inv);
-                    w.z = pack_bf16x2(__uint_as_float(v[8 * i + 4]) * inv, __uint_as_float(v[8 * i + 5]) * inv);
-                    w.w = pack_bf16x2(__uint_as_float(v[8 * i + 6]) * inv, __uint_as_float(v[8 * i + 7]) * inv);
-                    *reinterpret_cast<uint4*>(st_row + (((h * 4 + i) ^ (r & 7)) << 4)) = w;
-                }
-            }
+            // this thread's 32 output columns out of TMEM, then the O columns go back to the MMA warp
+            uint32_t v[32];
+            tmem_ld_32x32(t_o, v);
+            *l_mine = l;
+            tmem_ld_wait();
             tc_fence_before();
-            __syncwarp();
-            if (lane == 0) mbar_arrive(&b[O_FREE]);                  // the next item's first P V may overwrite O now
+            named_bar_sync(1 + s, 256);                             // both halves of every row have published their sums
+            if (lane == 0) mbar_arrive(&b[O_FREE]);
+            const float inv = 1.f / (l + *l_other);
+            // normalise, stage the half row (64 B, swizzled) in the row's own P block, then write the warp's 32 half rows coalesced
+            uint8_t* st_row = p_row + (p.pack == 2 ? hsel : 0) * AT_TILE_BYTES;
 #pragma unroll
-            for (int t = 0; t < 8; ++t) {
-                const int rr = q * 32 + t * 4 + (lane >> 3), ch = lane & 7;
+            for (int i = 0; i < 4; ++i) {
+                uint4 w;
+                w.x = pack_bf16x2(__uint_as_float(v[8 * i]) * inv, __uint_as_float(v[8 * i + 1]) * inv);
+                w.y = pack_bf16x2(__uint_as_float(v[8 * i + 2]) * inv, __uint_as_float(v[8 * i + 3]) * inv);
+                w.z = pack_bf16x2(__uint_as_float(v[8 * i + 4]) * inv, __uint_as_float(v[8 * i + 5]) * inv);
+                w.w = pack_bf16x2(__uint_as_float(v[8 * i + 6]) * inv, __uint_as_float(v[8 * i + 7]) * inv);
+                *reinterpret_cast<uint4*>(st_row + (((half * 4 + i) ^ (r & 7)) << 4)) = w;
+            }
+            __syncwarp();
+#pragma unroll
+            for (int t = 0; t < 4; ++t) {
+                const int rr = q * 32 + t * 8 + (lane >> 2), ch = half * 4 + (lane & 3);
                 const int hs = rr / R, qrow = it.qt * R + (rr % R);
                 if (qrow < p.S) {
                     const uint4 w = *reinterpret_cast<const uint4*>(sP + rr * 128 + (p.pack == 2 ? hs : 0) * AT_TILE_BYTES + ((ch ^ (rr & 7)) << 4));

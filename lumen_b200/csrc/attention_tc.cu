@@ -8,16 +8,18 @@
 //   pack == 2 (S <= 64): two heads of one image share a tile (rows 0..63 head h, rows 64..127 head h+1; same for the
 //                        keys); a block-diagonal mask keeps them apart, so short sequences (S = 50) still fill the MMA.
 // Per step:   S = Q K^T            UMMA 128x128x16 x4, A = Q tile, B = K tile, both K-major SWIZZLE_128B (TMA)
-//             P = exp2(...)         four softmax warps, thread = query row = TMEM lane; P goes to shared memory as the
-//                                   K-major A operand of the second matmul (bf16, swizzled like a TMA tile)
-//             O_step = P V          UMMA 128x64x16 x8, B = V tile as loaded ([key][dim], dim contiguous) = MN-major
+//             P = exp2(...)         softmax warps, thread = query row = TMEM lane; P goes back to TMEM (bf16 pairs, 64
+//                                   columns) and is the A operand of the second matmul straight from there: no shared
+//                                   memory round trip, and P V only streams V (P from shared memory would make the
+//                                   128x64x16 MMAs shared-memory-bandwidth bound)
+//             O (+)= P V            UMMA 128x64x16 x8, B = V tile as loaded ([key][dim], dim contiguous) = MN-major
 //             O accumulates in TMEM across the key steps.  The softmax reference maximum is only moved when a row's maximum
 //             grows by more than 2^8 (probabilities stay <= 256, exact in bf16/fp32 terms); then that warp rescales its
 //             32 O rows in place (tcgen05.ld -> multiply -> tcgen05.st).  After the first key step this is rare.
 // One persistent CTA per SM runs TWO such tiles at a time ("slots": own Q/K/V/P shared memory, own TMEM columns, own
 // softmax warpgroup), so the tensor core works on one slot while the other slot's softmax runs (the exp2 stream on the
-// SFUs is what bounds this kernel, not the MMAs).  warp 0 = TMA producer for both slots, warp 1 = MMA issuer for both,
-// warps 2..9 = softmax of slot 0, warps 10..17 = softmax of slot 1.  TMEM: scores at columns 0 / 128, outputs at 256 / 320.
+// SFUs is what bounds this kernel, not the MMAs).  The slots are independent pipelines: warps 0 / 18 = TMA producers,
+// warps 1 / 19 = MMA issuers, warps 2..9 / 10..17 = softmax (slot 0 / 1).  TMEM per slot (256 columns): scores 0..127, P 128..191, O 192..255.
 // A score row is shared by TWO softmax threads (same TMEM lane, warps w and w + 4): both scan all columns for the maximum
 // (cheap, and it keeps them in agreement without any exchange), each exponentiates one half of the columns and owns one
 // half of the row's output columns; the two partial row sums meet once per item.  Four busy warps per scheduler instead
@@ -31,12 +33,12 @@ namespace b200 {
 
 constexpr int AT_ROWS = 128, AT_DH = 64;
 constexpr int AT_TILE_BYTES = AT_ROWS * AT_DH * 2;            // 16 KB: one 128 x 64 bf16 tile (Q, K or V)
-constexpr int AT_P_BYTES = 2 * AT_TILE_BYTES;                 // 128 x 128 bf16 probabilities = two K-blocks of 64 keys
-// per slot: Q | K0 V0 | K1 V1 | P
-constexpr int AT_OFF_KV = AT_TILE_BYTES, AT_OFF_P = 5 * AT_TILE_BYTES, AT_SLOT_BYTES = 5 * AT_TILE_BYTES + AT_P_BYTES;
+// per slot: Q | K0 V0 | K1 V1 | output staging (128 rows x 128 B)
+constexpr int AT_OFF_KV = AT_TILE_BYTES, AT_OFF_STAGE = 5 * AT_TILE_BYTES, AT_SLOT_BYTES = 6 * AT_TILE_BYTES;
+constexpr int AT_TM_S = 0, AT_TM_P = 128, AT_TM_O = 192, AT_TM_SLOT = 256;   // TMEM columns inside a slot
 constexpr int AT_LSUM_BYTES = 2 * 2 * AT_ROWS * 4;            // partial row sums [slot][half][row]
-constexpr int AT_SMEM = 2 * AT_SLOT_BYTES + 256 + AT_LSUM_BYTES;   // no alignment slack: the base is checked at run time
-constexpr int AT_THREADS = 576;
+constexpr int AT_SMEM = 2 * AT_SLOT_BYTES + 256 + AT_LSUM_BYTES + 1024;
+constexpr int AT_THREADS = 640;
 static_assert(AT_SMEM <= 227 * 1024, "attention_tc: shared memory plan exceeds one SM");
 
 struct AttnParams {
@@ -112,6 +114,23 @@ __device__ __forceinline__ void tmem_st_32x32(uint32_t taddr, const uint32_t (&v
            "r"(v[24]), "r"(v[25]), "r"(v[26]), "r"(v[27]), "r"(v[28]), "r"(v[29]), "r"(v[30]), "r"(v[31])
         : "memory");
 }
+// 16 registers per thread -> 16 consecutive 32-bit columns (32 bf16 probabilities) of the thread's TMEM lane
+__device__ __forceinline__ void tmem_st_32x16(uint32_t taddr, const uint32_t (&v)[16]) {
+    asm volatile(
+        "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};"
+        :: "r"(taddr), "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]),
+           "r"(v[8]), "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15])
+        : "memory");
+}
+// D[tmem] (+)= A[tmem] * B[smem]: A = 128 lanes x 16 bf16 (8 columns of bf16 pairs), lane = row
+__device__ __forceinline__ void umma_f16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p;\n\t}"
+        ::"r"(tmem_d), "r"(tmem_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
 __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
 // One softmax step of one row, in two halves.  Both walk the 32-column chunks [c0, c1) of the 128 score columns; only the first
@@ -137,21 +156,19 @@ __device__ __forceinline__ float row_max(uint32_t t_s, float sl2, int c0, int c1
     }
     return fmaxf(m, fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3])) * sl2);
 }
-// 32 probabilities exp2(s * sl2 - mx) of chunk c as bf16 into the row's P bytes (the A operand of P V); adds them to s4.
-__device__ __forceinline__ void exp_chunk(const uint32_t (&v)[32], int c, uint8_t* p_row, int r, float sl2, float mx, float (&s4)[4]) {
-    uint8_t* blk = p_row + (c >> 1) * AT_TILE_BYTES;                // K-block of 64 keys
+// 32 probabilities exp2(s * sl2 - mx) of chunk c as bf16 pairs into the row's P columns (the A operand of P V); adds them to s4.
+__device__ __forceinline__ void exp_chunk(const uint32_t (&v)[32], uint32_t t_p_chunk, float sl2, float mx, float (&s4)[4]) {
+    uint32_t w[16];
 #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        float e[8];
-#pragma unroll
-        for (int j = 0; j < 8; ++j) { e[j] = ex2_approx(fmaf(__uint_as_float(v[8 * i + j]), sl2, -mx)); s4[j & 3] += e[j]; }
-        uint4 w;
-        w.x = pack_bf16x2(e[0], e[1]); w.y = pack_bf16x2(e[2], e[3]); w.z = pack_bf16x2(e[4], e[5]); w.w = pack_bf16x2(e[6], e[7]);
-        *reinterpret_cast<uint4*>(blk + ((((c & 1) * 4 + i) ^ (r & 7)) << 4)) = w;
+    for (int i = 0; i < 16; ++i) {
+        const float e0 = ex2_approx(fmaf(__uint_as_float(v[2 * i]), sl2, -mx)), e1 = ex2_approx(fmaf(__uint_as_float(v[2 * i + 1]), sl2, -mx));
+        s4[(2 * i) & 3] += e0; s4[(2 * i + 1) & 3] += e1;
+        w[i] = pack_bf16x2(e0, e1);
     }
+    tmem_st_32x16(t_p_chunk, w);
 }
 // chunks [c0, c1) are this thread's share; `first` is the row's first chunk (where the count of real keys starts)
-__device__ __forceinline__ float row_exp(uint32_t t_s, uint8_t* p_row, int r, float sl2, int c0, int c1, int first, int n_valid, float mx) {
+__device__ __forceinline__ float row_exp(uint32_t t_s, uint32_t t_p, float sl2, int c0, int c1, int first, int n_valid, float mx) {
     float s4[4] = {0.f, 0.f, 0.f, 0.f};
 #pragma unroll 1
     for (int c = c0; c < c1; ++c) {
@@ -159,19 +176,17 @@ __device__ __forceinline__ float row_exp(uint32_t t_s, uint8_t* p_row, int r, fl
         tmem_ld_32x32(t_s + c * 32, v);
         tmem_ld_wait();
         mask_tail(v, n_valid - (c - first) * 32);
-        exp_chunk(v, c, p_row, r, sl2, mx, s4);
+        exp_chunk(v, t_p + c * 16, sl2, mx, s4);
     }
+    tmem_st_wait();
     return (s4[0] + s4[1]) + (s4[2] + s4[3]);
 }
 
-// 18 warps = 5 on two of the SM's four register files (16 K registers each): 96 registers per thread is the ceiling
+// 20 warps = 5 on each of the SM's four register files (16 K registers each): 96 registers per thread is the ceiling
 __global__ void __launch_bounds__(AT_THREADS, 1)
 attention_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, AttnParams p) {
-    extern __shared__ __align__(1024) uint8_t smem[];
-    if (smem_u32(smem) & 1023u) {                      // SWIZZLE_128B tiles need 1024-byte alignment; there is no slack to fix it up
-        if (threadIdx.x == 0 && p.status) { p.status->code = 2; p.status->where = 30; }
-        return;
-    }
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 2 * AT_SLOT_BYTES);
     float* lsum = reinterpret_cast<float*>(smem + 2 * AT_SLOT_BYTES + 256);
     // per slot (stride 10): q_full, q_empty, kv_full[2], kv_empty[2], s_full, p_full, o_full (P V of a step done), o_free (per item)
@@ -194,59 +209,51 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, AttnParams p) {
         fence_mbar_init();
     }
     if (warp == 1) tmem_alloc(tmem_slot, 512);
-    for (int i = threadIdx.x; i < 2 * (AT_P_BYTES / 16); i += AT_THREADS) {
-        const int s = i / (AT_P_BYTES / 16), j = i % (AT_P_BYTES / 16);
-        reinterpret_cast<uint4*>(smem + s * AT_SLOT_BYTES + AT_OFF_P)[j] = make_uint4(0, 0, 0, 0);
-    }
-    fence_proxy_async();                               // the zeroed off-diagonal blocks are read by the tensor core
     tc_fence_before();
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
-    if (warp == 0) {
+    if (warp == 0 || warp == 18) {
+        // ---- TMA producer of one slot: Q once per item, K/V per key step through a ring of two
         if (lane == 0) {
+            const int s = warp == 0 ? 0 : 1;
+            const int my_items = my_pairs - ((s == 1 && odd_tail) ? 1 : 0);
+            uint64_t* b = bars + s * NBAR;
+            uint8_t* base = smem + s * AT_SLOT_BYTES;
             bool ok = true;
-            for (int li = 0; li < my_pairs && ok; ++li) {
-                const int pair = blockIdx.x + li * gridDim.x;
-                const int n_slots = (li == my_pairs - 1 && odd_tail) ? 1 : 2;
-                for (int s = 0; s < n_slots && ok; ++s) {
-                    const AttnItem it = attn_item(p, 2 * pair + s);
-                    uint64_t* b = bars + s * NBAR;
-                    uint8_t* base = smem + s * AT_SLOT_BYTES;
-                    if (!(ok = mbar_wait(&b[Q_EMPTY], (li & 1) ^ 1, p.status, 31))) break;
-                    mbar_arrive_expect_tx(&b[Q_FULL], AT_TILE_BYTES);
-                    for (int u = 0; u < p.pack; ++u)
-                        tma_load_2d(base + u * R * 128, &tmQKV, &b[Q_FULL], (it.h0 + u) * AT_DH, it.b * p.S + it.qt * R);
-                }
-                for (int kt = 0; kt < p.n_kt && ok; ++kt) {
-                    const int g = li * p.n_kt + kt, st = g & 1;
-                    for (int s = 0; s < n_slots && ok; ++s) {
-                        const AttnItem it = attn_item(p, 2 * pair + s);
-                        uint64_t* b = bars + s * NBAR;
-                        uint8_t* k_dst = smem + s * AT_SLOT_BYTES + AT_OFF_KV + st * 2 * AT_TILE_BYTES;
-                        if (!(ok = mbar_wait(&b[KV_EMPTY + st], ((g >> 1) & 1) ^ 1, p.status, 32))) break;
-                        mbar_arrive_expect_tx(&b[KV_FULL + st], 2 * AT_TILE_BYTES);
-                        for (int u = 0; u < p.pack; ++u) {
-                            const int row = it.b * p.S + kt * R;
-                            tma_load_2d(k_dst + u * R * 128, &tmQKV, &b[KV_FULL + st], p.d + (it.h0 + u) * AT_DH, row);
-                            tma_load_2d(k_dst + AT_TILE_BYTES + u * R * 128, &tmQKV, &b[KV_FULL + st], 2 * p.d + (it.h0 + u) * AT_DH, row);
-                        }
+            for (int li = 0, g = 0; li < my_items && ok; ++li) {
+                const AttnItem it = attn_item(p, 2 * (blockIdx.x + li * gridDim.x) + s);
+                if (!(ok = mbar_wait_parked(&b[Q_EMPTY], (li & 1) ^ 1, p.status, 31))) break;
+                mbar_arrive_expect_tx(&b[Q_FULL], AT_TILE_BYTES);
+                for (int u = 0; u < p.pack; ++u)
+                    tma_load_2d(base + u * R * 128, &tmQKV, &b[Q_FULL], (it.h0 + u) * AT_DH, it.b * p.S + it.qt * R);
+                for (int kt = 0; kt < p.n_kt; ++kt, ++g) {
+                    const int st = g & 1, row = it.b * p.S + kt * R;
+                    uint8_t* k_dst = base + AT_OFF_KV + st * 2 * AT_TILE_BYTES;
+                    if (!(ok = mbar_wait_parked(&b[KV_EMPTY + st], ((g >> 1) & 1) ^ 1, p.status, 32))) break;
+                    mbar_arrive_expect_tx(&b[KV_FULL + st], 2 * AT_TILE_BYTES);
+                    for (int u = 0; u < p.pack; ++u) {
+                        tma_load_2d(k_dst + u * R * 128, &tmQKV, &b[KV_FULL + st], p.d + (it.h0 + u) * AT_DH, row);
+                        tma_load_2d(k_dst + AT_TILE_BYTES + u * R * 128, &tmQKV, &b[KV_FULL + st], 2 * p.d + (it.h0 + u) * AT_DH, row);
                     }
                 }
             }
         }
-    } else if (warp == 1) {
+    } else if (warp == 1 || warp == 19) {
+        // ---- MMA issuer of one slot
         if (lane == 0) {
+            const int s = warp == 1 ? 0 : 1;
             constexpr uint32_t idesc_o = attn_idesc(128, 64, 1);
-            const int G0 = my_pairs * p.n_kt, G1 = (my_pairs - (odd_tail ? 1 : 0)) * p.n_kt;   // steps per slot
+            const int G = (my_pairs - ((s == 1 && odd_tail) ? 1 : 0)) * p.n_kt;     // steps of this slot
+            uint64_t* b = bars + s * NBAR;
+            uint8_t* base = smem + s * AT_SLOT_BYTES;
+            const uint32_t tm = tmem_base + s * AT_TM_SLOT;
             bool ok = true;
             // keys a step really holds, rounded up to the MMA's K granule (pack == 2 always runs the full tile)
             auto keys16 = [&](int g) { const int left = p.S - (g % p.n_kt) * 128; return (p.pack == 2 || left >= 128) ? 128 : ((left + 15) & ~15); };
-            // S = Q K^T of step g of a slot; the slot's score columns are free once P of step g - 1 was written
-            auto issue_s = [&](int s, int g) -> bool {
-                uint64_t* b = bars + s * NBAR;
-                uint8_t* base = smem + s * AT_SLOT_BYTES;
+            // S = Q K^T of step g; the score columns are free once P of step g - 1 was written
+            auto issue_s = [&](int g) -> bool {
                 const int kt = g % p.n_kt, st = g & 1;
                 if (kt == 0 && !mbar_wait_parked(&b[Q_FULL], (g / p.n_kt) & 1, p.status, 33)) return false;
                 if (!mbar_wait_parked(&b[KV_FULL + st], (g >> 1) & 1, p.status, 34)) return false;
@@ -255,50 +262,51 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, AttnParams p) {
                 const uint64_t dk = umma_desc_sw128(smem_u32(base + AT_OFF_KV + st * 2 * AT_TILE_BYTES));
                 const uint32_t idesc_s = attn_idesc(128, keys16(g), 0);
 #pragma unroll
-                for (int k = 0; k < 4; ++k) umma_f16(tmem_base + s * 128, dq + 2 * k, dk + 2 * k, idesc_s, k != 0);
+                for (int k = 0; k < 4; ++k) umma_f16(tm + AT_TM_S, dq + 2 * k, dk + 2 * k, idesc_s, k != 0);
                 umma_commit(&b[S_FULL]);
                 if (kt == p.n_kt - 1) umma_commit(&b[Q_EMPTY]);
                 return true;
             };
-            // O (+)= P V of step g; the first step of an item overwrites O, so the previous item's O must have been read out
-            auto issue_pv = [&](int s, int g) -> bool {
-                uint64_t* b = bars + s * NBAR;
-                uint8_t* base = smem + s * AT_SLOT_BYTES;
+            // O (+)= P V of step g, P read from TMEM; the first step of an item overwrites O, so the previous item's O must have been read out
+            auto issue_pv = [&](int g) -> bool {
                 const int st = g & 1, nk = keys16(g) >> 4, kt = g % p.n_kt, item = g / p.n_kt;
                 if (kt == 0 && item > 0 && !mbar_wait_parked(&b[O_FREE], (item - 1) & 1, p.status, 36)) return false;
                 tc_fence_after();
                 const uint64_t dv = umma_desc_mn_sw128(smem_u32(base + AT_OFF_KV + st * 2 * AT_TILE_BYTES + AT_TILE_BYTES));
 #pragma unroll
                 for (int k = 0; k < 8; ++k) {
-                    if (k < nk) {
-                        const uint64_t dp = umma_desc_sw128(smem_u32(base + AT_OFF_P + (k >> 2) * AT_TILE_BYTES)) + 2 * (k & 3);
-                        umma_f16(tmem_base + 256 + s * 64, dp, dv + (uint64_t)k * (2048 >> 4), idesc_o, (kt != 0 || k != 0) ? 1u : 0u);
-                    }
+                    if (k < nk)
+                        umma_f16_ts(tm + AT_TM_O, tm + AT_TM_P + k * 8, dv + (uint64_t)k * (2048 >> 4), idesc_o, (kt != 0 || k != 0) ? 1u : 0u);
                 }
                 umma_commit(&b[O_FULL]);
                 umma_commit(&b[KV_EMPTY + st]);
                 return true;
             };
-            for (int s = 0; s < 2 && ok; ++s) if ((s ? G1 : G0) > 0) ok = issue_s(s, 0);
-            for (int g = 0; g < G0 && ok; ++g)
-                for (int s = 0; s < 2 && ok; ++s) {
-                    const int Gs = s ? G1 : G0;
-                    if (g >= Gs) continue;
-                    // P(g) written => the score columns are free: start S(g + 1) first so the softmax warps never wait for it
-                    if (!(ok = mbar_wait_parked(&bars[s * NBAR + P_FULL], g & 1, p.status, 35))) break;
-                    if (g + 1 < Gs && !(ok = issue_s(s, g + 1))) break;
-                    ok = issue_pv(s, g);
-                }
+            if (G > 0) ok = issue_s(0);
+            for (int g = 0; g < G && ok; ++g) {
+                // P(g) written => the score columns are free: start S(g + 1) first so the softmax warps wait as little as possible
+                if (!(ok = mbar_wait_parked(&b[P_FULL], g & 1, p.status, 35))) break;
+                if (g + 1 < G && !(ok = issue_s(g + 1))) break;
+                ok = issue_pv(g);
+            }
         }
     } else {
         const int s = (warp - 2) >> 3, half = ((warp - 2) >> 2) & 1, q = warp & 3, r = q * 32 + lane;   // slot, column half, lane quarter, row
         const int hsel = r / R;                        // which head of the tile this row belongs to (0 when pack == 1)
         const float sl2 = 0.125f * 1.4426950408889634f;
-        const uint32_t t_s = tmem_base + ((uint32_t)(q * 32) << 16) + s * 128;
-        const uint32_t t_o = tmem_base + ((uint32_t)(q * 32) << 16) + 256 + s * 64 + half * 32;    // this thread's 32 output columns
+        const uint32_t t_lane = tmem_base + ((uint32_t)(q * 32) << 16) + s * AT_TM_SLOT;
+        const uint32_t t_s = t_lane + AT_TM_S, t_p = t_lane + AT_TM_P;
+        const uint32_t t_o = t_lane + AT_TM_O + half * 32;             // this thread's 32 output columns
         uint64_t* b = bars + s * NBAR;
-        uint8_t* sP = smem + s * AT_SLOT_BYTES + AT_OFF_P;
-        uint8_t* p_row = sP + r * 128;
+        uint8_t* stage = smem + s * AT_SLOT_BYTES + AT_OFF_STAGE;
+        if (p.pack == 2) {                                             // the other head's keys: probability 0, written once
+            uint32_t z[16];
+#pragma unroll
+            for (int i = 0; i < 16; ++i) z[i] = 0u;
+            tmem_st_32x16(t_p + half * 32, z);
+            tmem_st_32x16(t_p + half * 32 + 16, z);
+            tmem_st_wait();
+        }
         float* l_mine = lsum + (s * 2 + half) * AT_ROWS + r;
         const float* l_other = lsum + (s * 2 + (half ^ 1)) * AT_ROWS + r;
         const int my_items = my_pairs - ((s == 1 && odd_tail) ? 1 : 0);
@@ -333,8 +341,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, AttnParams p) {
                         if (grow) m = mx;
                     }
                 }
-                l += row_exp(t_s, p_row, r, sl2, e0, e1, c0, n_valid, m);
-                fence_proxy_async();
+                l += row_exp(t_s, t_p, sl2, e0, e1, c0, n_valid, m);
                 tc_fence_before();
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&b[P_FULL]);
@@ -350,8 +357,8 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, AttnParams p) {
             named_bar_sync(1 + s, 256);                             // both halves of every row have published their sums
             if (lane == 0) mbar_arrive(&b[O_FREE]);
             const float inv = 1.f / (l + *l_other);
-            // normalise, stage the half row (64 B, swizzled) in the row's own P block, then write the warp's 32 half rows coalesced
-            uint8_t* st_row = p_row + (p.pack == 2 ? hsel : 0) * AT_TILE_BYTES;
+            // normalise, stage the half row (64 B, swizzled), then write the warp's 32 half rows coalesced
+            uint8_t* st_row = stage + r * 128;
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
                 uint4 w;
@@ -367,7 +374,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, AttnParams p) {
                 const int rr = q * 32 + t * 8 + (lane >> 2), ch = half * 4 + (lane & 3);
                 const int hs = rr / R, qrow = it.qt * R + (rr % R);
                 if (qrow < p.S) {
-                    const uint4 w = *reinterpret_cast<const uint4*>(sP + rr * 128 + (p.pack == 2 ? hs : 0) * AT_TILE_BYTES + ((ch ^ (rr & 7)) << 4));
+                    const uint4 w = *reinterpret_cast<const uint4*>(stage + rr * 128 + ((ch ^ (rr & 7)) << 4));
                     *reinterpret_cast<uint4*>(p.out + (size_t)(it.b * p.S + qrow) * p.d + (it.h0 + hs) * AT_DH + ch * 8) = w;
                 }
             }

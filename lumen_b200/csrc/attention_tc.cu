@@ -3,27 +3,26 @@
 // The mma.sync attention in vit_ops.cu is bound by the legacy HMMA rate (32 % of a ViT-B/16 step, 44 % of ViT-L/14@336);
 // this kernel issues the two matmuls as tcgen05.mma with accumulators in TMEM.
 //
-// Tile = 128 query rows x 128 keys.
-//   pack == 1 (S > 64): 128 queries of one (image, head); keys are walked in steps of 128 with an online softmax.
-//   pack == 2 (S <= 64): two heads of one image share a tile (rows 0..63 head h, rows 64..127 head h+1; same for the
-//                        keys); a block-diagonal mask keeps them apart, so short sequences (S = 50) still fill the MMA.
-// Per step:   S = Q K^T            UMMA 128x128x16 x4, A = Q tile, B = K tile, both K-major SWIZZLE_128B (TMA)
-//             P = exp2(...)         softmax warps, thread = query row = TMEM lane; P goes back to TMEM (bf16 pairs, 64
-//                                   columns) and is the A operand of the second matmul straight from there: no shared
-//                                   memory round trip, and P V only streams V (P from shared memory would make the
-//                                   128x64x16 MMAs shared-memory-bandwidth bound)
-//             O (+)= P V            UMMA 128x64x16 x8, B = V tile as loaded ([key][dim], dim contiguous) = MN-major
+// Tile = 128 query rows, walked over the keys in steps of 64.
+//   pack == 1 (S > 64): 128 queries of one (image, head); online softmax over ceil(S / 64) key steps.
+//   pack == 2 (S <= 64): two heads of one image share a tile (rows 0..63 head h, rows 64..127 head h + 1) and the tile takes
+//                        two steps: step u holds the keys of head h + u; rows of the other head have probability 0 there
+//                        (written once), so short sequences (S = 50) still fill the 128-row MMA.
+// Per step g: S[g&1] = Q K^T     UMMA 128x64x16 x4 into one of TWO score buffers in TMEM: the tensor core computes the scores
+//                                of step g + 1 while the softmax warps work on step g
+//             P[g&1] = exp2(..)  softmax warps, thread = query row = TMEM lane; P goes back to TMEM (bf16 pairs, 32 columns,
+//                                double buffered) and is the A operand of the second matmul straight from there
+//             O (+)= P V         UMMA 128x64x16 x4, B = V tile as loaded ([key][dim], dim contiguous) = MN-major
 //             O accumulates in TMEM across the key steps.  The softmax reference maximum is only moved when a row's maximum
-//             grows by more than 2^8 (probabilities stay <= 256, exact in bf16/fp32 terms); then that warp rescales its
-//             32 O rows in place (tcgen05.ld -> multiply -> tcgen05.st).  After the first key step this is rare.
-// One persistent CTA per SM runs TWO such tiles at a time ("slots": own Q/K/V/P shared memory, own TMEM columns, own
-// softmax warpgroup), so the tensor core works on one slot while the other slot's softmax runs (the exp2 stream on the
-// SFUs is what bounds this kernel, not the MMAs).  The slots are independent pipelines: warps 0 / 18 = TMA producers,
-// warps 1 / 19 = MMA issuers, warps 2..9 / 10..17 = softmax (slot 0 / 1).  TMEM per slot (256 columns): scores 0..127, P 128..191, O 192..255.
-// A score row is shared by TWO softmax threads (same TMEM lane, warps w and w + 4): both scan all columns for the maximum
-// (cheap, and it keeps them in agreement without any exchange), each exponentiates one half of the columns and owns one
-// half of the row's output columns; the two partial row sums meet once per item.  Four busy warps per scheduler instead
-// of two is what keeps the SFU pipe fed while other warps wait on the tensor core.
+//             grows by more than 2^8 (probabilities stay <= 256, exact in bf16/fp32 terms); then the row's O is rescaled in
+//             place (tcgen05.ld -> multiply -> tcgen05.st).  After the first key steps this is rare.
+// One persistent CTA per SM runs TWO such tiles at a time ("slots": own Q/K/V shared memory, own 256 TMEM columns, own
+// warps), independent pipelines that share the SM: warps 0 / 18 = TMA producers, warps 1 / 19 = MMA issuers,
+// warps 2..9 / 10..17 = softmax (slot 0 / 1).  TMEM per slot: S0 0..63, S1 64..127, P0 128..159, P1 160..191, O 192..255.
+// A score row is shared by TWO softmax threads (same TMEM lane, warps w and w + 4): both load the step's 64 scores and take
+// the maximum (cheap, and it keeps them in agreement without any exchange), each exponentiates 32 of them and owns 32 of
+// the row's output columns; the two partial row sums meet once per item.  The exp2 stream on the SFUs (16 per clock and
+// SM) is what bounds this kernel, not the MMAs.
 #include "common.cuh"
 #include "kernels.h"
 
@@ -31,13 +30,15 @@
 
 namespace b200 {
 
-constexpr int AT_ROWS = 128, AT_DH = 64;
-constexpr int AT_TILE_BYTES = AT_ROWS * AT_DH * 2;            // 16 KB: one 128 x 64 bf16 tile (Q, K or V)
-// per slot: Q | K0 V0 | K1 V1 | output staging (128 rows x 128 B)
-constexpr int AT_OFF_KV = AT_TILE_BYTES, AT_OFF_STAGE = 5 * AT_TILE_BYTES, AT_SLOT_BYTES = 6 * AT_TILE_BYTES;
+constexpr int AT_ROWS = 128, AT_DH = 64, AT_KEYS = 64;        // query rows per tile, head dim, keys per step
+constexpr int AT_Q_BYTES = AT_ROWS * AT_DH * 2;               // 16 KB
+constexpr int AT_KV_BYTES = AT_KEYS * AT_DH * 2;              // 8 KB: K or V tile of one step
+constexpr int AT_STAGES = 4;                                  // K/V ring depth per slot
+// per slot: Q0 | Q1 | (K V) x AT_STAGES.  The Q buffer of a finished item doubles as its output staging area.
+constexpr int AT_OFF_KV = 2 * AT_Q_BYTES, AT_SLOT_BYTES = 2 * AT_Q_BYTES + AT_STAGES * 2 * AT_KV_BYTES;
 constexpr int AT_TM_S = 0, AT_TM_P = 128, AT_TM_O = 192, AT_TM_SLOT = 256;   // TMEM columns inside a slot
-constexpr int AT_LSUM_BYTES = 2 * 2 * AT_ROWS * 4;            // partial row sums [slot][half][row]
-constexpr int AT_SMEM = 2 * AT_SLOT_BYTES + 256 + AT_LSUM_BYTES + 1024;
+constexpr int AT_BAR_BYTES = 512, AT_LSUM_BYTES = 2 * 2 * AT_ROWS * 4;       // barriers; partial row sums [slot][half][row]
+constexpr int AT_SMEM = 2 * AT_SLOT_BYTES + AT_BAR_BYTES + AT_LSUM_BYTES + 1024;
 constexpr int AT_THREADS = 640;
 static_assert(AT_SMEM <= 227 * 1024, "attention_tc: shared memory plan exceeds one SM");
 
@@ -50,7 +51,7 @@ struct AttnParams {
     DeviceStatus* status;
 };
 
-// MN-major B operand (V tile: 128 keys x 64 dims, one 128-byte row per key, SWIZZLE_128B): 8-key groups 1024 B apart.
+// MN-major B operand (V tile: 64 keys x 64 dims, one 128-byte row per key, SWIZZLE_128B): 8-key groups 1024 B apart.
 __device__ __forceinline__ uint64_t umma_desc_mn_sw128(uint32_t smem_addr) {
     uint64_t d = 0;
     d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);
@@ -63,12 +64,6 @@ __device__ __forceinline__ uint64_t umma_desc_mn_sw128(uint32_t smem_addr) {
 // idesc with fp32 accumulate, bf16 operands, A K-major, B K-major (b_mn = 0) or MN-major (b_mn = 1)
 __host__ __device__ constexpr uint32_t attn_idesc(int M, int N, int b_mn) {
     return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)b_mn << 16) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
-}
-// 64 consecutive fp32 columns of this thread's TMEM lane
-__device__ __forceinline__ void tmem_ld_row64(uint32_t taddr, uint32_t (&v)[64]) {
-    tmem_ld_32x32(taddr, *reinterpret_cast<uint32_t(*)[32]>(&v[0]));
-    tmem_ld_32x32(taddr + 32, *reinterpret_cast<uint32_t(*)[32]>(&v[32]));
-    tmem_ld_wait();
 }
 __device__ __forceinline__ float ex2_approx(float x) {
     float y;
@@ -87,7 +82,7 @@ __device__ __forceinline__ AttnItem attn_item(const AttnParams& p, int item) {
 }
 
 // Bounded mbarrier wait with a suspend-time hint: the thread parks in hardware instead of spinning through the issue slots
-// the other slot's softmax warps need.
+// the softmax warps need.
 __device__ __forceinline__ bool mbar_wait_parked(uint64_t* bar, uint32_t parity, DeviceStatus* st, int where) {
 #pragma unroll 1
     for (uint32_t it = 0; it < (1u << 16); ++it) {
@@ -102,7 +97,7 @@ __device__ __forceinline__ bool mbar_wait_parked(uint64_t* bar, uint32_t parity,
     if (st) { st->code = 1; st->where = where; }
     return false;
 }
-// 32 registers per thread -> 32 consecutive fp32 columns of the thread's TMEM lane
+// 32 registers per thread <-> 32 consecutive fp32 columns of the thread's TMEM lane
 __device__ __forceinline__ void tmem_st_32x32(uint32_t taddr, const uint32_t (&v)[32]) {
     asm volatile(
         "tcgen05.st.sync.aligned.32x32b.x32.b32 [%0], "
@@ -122,6 +117,7 @@ __device__ __forceinline__ void tmem_st_32x16(uint32_t taddr, const uint32_t (&v
            "r"(v[8]), "r"(v[9]), "r"(v[10]), "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15])
         : "memory");
 }
+__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 // D[tmem] (+)= A[tmem] * B[smem]: A = 128 lanes x 16 bf16 (8 columns of bf16 pairs), lane = row
 __device__ __forceinline__ void umma_f16_ts(uint32_t tmem_d, uint32_t tmem_a, uint64_t desc_b, uint32_t idesc, uint32_t accumulate) {
     asm volatile(
@@ -131,55 +127,12 @@ __device__ __forceinline__ void umma_f16_ts(uint32_t tmem_d, uint32_t tmem_a, ui
         ::"r"(tmem_d), "r"(tmem_a), "l"(desc_b), "r"(idesc), "r"(accumulate)
         : "memory");
 }
-__device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
-
-// One softmax step of one row, in two halves.  Both walk the 32-column chunks [c0, c1) of the 128 score columns; only the first
-// `n_valid` columns counted from chunk c0 are real keys, the rest are forced to -inf (probability 0) before the common code runs.
-// Loops are kept rolled: the softmax warps sit at different program counters and share the instruction cache.
-__device__ __forceinline__ void mask_tail(uint32_t (&v)[32], int lim) {     // keep columns [0, lim) of this chunk
+__device__ __forceinline__ void tmem_ld_32x32_nowait(uint32_t taddr, uint32_t (&v)[32]) { tmem_ld_32x32(taddr, v); }
+__device__ __forceinline__ void mask_tail(uint32_t (&v)[32], int lim) {     // keep columns [0, lim) of this 32-column chunk
     if (lim < 32) {
 #pragma unroll
         for (int j = 0; j < 32; ++j) if (j >= lim) v[j] = 0xff800000u;       // -inf
     }
-}
-// row_max: new running maximum (scaled to the exp2 domain).
-__device__ __forceinline__ float row_max(uint32_t t_s, float sl2, int c0, int c1, int n_valid, float m) {
-    float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
-#pragma unroll 1
-    for (int c = c0; c < c1; ++c) {
-        uint32_t v[32];
-        tmem_ld_32x32(t_s + c * 32, v);
-        tmem_ld_wait();
-        mask_tail(v, n_valid - (c - c0) * 32);
-#pragma unroll
-        for (int j = 0; j < 32; ++j) mx4[j & 3] = fmaxf(mx4[j & 3], __uint_as_float(v[j]));
-    }
-    return fmaxf(m, fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3])) * sl2);
-}
-// 32 probabilities exp2(s * sl2 - mx) of chunk c as bf16 pairs into the row's P columns (the A operand of P V); adds them to s4.
-__device__ __forceinline__ void exp_chunk(const uint32_t (&v)[32], uint32_t t_p_chunk, float sl2, float mx, float (&s4)[4]) {
-    uint32_t w[16];
-#pragma unroll
-    for (int i = 0; i < 16; ++i) {
-        const float e0 = ex2_approx(fmaf(__uint_as_float(v[2 * i]), sl2, -mx)), e1 = ex2_approx(fmaf(__uint_as_float(v[2 * i + 1]), sl2, -mx));
-        s4[(2 * i) & 3] += e0; s4[(2 * i + 1) & 3] += e1;
-        w[i] = pack_bf16x2(e0, e1);
-    }
-    tmem_st_32x16(t_p_chunk, w);
-}
-// chunks [c0, c1) are this thread's share; `first` is the row's first chunk (where the count of real keys starts)
-__device__ __forceinline__ float row_exp(uint32_t t_s, uint32_t t_p, float sl2, int c0, int c1, int first, int n_valid, float mx) {
-    float s4[4] = {0.f, 0.f, 0.f, 0.f};
-#pragma unroll 1
-    for (int c = c0; c < c1; ++c) {
-        uint32_t v[32];
-        tmem_ld_32x32(t_s + c * 32, v);
-        tmem_ld_wait();
-        mask_tail(v, n_valid - (c - first) * 32);
-        exp_chunk(v, t_p + c * 16, sl2, mx, s4);
-    }
-    tmem_st_wait();
-    return (s4[0] + s4[1]) + (s4[2] + s4[3]);
 }
 
 // 20 warps = 5 on each of the SM's four register files (16 K registers each): 96 registers per thread is the ceiling
@@ -188,13 +141,18 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, AttnParams p) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
     uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 2 * AT_SLOT_BYTES);
-    float* lsum = reinterpret_cast<float*>(smem + 2 * AT_SLOT_BYTES + 256);
-    // per slot (stride 10): q_full, q_empty, kv_full[2], kv_empty[2], s_full, p_full, o_full (P V of a step done), o_free (per item)
-    enum { Q_FULL = 0, Q_EMPTY = 1, KV_FULL = 2, KV_EMPTY = 4, S_FULL = 6, P_FULL = 7, O_FULL = 8, O_FREE = 9, NBAR = 10 };
+    // per slot: q_full[2], q_empty[2], kv_full[STAGES], kv_empty[STAGES], s_full[2], p_full[2], o_full[2] (P V of a step done), o_free (per item).
+    // p_full is split by step parity: the scores of step g + 1 are ready early, so a fast warp may finish step g + 1 before a slow
+    // one has arrived for step g; it cannot reach step g + 2 (those scores need P of step g complete).  o_full is split the same way
+    // because the softmax warps do not wait for every P V: S_FULL(g) only proves P V(g - 2) done, so a single barrier could still
+    // be one phase behind the one a parity wait assumes.
+    enum { Q_FULL = 0, Q_EMPTY = 2, KV_FULL = 4, KV_EMPTY = 4 + AT_STAGES, S_FULL = 4 + 2 * AT_STAGES, P_FULL = S_FULL + 2,
+           O_FULL = P_FULL + 2, O_FREE = O_FULL + 2, NBAR = O_FREE + 1 };
+    static_assert(2 * NBAR * 8 + 8 <= AT_BAR_BYTES, "attention_tc: barrier area too small");
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * NBAR);
+    float* lsum = reinterpret_cast<float*>(smem + 2 * AT_SLOT_BYTES + AT_BAR_BYTES);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-    const int R = AT_ROWS / p.pack;                    // tile rows (and keys per step) per head
     const int n_pairs = (p.items + 1) >> 1;            // CTA c works on item pairs c, c + grid, ...; slot = item & 1
     const int my_pairs = blockIdx.x < n_pairs ? (n_pairs - 1 - (int)blockIdx.x) / (int)gridDim.x + 1 : 0;
     // the very last pair may hold a single item (slot 1 empty); it belongs to the CTA that owns pair n_pairs - 1
@@ -204,7 +162,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, AttnParams p) {
         tma_prefetch_desc(&tmQKV);
         for (int s = 0; s < 2; ++s) {
             uint64_t* b = bars + s * NBAR;
-            for (int i = 0; i < NBAR; ++i) mbar_init(&b[i], (i == P_FULL || i == O_FREE) ? 8 : 1);
+            for (int i = 0; i < NBAR; ++i) mbar_init(&b[i], (i == Q_EMPTY || i == Q_EMPTY + 1 || i == P_FULL || i == P_FULL + 1 || i == O_FREE) ? 8 : 1);
         }
         fence_mbar_init();
     }
@@ -215,7 +173,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, AttnParams p) {
     const uint32_t tmem_base = *tmem_slot;
 
     if (warp == 0 || warp == 18) {
-        // ---- TMA producer of one slot: Q once per item, K/V per key step through a ring of two
+        // ---- TMA producer of one slot: Q (two 64-row boxes) once per item, K and V of a step through the ring
         if (lane == 0) {
             const int s = warp == 0 ? 0 : 1;
             const int my_items = my_pairs - ((s == 1 && odd_tail) ? 1 : 0);
@@ -224,19 +182,21 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, AttnParams p) {
             bool ok = true;
             for (int li = 0, g = 0; li < my_items && ok; ++li) {
                 const AttnItem it = attn_item(p, 2 * (blockIdx.x + li * gridDim.x) + s);
-                if (!(ok = mbar_wait_parked(&b[Q_EMPTY], (li & 1) ^ 1, p.status, 31))) break;
-                mbar_arrive_expect_tx(&b[Q_FULL], AT_TILE_BYTES);
-                for (int u = 0; u < p.pack; ++u)
-                    tma_load_2d(base + u * R * 128, &tmQKV, &b[Q_FULL], (it.h0 + u) * AT_DH, it.b * p.S + it.qt * R);
+                const int qi = li & 1, row0 = it.b * p.S;
+                if (!(ok = mbar_wait_parked(&b[Q_EMPTY + qi], ((li >> 1) & 1) ^ 1, p.status, 31))) break;
+                mbar_arrive_expect_tx(&b[Q_FULL + qi], AT_Q_BYTES);
+                for (int u = 0; u < 2; ++u) {
+                    if (p.pack == 1) tma_load_2d(base + qi * AT_Q_BYTES + u * 8192, &tmQKV, &b[Q_FULL + qi], it.h0 * AT_DH, row0 + it.qt * AT_ROWS + u * 64);
+                    else tma_load_2d(base + qi * AT_Q_BYTES + u * 8192, &tmQKV, &b[Q_FULL + qi], (it.h0 + u) * AT_DH, row0);
+                }
                 for (int kt = 0; kt < p.n_kt; ++kt, ++g) {
-                    const int st = g & 1, row = it.b * p.S + kt * R;
-                    uint8_t* k_dst = base + AT_OFF_KV + st * 2 * AT_TILE_BYTES;
-                    if (!(ok = mbar_wait_parked(&b[KV_EMPTY + st], ((g >> 1) & 1) ^ 1, p.status, 32))) break;
-                    mbar_arrive_expect_tx(&b[KV_FULL + st], 2 * AT_TILE_BYTES);
-                    for (int u = 0; u < p.pack; ++u) {
-                        tma_load_2d(k_dst + u * R * 128, &tmQKV, &b[KV_FULL + st], p.d + (it.h0 + u) * AT_DH, row);
-                        tma_load_2d(k_dst + AT_TILE_BYTES + u * R * 128, &tmQKV, &b[KV_FULL + st], 2 * p.d + (it.h0 + u) * AT_DH, row);
-                    }
+                    const int st = g % AT_STAGES;
+                    const int row = p.pack == 1 ? row0 + kt * AT_KEYS : row0, col = (p.pack == 1 ? it.h0 : it.h0 + kt) * AT_DH;
+                    uint8_t* k_dst = base + AT_OFF_KV + st * 2 * AT_KV_BYTES;
+                    if (!(ok = mbar_wait_parked(&b[KV_EMPTY + st], ((g / AT_STAGES) & 1) ^ 1, p.status, 32))) break;
+                    mbar_arrive_expect_tx(&b[KV_FULL + st], 2 * AT_KV_BYTES);
+                    tma_load_2d(k_dst, &tmQKV, &b[KV_FULL + st], p.d + col, row);
+                    tma_load_2d(k_dst + AT_KV_BYTES, &tmQKV, &b[KV_FULL + st], 2 * p.d + col, row);
                 }
             }
         }
@@ -250,115 +210,133 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, AttnParams p) {
             uint8_t* base = smem + s * AT_SLOT_BYTES;
             const uint32_t tm = tmem_base + s * AT_TM_SLOT;
             bool ok = true;
-            // keys a step really holds, rounded up to the MMA's K granule (pack == 2 always runs the full tile)
-            auto keys16 = [&](int g) { const int left = p.S - (g % p.n_kt) * 128; return (p.pack == 2 || left >= 128) ? 128 : ((left + 15) & ~15); };
-            // S = Q K^T of step g; the score columns are free once P of step g - 1 was written
+            // keys a step really holds, rounded up to the MMA's K granule
+            auto keys16 = [&](int g) {
+                const int left = p.pack == 1 ? p.S - (g % p.n_kt) * AT_KEYS : p.S;
+                return left >= AT_KEYS ? AT_KEYS : ((left + 15) & ~15);
+            };
+            // S[g & 1] = Q K^T of step g; that score buffer is free once P of step g - 2 was written
             auto issue_s = [&](int g) -> bool {
-                const int kt = g % p.n_kt, st = g & 1;
-                if (kt == 0 && !mbar_wait_parked(&b[Q_FULL], (g / p.n_kt) & 1, p.status, 33)) return false;
-                if (!mbar_wait_parked(&b[KV_FULL + st], (g >> 1) & 1, p.status, 34)) return false;
+                const int kt = g % p.n_kt, item = g / p.n_kt, qi = item & 1, st = g % AT_STAGES;
+                if (kt == 0 && !mbar_wait_parked(&b[Q_FULL + qi], (item >> 1) & 1, p.status, 33)) return false;
+                if (!mbar_wait_parked(&b[KV_FULL + st], (g / AT_STAGES) & 1, p.status, 34)) return false;
                 tc_fence_after();
-                const uint64_t dq = umma_desc_sw128(smem_u32(base));
-                const uint64_t dk = umma_desc_sw128(smem_u32(base + AT_OFF_KV + st * 2 * AT_TILE_BYTES));
+                const uint64_t dq = umma_desc_sw128(smem_u32(base + qi * AT_Q_BYTES));
+                const uint64_t dk = umma_desc_sw128(smem_u32(base + AT_OFF_KV + st * 2 * AT_KV_BYTES));
                 const uint32_t idesc_s = attn_idesc(128, keys16(g), 0);
 #pragma unroll
-                for (int k = 0; k < 4; ++k) umma_f16(tm + AT_TM_S, dq + 2 * k, dk + 2 * k, idesc_s, k != 0);
-                umma_commit(&b[S_FULL]);
-                if (kt == p.n_kt - 1) umma_commit(&b[Q_EMPTY]);
+                for (int k = 0; k < 4; ++k) umma_f16(tm + AT_TM_S + (g & 1) * 64, dq + 2 * k, dk + 2 * k, idesc_s, k != 0);
+                umma_commit(&b[S_FULL + (g & 1)]);
                 return true;
             };
-            // O (+)= P V of step g, P read from TMEM; the first step of an item overwrites O, so the previous item's O must have been read out
+            // O (+)= P[g & 1] V of step g, P read from TMEM; the first step of an item overwrites O, so the previous item's O must have been read out
             auto issue_pv = [&](int g) -> bool {
-                const int st = g & 1, nk = keys16(g) >> 4, kt = g % p.n_kt, item = g / p.n_kt;
+                const int st = g % AT_STAGES, nk = keys16(g) >> 4, kt = g % p.n_kt, item = g / p.n_kt;
                 if (kt == 0 && item > 0 && !mbar_wait_parked(&b[O_FREE], (item - 1) & 1, p.status, 36)) return false;
                 tc_fence_after();
-                const uint64_t dv = umma_desc_mn_sw128(smem_u32(base + AT_OFF_KV + st * 2 * AT_TILE_BYTES + AT_TILE_BYTES));
+                const uint64_t dv = umma_desc_mn_sw128(smem_u32(base + AT_OFF_KV + st * 2 * AT_KV_BYTES + AT_KV_BYTES));
 #pragma unroll
-                for (int k = 0; k < 8; ++k) {
+                for (int k = 0; k < 4; ++k) {
                     if (k < nk)
-                        umma_f16_ts(tm + AT_TM_O, tm + AT_TM_P + k * 8, dv + (uint64_t)k * (2048 >> 4), idesc_o, (kt != 0 || k != 0) ? 1u : 0u);
+                        umma_f16_ts(tm + AT_TM_O, tm + AT_TM_P + (g & 1) * 32 + k * 8, dv + (uint64_t)k * (2048 >> 4), idesc_o, (kt != 0 || k != 0) ? 1u : 0u);
                 }
-                umma_commit(&b[O_FULL]);
+                umma_commit(&b[O_FULL + (g & 1)]);
                 umma_commit(&b[KV_EMPTY + st]);
                 return true;
             };
             if (G > 0) ok = issue_s(0);
+            if (ok && G > 1) ok = issue_s(1);
             for (int g = 0; g < G && ok; ++g) {
-                // P(g) written => the score columns are free: start S(g + 1) first so the softmax warps wait as little as possible
-                if (!(ok = mbar_wait_parked(&b[P_FULL], g & 1, p.status, 35))) break;
-                if (g + 1 < G && !(ok = issue_s(g + 1))) break;
-                ok = issue_pv(g);
+                if (!(ok = mbar_wait_parked(&b[P_FULL + (g & 1)], (g >> 1) & 1, p.status, 35))) break;
+                if (!(ok = issue_pv(g))) break;
+                if (g + 2 < G) ok = issue_s(g + 2);       // the scores of step g + 1 are already there (or on their way)
             }
         }
     } else {
-        const int s = (warp - 2) >> 3, half = ((warp - 2) >> 2) & 1, q = warp & 3, r = q * 32 + lane;   // slot, column half, lane quarter, row
-        const int hsel = r / R;                        // which head of the tile this row belongs to (0 when pack == 1)
+        // ---- softmax: slot, column half, TMEM lane quarter, tile row
+        const int s = (warp - 2) >> 3, half = ((warp - 2) >> 2) & 1, q = warp & 3, r = q * 32 + lane;
+        const int hsel = r >> 6;                       // pack == 2: which head of the pair this row belongs to
         const float sl2 = 0.125f * 1.4426950408889634f;
         const uint32_t t_lane = tmem_base + ((uint32_t)(q * 32) << 16) + s * AT_TM_SLOT;
-        const uint32_t t_s = t_lane + AT_TM_S, t_p = t_lane + AT_TM_P;
         const uint32_t t_o = t_lane + AT_TM_O + half * 32;             // this thread's 32 output columns
         uint64_t* b = bars + s * NBAR;
-        uint8_t* stage = smem + s * AT_SLOT_BYTES + AT_OFF_STAGE;
+        uint8_t* base = smem + s * AT_SLOT_BYTES;
+        float* l_mine = lsum + (s * 2 + half) * AT_ROWS + r;
+        const float* l_other = lsum + (s * 2 + (half ^ 1)) * AT_ROWS + r;
+        const int my_items = my_pairs - ((s == 1 && odd_tail) ? 1 : 0);
         if (p.pack == 2) {                                             // the other head's keys: probability 0, written once
             uint32_t z[16];
 #pragma unroll
             for (int i = 0; i < 16; ++i) z[i] = 0u;
-            tmem_st_32x16(t_p + half * 32, z);
-            tmem_st_32x16(t_p + half * 32 + 16, z);
+            tmem_st_32x16(t_lane + AT_TM_P + half * 16, z);
+            tmem_st_32x16(t_lane + AT_TM_P + 32 + half * 16, z);
             tmem_st_wait();
         }
-        float* l_mine = lsum + (s * 2 + half) * AT_ROWS + r;
-        const float* l_other = lsum + (s * 2 + (half ^ 1)) * AT_ROWS + r;
-        const int my_items = my_pairs - ((s == 1 && odd_tail) ? 1 : 0);
         int g = 0; bool ok = true;
         for (int li = 0; li < my_items && ok; ++li) {
             const AttnItem it = attn_item(p, 2 * (blockIdx.x + li * gridDim.x) + s);
-            float m = -INFINITY, l = 0.f;                           // m: reference maximum the probabilities are taken against
+            const int qi = li & 1;
+            float m = -INFINITY, l = 0.f;                               // m: reference maximum the probabilities are taken against
             for (int kt = 0; kt < p.n_kt; ++kt, ++g) {
-                if (!(ok = mbar_wait_parked(&b[S_FULL], g & 1, p.status, 37))) break;
+                if (!(ok = mbar_wait_parked(&b[S_FULL + (g & 1)], (g >> 1) & 1, p.status, 37))) break;
                 tc_fence_after();
-                int c0, c1, n_valid, e0, e1;                        // row's 32-column chunks, real keys among them; this thread's share
-                if (p.pack == 1) { n_valid = min(128, p.S - kt * 128); c0 = 0; c1 = (n_valid + 31) >> 5; e0 = 2 * half; e1 = min(c1, e0 + 2); }
-                else { n_valid = p.S; c0 = hsel * 2; c1 = c0 + 2; e0 = c0 + half; e1 = e0 + 1; }
-                const float mx = row_max(t_s, sl2, c0, c1, n_valid, m);
-                if (kt == 0) {
-                    m = mx;
-                } else {
-                    // P V of the previous step ran under the max pass; it must be done before P is overwritten or O rescaled
-                    if (!(ok = mbar_wait_parked(&b[O_FULL], (g - 1) & 1, p.status, 38))) break;
-                    const bool grow = mx - m > 8.f;
+                const int nv = p.pack == 1 ? min(AT_KEYS, p.S - kt * AT_KEYS) : (hsel == kt ? p.S : 0);   // real keys of this row in this step
+                if (nv > 0) {
+                    const uint32_t t_s = t_lane + AT_TM_S + (g & 1) * 64;
+                    uint32_t va[32], vb[32];                            // own 32 scores, the partner's 32 scores
+                    tmem_ld_32x32_nowait(t_s + half * 32, va);
+                    tmem_ld_32x32_nowait(t_s + (half ^ 1) * 32, vb);
+                    tmem_ld_wait();
+                    mask_tail(va, nv - half * 32);
+                    mask_tail(vb, nv - (half ^ 1) * 32);
+                    float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) mx4[j & 3] = fmaxf(mx4[j & 3], fmaxf(__uint_as_float(va[j]), __uint_as_float(vb[j])));
+                    const float mx = fmaxf(m, fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3])) * sl2);
+                    const bool first = m == -INFINITY;                  // nothing accumulated for this row yet
+                    const bool grow = !first && mx - m > 8.f;
                     if (__any_sync(0xffffffffu, grow)) {
+                        // rare: move the reference; P V of the previous step must have landed before O is touched
+                        if (!(ok = mbar_wait_parked(&b[O_FULL + ((g - 1) & 1)], ((g - 1) >> 1) & 1, p.status, 38))) break;
                         tc_fence_after();
                         const float alpha = grow ? ex2_approx(m - mx) : 1.f;
-                        uint32_t v[32];
-                        tmem_ld_32x32(t_o, v);
+                        tmem_ld_32x32_nowait(t_o, vb);                  // (the partner's scores are dead: reuse the registers)
                         tmem_ld_wait();
 #pragma unroll
-                        for (int c = 0; c < 32; ++c) v[c] = __float_as_uint(__uint_as_float(v[c]) * alpha);
-                        tmem_st_32x32(t_o, v);
-                        tmem_st_wait();
+                        for (int c = 0; c < 32; ++c) vb[c] = __float_as_uint(__uint_as_float(vb[c]) * alpha);
+                        tmem_st_32x32(t_o, vb);
                         l *= alpha;
-                        if (grow) m = mx;
                     }
+                    if (first || grow) m = mx;
+                    float s4[4] = {0.f, 0.f, 0.f, 0.f};
+                    uint32_t w[16];
+#pragma unroll
+                    for (int i = 0; i < 16; ++i) {
+                        const float e0 = ex2_approx(fmaf(__uint_as_float(va[2 * i]), sl2, -m)), e1 = ex2_approx(fmaf(__uint_as_float(va[2 * i + 1]), sl2, -m));
+                        s4[(2 * i) & 3] += e0; s4[(2 * i + 1) & 3] += e1;
+                        w[i] = pack_bf16x2(e0, e1);
+                    }
+                    l += (s4[0] + s4[1]) + (s4[2] + s4[3]);
+                    tmem_st_32x16(t_lane + AT_TM_P + (g & 1) * 32 + half * 16, w);
+                    tmem_st_wait();
                 }
-                l += row_exp(t_s, t_p, sl2, e0, e1, c0, n_valid, m);
                 tc_fence_before();
                 __syncwarp();
-                if (lane == 0) mbar_arrive(&b[P_FULL]);
+                if (lane == 0) mbar_arrive(&b[P_FULL + (g & 1)]);
             }
-            if (!ok || !(ok = mbar_wait_parked(&b[O_FULL], (g - 1) & 1, p.status, 39))) break;
+            if (!ok || !(ok = mbar_wait_parked(&b[O_FULL + ((g - 1) & 1)], ((g - 1) >> 1) & 1, p.status, 39))) break;
             tc_fence_after();
             // this thread's 32 output columns out of TMEM, then the O columns go back to the MMA warp
             uint32_t v[32];
-            tmem_ld_32x32(t_o, v);
+            tmem_ld_32x32_nowait(t_o, v);
             *l_mine = l;
             tmem_ld_wait();
             tc_fence_before();
-            named_bar_sync(1 + s, 256);                             // both halves of every row have published their sums
+            named_bar_sync(1 + s, 256);                                 // both halves of every row have published their sums
             if (lane == 0) mbar_arrive(&b[O_FREE]);
             const float inv = 1.f / (l + *l_other);
-            // normalise, stage the half row (64 B, swizzled), then write the warp's 32 half rows coalesced
-            uint8_t* st_row = stage + r * 128;
+            // normalise, stage the half row (64 B, swizzled) in the item's Q buffer (its MMAs are done), write 32 half rows coalesced
+            uint8_t* stage = base + qi * AT_Q_BYTES;
 #pragma unroll
             for (int i = 0; i < 4; ++i) {
                 uint4 w;
@@ -366,19 +344,21 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, AttnParams p) {
                 w.y = pack_bf16x2(__uint_as_float(v[8 * i + 2]) * inv, __uint_as_float(v[8 * i + 3]) * inv);
                 w.z = pack_bf16x2(__uint_as_float(v[8 * i + 4]) * inv, __uint_as_float(v[8 * i + 5]) * inv);
                 w.w = pack_bf16x2(__uint_as_float(v[8 * i + 6]) * inv, __uint_as_float(v[8 * i + 7]) * inv);
-                *reinterpret_cast<uint4*>(st_row + (((half * 4 + i) ^ (r & 7)) << 4)) = w;
+                *reinterpret_cast<uint4*>(stage + r * 128 + (((half * 4 + i) ^ (r & 7)) << 4)) = w;
             }
             __syncwarp();
 #pragma unroll
             for (int t = 0; t < 4; ++t) {
                 const int rr = q * 32 + t * 8 + (lane >> 2), ch = half * 4 + (lane & 3);
-                const int hs = rr / R, qrow = it.qt * R + (rr % R);
+                const int hs = p.pack == 2 ? rr >> 6 : 0, qrow = p.pack == 2 ? (rr & 63) : it.qt * AT_ROWS + rr;
                 if (qrow < p.S) {
                     const uint4 w = *reinterpret_cast<const uint4*>(stage + rr * 128 + ((ch ^ (rr & 7)) << 4));
                     *reinterpret_cast<uint4*>(p.out + (size_t)(it.b * p.S + qrow) * p.d + (it.h0 + hs) * AT_DH + ch * 8) = w;
                 }
             }
+            fence_proxy_async();                                        // the buffer goes back to the TMA producer
             __syncwarp();
+            if (lane == 0) mbar_arrive(&b[Q_EMPTY + qi]);
         }
     }
     tc_fence_before();
@@ -399,12 +379,12 @@ int launch_attention_tc(const void* qkv, void* out, int B, int S, int d, int hea
     p.S = S; p.d = d; p.heads = heads; p.B = B;
     p.pack = S <= 64 ? 2 : 1;
     p.n_qt = p.pack == 2 ? 1 : (S + AT_ROWS - 1) / AT_ROWS;
-    p.n_kt = p.n_qt;
+    p.n_kt = p.pack == 2 ? 2 : (S + AT_KEYS - 1) / AT_KEYS;
     p.items = B * (heads / p.pack) * p.n_qt;
     p.out = static_cast<__nv_bfloat16*>(out);
     p.status = status;
     CUtensorMap tm;
-    int rc = make_tmap_2d(&tm, qkv, (uint64_t)B * S, (uint64_t)3 * d, (uint64_t)3 * d * 2, AT_ROWS / p.pack, false);
+    int rc = make_tmap_2d(&tm, qkv, (uint64_t)B * S, (uint64_t)3 * d, (uint64_t)3 * d * 2, 64, false);
     if (rc) return rc;
     B200_CUDA_OK(cudaFuncSetAttribute(attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM));
     const int n_pairs = (p.items + 1) / 2;

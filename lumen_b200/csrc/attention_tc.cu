@@ -17,12 +17,12 @@
 //             grows by more than 2^8 (probabilities stay <= 256, exact in bf16/fp32 terms); then the row's O is rescaled in
 //             place (tcgen05.ld -> multiply -> tcgen05.st).  After the first key steps this is rare.
 // One persistent CTA per SM runs TWO such tiles at a time ("slots": own Q/K/V shared memory, own 256 TMEM columns, own
-// warps), independent pipelines that share the SM: warps 0 / 18 = TMA producers, warps 1 / 19 = MMA issuers,
-// warps 2..9 / 10..17 = softmax (slot 0 / 1).  TMEM per slot: S0 0..63, S1 64..127, P0 128..159, P1 160..191, O 192..255.
-// A score row is shared by TWO softmax threads (same TMEM lane, warps w and w + 4): both load the step's 64 scores and take
-// the maximum (cheap, and it keeps them in agreement without any exchange), each exponentiates 32 of them and owns 32 of
-// the row's output columns; the two partial row sums meet once per item.  The exp2 stream on the SFUs (16 per clock and
-// SM) is what bounds this kernel, not the MMAs.
+// warps), independent pipelines that share the SM: warps 0 / 10 = TMA producers, warps 1 / 11 = MMA issuers,
+// warps 2..5 / 6..9 = softmax (slot 0 / 1).  TMEM per slot: S0 0..63, S1 64..127, P0 128..159, P1 160..191, O 192..255.
+// The exp2 stream on the SFUs (16 per clock and SM) is what bounds this kernel, not the MMAs, and a scheduler only sees
+// two softmax warps (one per slot).  So the softmax thread is software-pipelined: the TMEM loads of step g + 1 (ready
+// early, thanks to the second score buffer) and its row maximum are interleaved with the exponentials of step g, and the
+// SFU pipe always has work queued while loads are in flight.
 #include "common.cuh"
 #include "kernels.h"
 
@@ -37,9 +37,9 @@ constexpr int AT_STAGES = 4;                                  // K/V ring depth 
 // per slot: Q0 | Q1 | (K V) x AT_STAGES.  The Q buffer of a finished item doubles as its output staging area.
 constexpr int AT_OFF_KV = 2 * AT_Q_BYTES, AT_SLOT_BYTES = 2 * AT_Q_BYTES + AT_STAGES * 2 * AT_KV_BYTES;
 constexpr int AT_TM_S = 0, AT_TM_P = 128, AT_TM_O = 192, AT_TM_SLOT = 256;   // TMEM columns inside a slot
-constexpr int AT_BAR_BYTES = 512, AT_LSUM_BYTES = 2 * 2 * AT_ROWS * 4;       // barriers; partial row sums [slot][half][row]
-constexpr int AT_SMEM = 2 * AT_SLOT_BYTES + AT_BAR_BYTES + AT_LSUM_BYTES + 1024;
-constexpr int AT_THREADS = 640;
+constexpr int AT_BAR_BYTES = 512;
+constexpr int AT_SMEM = 2 * AT_SLOT_BYTES + AT_BAR_BYTES + 1024;
+constexpr int AT_THREADS = 384;
 static_assert(AT_SMEM <= 227 * 1024, "attention_tc: shared memory plan exceeds one SM");
 
 struct AttnParams {
@@ -97,6 +97,14 @@ __device__ __forceinline__ bool mbar_wait_parked(uint64_t* bar, uint32_t parity,
     if (st) { st->code = 1; st->where = where; }
     return false;
 }
+// Bounded spinning wait for the latency-critical hand-offs (MMA issuer, scores of the next step)
+__device__ __forceinline__ bool mbar_wait_spin(uint64_t* bar, uint32_t parity, DeviceStatus* st, int where) {
+#pragma unroll 1
+    for (uint32_t it = 0; it < (1u << 26); ++it)
+        if (mbar_try_wait(bar, parity)) return true;
+    if (st) { st->code = 1; st->where = where; }
+    return false;
+}
 // 32 registers per thread <-> 32 consecutive fp32 columns of the thread's TMEM lane
 __device__ __forceinline__ void tmem_st_32x32(uint32_t taddr, const uint32_t (&v)[32]) {
     asm volatile(
@@ -135,7 +143,7 @@ __device__ __forceinline__ void mask_tail(uint32_t (&v)[32], int lim) {     // k
     }
 }
 
-// 20 warps = 5 on each of the SM's four register files (16 K registers each): 96 registers per thread is the ceiling
+// 12 warps = 3 on each of the SM's four register files (16 K registers each): 168 registers per thread is the ceiling
 __global__ void __launch_bounds__(AT_THREADS, 1)
 attention_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, AttnParams p) {
     extern __shared__ uint8_t smem_raw[];
@@ -150,7 +158,6 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, AttnParams p) {
            O_FULL = P_FULL + 2, O_FREE = O_FULL + 2, NBAR = O_FREE + 1 };
     static_assert(2 * NBAR * 8 + 8 <= AT_BAR_BYTES, "attention_tc: barrier area too small");
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * NBAR);
-    float* lsum = reinterpret_cast<float*>(smem + 2 * AT_SLOT_BYTES + AT_BAR_BYTES);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int n_pairs = (p.items + 1) >> 1;            // CTA c works on item pairs c, c + grid, ...; slot = item & 1
@@ -162,7 +169,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, AttnParams p) {
         tma_prefetch_desc(&tmQKV);
         for (int s = 0; s < 2; ++s) {
             uint64_t* b = bars + s * NBAR;
-            for (int i = 0; i < NBAR; ++i) mbar_init(&b[i], (i == Q_EMPTY || i == Q_EMPTY + 1 || i == P_FULL || i == P_FULL + 1 || i == O_FREE) ? 8 : 1);
+            for (int i = 0; i < NBAR; ++i) mbar_init(&b[i], (i == Q_EMPTY || i == Q_EMPTY + 1 || i == P_FULL || i == P_FULL + 1 || i == O_FREE) ? 4 : 1);
         }
         fence_mbar_init();
     }
@@ -172,7 +179,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, AttnParams p) {
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
 
-    if (warp == 0 || warp == 18) {
+    if (warp == 0 || warp == 10) {
         // ---- TMA producer of one slot: Q (two 64-row boxes) once per item, K and V of a step through the ring
         if (lane == 0) {
             const int s = warp == 0 ? 0 : 1;
@@ -200,7 +207,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, AttnParams p) {
                 }
             }
         }
-    } else if (warp == 1 || warp == 19) {
+    } else if (warp == 1 || warp == 11) {
         // ---- MMA issuer of one slot
         if (lane == 0) {
             const int s = warp == 1 ? 0 : 1;
@@ -247,109 +254,175 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, AttnParams p) {
             if (G > 0) ok = issue_s(0);
             if (ok && G > 1) ok = issue_s(1);
             for (int g = 0; g < G && ok; ++g) {
-                if (!(ok = mbar_wait_parked(&b[P_FULL + (g & 1)], (g >> 1) & 1, p.status, 35))) break;
-                if (!(ok = issue_pv(g))) break;
-                if (g + 2 < G) ok = issue_s(g + 2);       // the scores of step g + 1 are already there (or on their way)
+                if (!(ok = mbar_wait_spin(&b[P_FULL + (g & 1)], (g >> 1) & 1, p.status, 35))) break;
+                // P(g) is written, so S[g & 1] is free: the scores the softmax warps will ask for next go first
+                if (g + 2 < G && !(ok = issue_s(g + 2))) break;
+                ok = issue_pv(g);
             }
         }
     } else {
-        // ---- softmax: slot, column half, TMEM lane quarter, tile row
-        const int s = (warp - 2) >> 3, half = ((warp - 2) >> 2) & 1, q = warp & 3, r = q * 32 + lane;
+        // ---- softmax: slot, TMEM lane quarter, tile row (one thread per row)
+        const int s = (warp - 2) >> 2, q = warp & 3, r = q * 32 + lane;
         const int hsel = r >> 6;                       // pack == 2: which head of the pair this row belongs to
         const float sl2 = 0.125f * 1.4426950408889634f;
         const uint32_t t_lane = tmem_base + ((uint32_t)(q * 32) << 16) + s * AT_TM_SLOT;
-        const uint32_t t_o = t_lane + AT_TM_O + half * 32;             // this thread's 32 output columns
+        const uint32_t t_o = t_lane + AT_TM_O;
         uint64_t* b = bars + s * NBAR;
         uint8_t* base = smem + s * AT_SLOT_BYTES;
-        float* l_mine = lsum + (s * 2 + half) * AT_ROWS + r;
-        const float* l_other = lsum + (s * 2 + (half ^ 1)) * AT_ROWS + r;
         const int my_items = my_pairs - ((s == 1 && odd_tail) ? 1 : 0);
         if (p.pack == 2) {                                             // the other head's keys: probability 0, written once
             uint32_t z[16];
 #pragma unroll
             for (int i = 0; i < 16; ++i) z[i] = 0u;
-            tmem_st_32x16(t_lane + AT_TM_P + half * 16, z);
-            tmem_st_32x16(t_lane + AT_TM_P + 32 + half * 16, z);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) tmem_st_32x16(t_lane + AT_TM_P + i * 16, z);
             tmem_st_wait();
         }
         int g = 0; bool ok = true;
+        float m = 0.f, l = 0.f;                                         // m: reference maximum the probabilities are taken against
+        float s4[4];
+        // 32 probabilities exp2(s * sl2 - m) -> bf16 pairs into columns [c16, c16 + 16) of P[gg & 1]
+        auto exp32 = [&](const uint32_t (&v)[32], int gg, int c16) {
+            uint32_t w[16];
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+                const float e0 = ex2_approx(fmaf(__uint_as_float(v[2 * i]), sl2, -m)), e1 = ex2_approx(fmaf(__uint_as_float(v[2 * i + 1]), sl2, -m));
+                s4[(2 * i) & 3] += e0; s4[(2 * i + 1) & 3] += e1;
+                w[i] = pack_bf16x2(e0, e1);
+            }
+            tmem_st_32x16(t_lane + AT_TM_P + (gg & 1) * 32 + c16, w);
+        };
+        auto max32 = [&](const uint32_t (&v)[32]) {
+            float a = fmaxf(__uint_as_float(v[0]), __uint_as_float(v[1])), c = fmaxf(__uint_as_float(v[2]), __uint_as_float(v[3]));
+#pragma unroll
+            for (int j = 4; j < 32; j += 4) {
+                a = fmaxf(a, fmaxf(__uint_as_float(v[j]), __uint_as_float(v[j + 1])));
+                c = fmaxf(c, fmaxf(__uint_as_float(v[j + 2]), __uint_as_float(v[j + 3])));
+            }
+            return fmaxf(a, c);
+        };
+        auto publish = [&](int gg) {                                    // P of step gg is complete in TMEM
+            tmem_st_wait();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(&b[P_FULL + (gg & 1)]);
+        };
+        // One pipelined step (pack == 1): (lo, hi) hold the masked scores of step g and m is already valid for them; the scores of
+        // step g + 1 are fetched into (nlo, nhi) and reduced to the next maximum while the SFUs work through step g.
+        auto step = [&](uint32_t (&lo)[32], uint32_t (&hi)[32], uint32_t (&nlo)[32], uint32_t (&nhi)[32], int kt) -> bool {
+            const bool has_next = kt + 1 < p.n_kt;
+            const int nv_next = min(AT_KEYS, p.S - (kt + 1) * AT_KEYS);
+            const uint32_t t_next = t_lane + AT_TM_S + ((g + 1) & 1) * 64;
+            s4[0] = s4[1] = s4[2] = s4[3] = 0.f;
+            exp32(lo, g, 0);
+            if (has_next) {
+                // S(g + 1) was started when P(g - 1) was published, one half step ago: by now it is (nearly) there
+                if (!mbar_wait_spin(&b[S_FULL + ((g + 1) & 1)], ((g + 1) >> 1) & 1, p.status, 37)) return false;
+                tc_fence_after();
+                tmem_ld_32x32(t_next, nlo);
+                tmem_ld_32x32(t_next + 32, nhi);
+            }
+            exp32(hi, g, 16);
+            l += (s4[0] + s4[1]) + (s4[2] + s4[3]);
+            publish(g);
+            if (has_next) {
+                tmem_ld_wait();
+                mask_tail(nlo, nv_next);
+                mask_tail(nhi, nv_next - 32);
+                const float mx = fmaxf(m, fmaxf(max32(nlo), max32(nhi)) * sl2);
+                const bool grow = mx - m > 8.f;
+                if (__any_sync(0xffffffffu, grow)) {
+                    // rare: move the reference; P V of step g (just released) must land before O is touched
+                    if (!mbar_wait_parked(&b[O_FULL + (g & 1)], (g >> 1) & 1, p.status, 38)) return false;
+                    tc_fence_after();
+                    const float alpha = grow ? ex2_approx(m - mx) : 1.f;
+#pragma unroll 1
+                    for (int h = 0; h < 2; ++h) {
+                        tmem_ld_32x32(t_o + h * 32, lo);                // (step g's scores are dead: reuse the registers)
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int c = 0; c < 32; ++c) lo[c] = __float_as_uint(__uint_as_float(lo[c]) * alpha);
+                        tmem_st_32x32(t_o + h * 32, lo);
+                    }
+                    tmem_st_wait();
+                    l *= alpha;
+                    if (grow) m = mx;
+                }
+            }
+            return true;
+        };
         for (int li = 0; li < my_items && ok; ++li) {
             const AttnItem it = attn_item(p, 2 * (blockIdx.x + li * gridDim.x) + s);
             const int qi = li & 1;
-            float m = -INFINITY, l = 0.f;                               // m: reference maximum the probabilities are taken against
-            for (int kt = 0; kt < p.n_kt; ++kt, ++g) {
+            uint32_t a_lo[32], a_hi[32], b_lo[32], b_hi[32];
+            l = 0.f;
+            if (p.pack == 1) {
+                // first step of the item: load, mask, take the maximum as the reference
                 if (!(ok = mbar_wait_parked(&b[S_FULL + (g & 1)], (g >> 1) & 1, p.status, 37))) break;
                 tc_fence_after();
-                const int nv = p.pack == 1 ? min(AT_KEYS, p.S - kt * AT_KEYS) : (hsel == kt ? p.S : 0);   // real keys of this row in this step
-                if (nv > 0) {
-                    const uint32_t t_s = t_lane + AT_TM_S + (g & 1) * 64;
-                    uint32_t va[32], vb[32];                            // own 32 scores, the partner's 32 scores
-                    tmem_ld_32x32_nowait(t_s + half * 32, va);
-                    tmem_ld_32x32_nowait(t_s + (half ^ 1) * 32, vb);
-                    tmem_ld_wait();
-                    mask_tail(va, nv - half * 32);
-                    mask_tail(vb, nv - (half ^ 1) * 32);
-                    float mx4[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY};
-#pragma unroll
-                    for (int j = 0; j < 32; ++j) mx4[j & 3] = fmaxf(mx4[j & 3], fmaxf(__uint_as_float(va[j]), __uint_as_float(vb[j])));
-                    const float mx = fmaxf(m, fmaxf(fmaxf(mx4[0], mx4[1]), fmaxf(mx4[2], mx4[3])) * sl2);
-                    const bool first = m == -INFINITY;                  // nothing accumulated for this row yet
-                    const bool grow = !first && mx - m > 8.f;
-                    if (__any_sync(0xffffffffu, grow)) {
-                        // rare: move the reference; P V of the previous step must have landed before O is touched
-                        if (!(ok = mbar_wait_parked(&b[O_FULL + ((g - 1) & 1)], ((g - 1) >> 1) & 1, p.status, 38))) break;
-                        tc_fence_after();
-                        const float alpha = grow ? ex2_approx(m - mx) : 1.f;
-                        tmem_ld_32x32_nowait(t_o, vb);                  // (the partner's scores are dead: reuse the registers)
-                        tmem_ld_wait();
-#pragma unroll
-                        for (int c = 0; c < 32; ++c) vb[c] = __float_as_uint(__uint_as_float(vb[c]) * alpha);
-                        tmem_st_32x32(t_o, vb);
-                        l *= alpha;
-                    }
-                    if (first || grow) m = mx;
-                    float s4[4] = {0.f, 0.f, 0.f, 0.f};
-                    uint32_t w[16];
-#pragma unroll
-                    for (int i = 0; i < 16; ++i) {
-                        const float e0 = ex2_approx(fmaf(__uint_as_float(va[2 * i]), sl2, -m)), e1 = ex2_approx(fmaf(__uint_as_float(va[2 * i + 1]), sl2, -m));
-                        s4[(2 * i) & 3] += e0; s4[(2 * i + 1) & 3] += e1;
-                        w[i] = pack_bf16x2(e0, e1);
-                    }
-                    l += (s4[0] + s4[1]) + (s4[2] + s4[3]);
-                    tmem_st_32x16(t_lane + AT_TM_P + (g & 1) * 32 + half * 16, w);
-                    tmem_st_wait();
+                const uint32_t t_s = t_lane + AT_TM_S + (g & 1) * 64;
+                tmem_ld_32x32(t_s, a_lo);
+                tmem_ld_32x32(t_s + 32, a_hi);
+                tmem_ld_wait();
+                const int nv = min(AT_KEYS, p.S);
+                mask_tail(a_lo, nv);
+                mask_tail(a_hi, nv - 32);
+                m = fmaxf(max32(a_lo), max32(a_hi)) * sl2;
+                for (int kt = 0; kt < p.n_kt && ok; kt += 2) {
+                    if (!(ok = step(a_lo, a_hi, b_lo, b_hi, kt))) break;
+                    ++g;
+                    if (kt + 1 < p.n_kt) { if (!(ok = step(b_lo, b_hi, a_lo, a_hi, kt + 1))) break; ++g; }
                 }
-                tc_fence_before();
-                __syncwarp();
-                if (lane == 0) mbar_arrive(&b[P_FULL + (g & 1)]);
+                if (!ok) break;
+            } else {
+                // two heads per tile: step u holds the keys of head u; a row works in its own head's step only
+                for (int kt = 0; kt < 2; ++kt, ++g) {
+                    if (!(ok = mbar_wait_parked(&b[S_FULL + (g & 1)], (g >> 1) & 1, p.status, 37))) break;
+                    tc_fence_after();
+                    if (kt == hsel) {
+                        const uint32_t t_s = t_lane + AT_TM_S + (g & 1) * 64;
+                        tmem_ld_32x32(t_s, a_lo);
+                        tmem_ld_32x32(t_s + 32, a_hi);
+                        tmem_ld_wait();
+                        mask_tail(a_lo, p.S);
+                        mask_tail(a_hi, p.S - 32);
+                        m = fmaxf(max32(a_lo), max32(a_hi)) * sl2;
+                        s4[0] = s4[1] = s4[2] = s4[3] = 0.f;
+                        exp32(a_lo, g, 0);
+                        exp32(a_hi, g, 16);
+                        l = (s4[0] + s4[1]) + (s4[2] + s4[3]);
+                    }
+                    publish(g);
+                }
+                if (!ok) break;
             }
-            if (!ok || !(ok = mbar_wait_parked(&b[O_FULL + ((g - 1) & 1)], ((g - 1) >> 1) & 1, p.status, 39))) break;
+            if (!(ok = mbar_wait_parked(&b[O_FULL + ((g - 1) & 1)], ((g - 1) >> 1) & 1, p.status, 39))) break;
             tc_fence_after();
-            // this thread's 32 output columns out of TMEM, then the O columns go back to the MMA warp
-            uint32_t v[32];
-            tmem_ld_32x32_nowait(t_o, v);
-            *l_mine = l;
+            // the row's 64 output columns out of TMEM (then the O columns go back to the MMA warp), normalised, staged as one
+            // swizzled 128-byte row in the item's Q buffer (its MMAs are done)
+            const float inv = 1.f / l;
+            uint8_t* stage = base + qi * AT_Q_BYTES;
+            tmem_ld_32x32(t_o, a_lo);
+            tmem_ld_32x32(t_o + 32, a_hi);
             tmem_ld_wait();
             tc_fence_before();
-            named_bar_sync(1 + s, 256);                                 // both halves of every row have published their sums
+            __syncwarp();
             if (lane == 0) mbar_arrive(&b[O_FREE]);
-            const float inv = 1.f / (l + *l_other);
-            // normalise, stage the half row (64 B, swizzled) in the item's Q buffer (its MMAs are done), write 32 half rows coalesced
-            uint8_t* stage = base + qi * AT_Q_BYTES;
 #pragma unroll
-            for (int i = 0; i < 4; ++i) {
+            for (int i = 0; i < 8; ++i) {
+                const uint32_t (&v)[32] = i < 4 ? a_lo : a_hi;
+                const int o = (i & 3) * 8;
                 uint4 w;
-                w.x = pack_bf16x2(__uint_as_float(v[8 * i]) * inv, __uint_as_float(v[8 * i + 1]) * inv);
-                w.y = pack_bf16x2(__uint_as_float(v[8 * i + 2]) * inv, __uint_as_float(v[8 * i + 3]) * inv);
-                w.z = pack_bf16x2(__uint_as_float(v[8 * i + 4]) * inv, __uint_as_float(v[8 * i + 5]) * inv);
-                w.w = pack_bf16x2(__uint_as_float(v[8 * i + 6]) * inv, __uint_as_float(v[8 * i + 7]) * inv);
-                *reinterpret_cast<uint4*>(stage + r * 128 + (((half * 4 + i) ^ (r & 7)) << 4)) = w;
+                w.x = pack_bf16x2(__uint_as_float(v[o]) * inv, __uint_as_float(v[o + 1]) * inv);
+                w.y = pack_bf16x2(__uint_as_float(v[o + 2]) * inv, __uint_as_float(v[o + 3]) * inv);
+                w.z = pack_bf16x2(__uint_as_float(v[o + 4]) * inv, __uint_as_float(v[o + 5]) * inv);
+                w.w = pack_bf16x2(__uint_as_float(v[o + 6]) * inv, __uint_as_float(v[o + 7]) * inv);
+                *reinterpret_cast<uint4*>(stage + r * 128 + ((i ^ (r & 7)) << 4)) = w;
             }
             __syncwarp();
 #pragma unroll
-            for (int t = 0; t < 4; ++t) {
-                const int rr = q * 32 + t * 8 + (lane >> 2), ch = half * 4 + (lane & 3);
+            for (int t = 0; t < 8; ++t) {                               // the warp's 32 rows, four 128-byte rows per instruction
+                const int rr = q * 32 + t * 4 + (lane >> 3), ch = lane & 7;
                 const int hs = p.pack == 2 ? rr >> 6 : 0, qrow = p.pack == 2 ? (rr & 63) : it.qt * AT_ROWS + rr;
                 if (qrow < p.S) {
                     const uint4 w = *reinterpret_cast<const uint4*>(stage + rr * 128 + ((ch ^ (rr & 7)) << 4));

@@ -154,7 +154,10 @@ def test_layernorm_and_attention():
     for B, S, heads in ((3, 50, 12), (2, 197, 12), (1, 577, 16), (5, 17, 2), (4, 64, 4), (2, 128, 2), (2, 129, 2), (3, 257, 16),
                         (300, 50, 12), (40, 197, 12), (2, 50, 3), (1, 1, 2)):
         d = heads * 64
-        qkv = torch.randn(B * S, 3 * d, device="cuda", generator=g).to(torch.bfloat16)
+        qkv = torch.randn(B * S, 3 * d, device="cuda", generator=g)
+        if B == 40:   # keys grow along the sequence: later key steps raise the row maximum by far more than 2^8 (in-place O rescale)
+            qkv[:, d:2 * d] *= torch.linspace(0.2, 3.0, S, device="cuda").repeat(B)[:, None]
+        qkv = qkv.to(torch.bfloat16)
         out = eng.attention(qkv, B, S, d, heads)
         q, k, v = [t.view(B, S, heads, 64).transpose(1, 2) for t in qkv.float().split(d, dim=1)]
         ref = torch.softmax(q @ k.transpose(-1, -2) * 0.125, -1) @ v

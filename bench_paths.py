@@ -160,11 +160,33 @@ def bench_gemm(args):
     eng.close()
 
 
+def bench_attention(args):
+    """K5 alone through b200clip_attention on the three towers' shapes (the kernel is picked by shape)."""
+    import torch
+    from lumen_b200.engine import Engine
+    pk = peaks()
+    eng = Engine({}, device=0)
+    for name, B, S, heads in (("ViT-B-32", 512, 50, 12), ("ViT-B-16", 256, 197, 12), ("ViT-L-14-336", 128, 577, 16)):
+        d = heads * 64
+        qkv = torch.randn(B * S, 3 * d, device="cuda").to(torch.bfloat16)
+        out = torch.empty((B * S, d), dtype=torch.bfloat16, device="cuda")
+        ms = timed(lambda: eng.attention(qkv, B, S, d, heads, out=out), 20)
+        fl, ex = 4.0 * B * heads * S * S * 64, float(B) * heads * S * S
+        byt = B * S * 4 * d * 2
+        print(json.dumps({"path": "K5 attention", "model": name, "B": B, "S": S, "heads": heads, "us": ms * 1e3,
+                          "kernel": "attention_tc_kernel (tcgen05)" if S > 64 else "attention_kernel (mma.sync)",
+                          "tflops_useful": fl / ms / 1e9, "gexp_per_s": ex / ms / 1e6,
+                          "frac_of_sfu_exp2_peak": ex / ms / 1e6 / (148 * 16 * 1.92), "hbm_gbs": byt / ms / 1e6,
+                          "hbm_frac": byt / ms / 1e6 / pk["hbm_gbs"]}), flush=True)
+    eng.close()
+
+
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
-    ap.add_argument("what", choices=["preprocess", "search", "classify", "models", "gemm"])
+    ap.add_argument("what", choices=["preprocess", "search", "classify", "models", "gemm", "attention"])
     ap.add_argument("--gallery", type=int, default=1_250_000, help="total gallery rows (all GPUs)")
     ap.add_argument("--sharded", action="store_true")
     ap.add_argument("--qs", default="", help="comma-separated query counts for the search sweep")
     a = ap.parse_args()
-    {"preprocess": bench_preprocess, "search": bench_search, "classify": bench_classify, "models": bench_models, "gemm": bench_gemm}[a.what](a)
+    {"preprocess": bench_preprocess, "search": bench_search, "classify": bench_classify, "models": bench_models, "gemm": bench_gemm,
+     "attention": bench_attention}[a.what](a)

@@ -301,9 +301,10 @@ class Engine:
                                                C.c_void_p(out.data_ptr()), epilogue, activation, self._stream()))
         return out
 
-    def attention(self, qkv_bf16, B: int, S: int, width: int, heads: int):
+    def attention(self, qkv_bf16, B: int, S: int, width: int, heads: int, out=None):
         torch = _torch()
-        out = torch.empty((B * S, width), dtype=torch.bfloat16, device=qkv_bf16.device)
+        if out is None:
+            out = torch.empty((B * S, width), dtype=torch.bfloat16, device=qkv_bf16.device)
         _lib.check(self.lib.b200clip_attention(self._h, C.c_void_p(qkv_bf16.data_ptr()), C.c_void_p(out.data_ptr()), B, S, width, heads,
                                                self._stream()))
         return out

@@ -181,12 +181,47 @@ def bench_attention(args):
     eng.close()
 
 
+def bench_decode(args):
+    """P0 / N2: JPEG bytes -> device RGB (host-thread Huffman + device IDCT / upsampling / colour), against Pillow on one core."""
+    import io
+    import time
+    import torch
+    from PIL import Image
+    from lumen_b200.engine import Engine
+    pk = peaks()
+    eng = Engine({}, device=0)
+    rng = np.random.default_rng(0)
+    for (h, w, B) in ((480, 640, 128), (1080, 1920, 32)):
+        datas = []
+        for i in range(B):
+            yy, xx = np.mgrid[0:h, 0:w]
+            a = np.stack([128 + 90 * np.sin(xx / (20.0 + i)) + rng.normal(0, 10, (h, w)), 128 + 90 * np.cos(yy / (13.0 + i)) + rng.normal(0, 10, (h, w)),
+                          128 + 60 * np.sin((xx + yy) / 23.0) + rng.normal(0, 10, (h, w))], -1).clip(0, 255).astype(np.uint8)
+            buf = io.BytesIO(); Image.fromarray(a).save(buf, "JPEG", quality=85, subsampling=2); datas.append(buf.getvalue())
+        t0 = time.perf_counter()
+        for d in datas[:8]: np.asarray(Image.open(io.BytesIO(d)).convert("RGB"))
+        pil_ms = (time.perf_counter() - t0) / 8 * 1e3
+        for threads in (1, 0):
+            def run():
+                eng.decode_jpeg(datas, host_threads=threads)
+            for _ in range(2): run()
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            for _ in range(5): run()
+            torch.cuda.synchronize()
+            ms = (time.perf_counter() - t0) / 5 * 1e3
+            print(json.dumps({"path": "P0 jpeg decode", "src": f"{w}x{h} 4:2:0 q85", "batch": B, "host_threads": threads or os.cpu_count(),
+                              "ms": ms, "images_per_s": B / ms * 1e3, "mpix_per_s": B * h * w / ms / 1e3, "jpeg_mb": sum(map(len, datas)) / 1e6,
+                              "pillow_one_core_images_per_s": 1e3 / pil_ms, "timing": "wall clock around the call (host Huffman + H2D + 2 kernels)"}), flush=True)
+    eng.close()
+
+
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
-    ap.add_argument("what", choices=["preprocess", "search", "classify", "models", "gemm", "attention"])
+    ap.add_argument("what", choices=["preprocess", "search", "classify", "models", "gemm", "attention", "decode"])
     ap.add_argument("--gallery", type=int, default=1_250_000, help="total gallery rows (all GPUs)")
     ap.add_argument("--sharded", action="store_true")
     ap.add_argument("--qs", default="", help="comma-separated query counts for the search sweep")
     a = ap.parse_args()
     {"preprocess": bench_preprocess, "search": bench_search, "classify": bench_classify, "models": bench_models, "gemm": bench_gemm,
-     "attention": bench_attention}[a.what](a)
+     "attention": bench_attention, "decode": bench_decode}[a.what](a)

@@ -94,6 +94,19 @@ int b200clip_embed_u8(b200clip_handle* h, const uint8_t* src_dev, const int64_t*
 int b200clip_embed_host(b200clip_handle* h, const uint8_t* src_host, int64_t total_bytes, const int64_t* offsets,
                         const int32_t* hw, int32_t B, int32_t mode, float* emb_host, void* stream);
 
+/* P0 / N2 — JPEG bytes -> decoded RGB on the device, in front of K1.  Replaces `Image.open(io.BytesIO(b)).convert("RGB")`
+ * (backends/onnxrt_backend.py:478,412; backends/torch_backend.py:570,635), i.e. Pillow -> libjpeg-turbo defaults (islow IDCT,
+ * fancy chroma upsampling, fixed-point YCbCr->RGB), bit for bit.  jpegs[i] / lens[i]: n byte strings in host memory.  Huffman
+ * decoding runs on `host_threads` host threads (0 = all cores); IDCT, upsampling and colour conversion run on the device and
+ * write image i as H x W x 3 uint8 at dst_dev + offsets_out[i] (16-byte aligned, the layout b200clip_preprocess reads);
+ * hw_out[2i], hw_out[2i+1] = H, W; *total_out = bytes used.  status_out[i] = 0 decoded, 1 = a flavour this decoder does not
+ * cover (progressive, CMYK, 4:1:1, not a JPEG ...): nothing is written for it, hw_out is 0 and the caller decodes that image
+ * itself.  A corrupt baseline stream fails the whole call.  b200clip_jpeg_probe reads only the headers (no device work). */
+int b200clip_jpeg_probe(const void* jpeg, size_t len, int32_t* hw, int32_t* ncomp);
+int b200clip_decode_jpeg(b200clip_handle* h, const void* const* jpegs, const size_t* lens, int32_t n, uint8_t* dst_dev,
+                         int64_t dst_capacity, int64_t* offsets_out, int32_t* hw_out, int32_t* status_out, int64_t* total_out,
+                         int32_t host_threads, void* stream);
+
 /* Label / gallery upload for classify: replaces ModelResources.label_embeddings (resources/loader.py:366); rows are
  * L2-normalised once on the device (general_clip/clip_model.py:289-291 does it per call). slot 0 = labels, 1 = scenes. */
 int b200clip_set_labels(b200clip_handle* h, int32_t slot, const float* host_labels, int32_t N, int32_t D, void* stream);

@@ -162,7 +162,7 @@ class B200ClipBackend(BaseClipBackend):
             raise InvalidInputError("image_bytes cannot be empty")
         try:
             with self._lock:
-                return self._engine.embed_host([self._decode(image_bytes)], self._mode)[0]
+                return self._engine.embed_bytes([image_bytes], self._mode, host_decode=self._decode)[0]
         except Exception as e:  # noqa: BLE001
             raise InferenceError(f"Image encoding failed: {e}") from e
 
@@ -171,13 +171,12 @@ class B200ClipBackend(BaseClipBackend):
             return np.empty((0, 0), dtype=np.float32)       # onnxrt_backend.py:499-500
         self._ensure_initialized()
         try:
-            decoded = []
             for b in images:
                 if not b:
                     raise InvalidInputError("image bytes cannot be empty")
-                decoded.append(self._decode(b))
+            # baseline JPEGs are decoded on the device (bit-exact with the reference's PIL call); other formats go through PIL
             with self._lock:
-                return self._engine.embed_host(decoded, self._mode)
+                return self._engine.embed_bytes(list(images), self._mode, host_decode=self._decode)
         except Exception as e:  # noqa: BLE001
             raise InferenceError(f"Batch image encoding failed: {e}") from e
 

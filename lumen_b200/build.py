@@ -8,7 +8,7 @@ from pathlib import Path
 PKG = Path(__file__).resolve().parent
 CSRC = PKG / "csrc"
 LIB = PKG / "libb200clip.so"
-SOURCES = ["api.cu", "preprocess.cu", "gemm_tc.cu", "vit_ops.cu", "attention_tc.cu", "topk.cu", "classify.cu"]
+SOURCES = ["api.cu", "preprocess.cu", "gemm_tc.cu", "vit_ops.cu", "attention_tc.cu", "topk.cu", "classify.cu", "jpeg.cu"]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "--use_fast_math=false",
               "-Xcompiler", "-fPIC,-ffp-contract=off", "-Xptxas", "-v"]
 

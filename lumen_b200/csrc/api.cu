@@ -56,6 +56,7 @@ struct b200clip_handle {
     // search scratch
     void* topk_scratch = nullptr; size_t topk_cap = 0;
     PreprocessState* pre = nullptr;
+    JpegState* jpeg = nullptr;          // created on first decode
     DeviceStatus* status = nullptr;
     int64_t launches = 0;
     // optional per-kernel-class timing (bench.py roofline): CUDA events recorded around each launch
@@ -151,6 +152,7 @@ extern "C" void b200clip_destroy(b200clip_handle* h) {
     cudaFree(h->upload_tmp); cudaFree(h->img_dev); cudaFree(h->emb_dev); cudaFree(h->topk_scratch);
     cudaFree(h->labels[0]); cudaFree(h->labels[1]);
     if (h->pre) preprocess_state_destroy(h->pre);
+    jpeg_state_destroy(h->jpeg);
     delete h;
 }
 
@@ -466,6 +468,25 @@ extern "C" int b200clip_merge_topk(b200clip_handle* h, const float* part_scores,
     rc = merge_topk_run(part_scores, reinterpret_cast<const long long*>(part_index), parts, Q, k, out_scores,
                         reinterpret_cast<long long*>(out_index), (cudaStream_t)stream);
     if (rc == B200_OK && Q > 0) h->launches += 1;
+    return rc;
+}
+
+// ------------------------------------------------------------------------------------------ N2: JPEG decode in front of K1
+extern "C" int b200clip_jpeg_probe(const void* jpeg, size_t len, int32_t* hw, int32_t* ncomp) {
+    B200_REQUIRE(jpeg && hw && ncomp, "jpeg_probe: null argument");
+    return jpeg_probe(jpeg, len, hw, ncomp);
+}
+extern "C" int b200clip_decode_jpeg(b200clip_handle* h, const void* const* jpegs, const size_t* lens, int32_t n, uint8_t* dst_dev,
+                                    int64_t dst_capacity, int64_t* offsets_out, int32_t* hw_out, int32_t* status_out, int64_t* total_out,
+                                    int32_t host_threads, void* stream) {
+    int rc = set_device(h); if (rc) return rc;
+    B200_REQUIRE(n >= 0 && (n == 0 || (jpegs && lens && offsets_out && hw_out && status_out)) && total_out && dst_capacity >= 0, "decode_jpeg: bad argument");
+    std::lock_guard<std::mutex> lock(h->mu);
+    if (!h->jpeg) { h->jpeg = jpeg_state_create(&rc); if (!h->jpeg) return rc; }
+    int launches = 0;
+    rc = jpeg_decode_batch(h->jpeg, jpegs, lens, n, dst_dev, (size_t)dst_capacity, offsets_out, hw_out, status_out, total_out, host_threads,
+                           (cudaStream_t)stream, &launches);
+    h->launches += launches;
     return rc;
 }
 

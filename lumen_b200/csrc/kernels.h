@@ -4,6 +4,13 @@
 
 namespace b200 {
 
+struct JpegState;
+JpegState* jpeg_state_create(int* rc);
+void jpeg_state_destroy(JpegState*);
+int jpeg_probe(const void* buf, size_t len, int32_t* hw, int32_t* ncomp);
+int jpeg_decode_batch(JpegState*, const void* const* bufs, const size_t* lens, int n, void* dst, size_t dst_capacity, int64_t* offsets_out,
+                      int32_t* hw_out, int32_t* status_out, int64_t* total_out, int threads, cudaStream_t st, int* launches);
+
 struct PreprocessState;
 PreprocessState* preprocess_state_create(const float* mean, const float* stdv, int* rc);
 void preprocess_state_destroy(PreprocessState*);

@@ -68,6 +68,7 @@ class Engine:
         self._h = C.c_void_p()
         _lib.check(self.lib.b200clip_create(C.byref(c), C.byref(self._h)))
         self._pin_in = None
+        self._jpeg_dev = None
         self._pin_out = None
 
     # ------------------------------------------------------------------ lifecycle
@@ -149,6 +150,60 @@ class Engine:
         _lib.check(self.lib.b200clip_embed_u8(self._h, C.c_void_p(src_dev.data_ptr()), offsets.ctypes.data_as(C.c_void_p),
                                               hw.ctypes.data_as(C.c_void_p), B, mode, C.c_void_p(out.data_ptr()), self._stream()))
         return out
+
+    # ------------------------------------------------------------------ N2: encoded bytes -> device RGB -> embeddings
+    @staticmethod
+    def jpeg_probe(data: bytes):
+        """(H, W, components) from the headers, or None when this decoder does not cover the stream (see include/b200clip.h)."""
+        hw = (C.c_int32 * 2)()
+        nc = C.c_int32()
+        rc = _lib.load().b200clip_jpeg_probe(data, len(data), hw, C.byref(nc))
+        return (int(hw[0]), int(hw[1]), int(nc.value)) if rc == 0 else None
+
+    def decode_jpeg(self, images: Sequence[bytes], host_threads: int = 0, extra_bytes: int = 0):
+        """Baseline JPEG byte strings -> packed ragged RGB in device memory (Pillow / libjpeg-turbo exact).
+        Returns (uint8 device tensor, offsets int64[n], hw int32[n,2], status int32[n], used_bytes); status 1 marks images the
+        device decoder does not cover (nothing written, hw = 0).  `extra_bytes` reserves room behind the decoded images."""
+        torch = _torch()
+        n = len(images)
+        offsets, hw, status = np.zeros(n, np.int64), np.zeros((n, 2), np.int32), np.zeros(n, np.int32)
+        need = 16
+        for b in images:
+            info = self.jpeg_probe(b)
+            if info is not None:
+                need += (info[0] * info[1] * 3 + 15) & ~15
+        cap = need + int(extra_bytes)
+        if self._jpeg_dev is None or self._jpeg_dev.numel() < cap:
+            self._jpeg_dev = torch.empty(int(cap * 1.25), dtype=torch.uint8, device=f"cuda:{self.device}")
+        ptrs = (C.c_char_p * max(n, 1))(*images)
+        lens = (C.c_size_t * max(n, 1))(*[len(b) for b in images])
+        total = C.c_int64()
+        _lib.check(self.lib.b200clip_decode_jpeg(self._h, ptrs, lens, n, C.c_void_p(self._jpeg_dev.data_ptr()), self._jpeg_dev.numel(),
+                                                 offsets.ctypes.data_as(C.c_void_p), hw.ctypes.data_as(C.c_void_p),
+                                                 status.ctypes.data_as(C.c_void_p), C.byref(total), int(host_threads), self._stream()))
+        return self._jpeg_dev, offsets, hw, status, int(total.value)
+
+    def embed_bytes(self, images: Sequence[bytes], mode: int = MODE_SQUASH, host_decode=None, host_threads: int = 0) -> np.ndarray:
+        """image_batch_to_vectors on encoded bytes: JPEGs the device decoder covers never exist as pixels on the host; the rest
+        go through `host_decode(bytes) -> uint8 HWC` (the reference's PIL call) and are uploaded behind them."""
+        torch = _torch()
+        n = len(images)
+        if n == 0:
+            return np.empty((0, self.embed_dim), np.float32)
+        probes = [self.jpeg_probe(b) for b in images]
+        others = {i: np.array(host_decode(images[i]), dtype=np.uint8, order="C") for i in range(n) if probes[i] is None} if host_decode else {}
+        if any(p is None for p in probes) and not host_decode:
+            raise _lib.B200ClipError(-1, "embed_bytes: an image is not a baseline JPEG and no host decoder was given")
+        extra = sum(((a.size + 15) & ~15) for a in others.values())
+        dev, offsets, hw, status, used = self.decode_jpeg(images, host_threads, extra)
+        for i, a in others.items():
+            if a.ndim != 3 or a.shape[2] != 3:
+                raise _lib.B200ClipError(-1, "embed_bytes: host decoder must return H x W x 3 uint8")
+            dev[used:used + a.size].copy_(torch.from_numpy(a.reshape(-1)), non_blocking=False)
+            offsets[i], hw[i] = used, a.shape[:2]
+            used += (a.size + 15) & ~15
+        out = self.embed_u8(dev, offsets, hw, mode)
+        return out.cpu().numpy()
 
     # ------------------------------------------------------------------ host-buffer API (what the backend calls)
     def embed_host(self, images: Sequence[np.ndarray], mode: int = MODE_SQUASH) -> np.ndarray:

@@ -17,4 +17,6 @@ ncu --set full --clock-control none -k regex:"preprocess_kernel" -s 2 -c 1 -o gp
 python bench_paths.py search --qs 1,4096 > gpurun_out/plain4.log 2>&1 && \
 ncu --set full --clock-control none -k regex:"topk_tc|merge_topk" -s 2 -c 2 -o gpurun_out/search_q1_r1 python bench_paths.py search --qs 1 > gpurun_out/ncu_s1.log 2>&1
 ncu --set full --clock-control none -k regex:"topk_tc" -s 2 -c 1 -o gpurun_out/search_q4096_r1 python bench_paths.py search --qs 4096 > gpurun_out/ncu_s2.log 2>&1
+python scratch_tools/attn_one.py 128 577 16 > gpurun_out/plain5.log 2>&1 && \
+ncu --set full --clock-control none --import-source on -k regex:"attention_tc" -s 2 -c 1 -o gpurun_out/attn_l14_r1 python scratch_tools/attn_one.py 128 577 16 > gpurun_out/ncu_attn.log 2>&1
 ls -la gpurun_out

@@ -17,6 +17,7 @@ L.append("| `launches_r1.csv` | ncu `gpu__time_duration.sum` for every launch of
 L.append("| `step_r1_ncu.csv` | `--set full` metrics of the per-layer kernels (GEMM shapes, attention, LayerNorm) |")
 L.append("| `k1_resize_r1_ncu.csv`, `search_q1_r1_ncu.csv`, `search_q4096_r1_ncu.csv` | same for K1 (640x480 -> 224) and K10/K12 |")
 L.append("| `gemm_traffic_r1.json` | dram bytes per GEMM launch (feeds `roofline.traffic` in bench.py) |")
+L.append("| `attn_l14_r1_ncu.csv` | `--set full` metrics of `attention_tc_kernel` at the ViT-L/14@336 shape |")
 L.append("| `pytest_gpu.txt` | tail of `pytest -m gpu` on the same box |\n")
 r = b["roofline"]
 L.append("## Headline (`bench_r1.json`)\n")
@@ -27,15 +28,42 @@ L.append(f"* dominant kernel (tcgen05 GEMM): {r['achieved']:.0f} TFLOP/s = **{r[
          f"dram traffic per launch (ncu) {r['traffic'] / 1e6:.0f} MB.")
 L.append(f"* CPU arm (`--impl reference`, oracle port, {ref['cpu_baseline']['cores']} host threads): {ref['value']:.0f} images/s; "
          f"in-run CPU baseline {b['cpu_baseline']['value']:.0f} images/s.  Clocks during the timed region: {b['clocks']}.")
-L.append("* ncu launch list shares of one step: GEMM 0.755, attention 0.132, LayerNorm 0.094, preprocess 0.013 — agrees with the CUDA-event shares.\n")
+import collections, csv
+rows = list(csv.reader(open(P / "launches_r1.csv")))
+hi = [i for i, r in enumerate(rows) if r and r[0] == "ID"][0]
+ki, vi = rows[hi].index("Kernel Name"), rows[hi].index("Metric Value")
+agg, tot = collections.Counter(), 0.0
+for r_ in rows[hi + 2:]:
+    if len(r_) <= vi:
+        continue
+    t, n = float(r_[vi].replace(",", "")), r_[ki]
+    key = "GEMM" if "gemm_tc" in n else "attention" if "attention" in n else "LayerNorm" if ("layernorm" in n or "preln" in n) else \
+        "preprocess" if ("preprocess" in n or "convert" in n or "pull_desc" in n) else "other"
+    agg[key] += t; tot += t
+L.append("* ncu launch list (`launches_r1.csv`) shares of one step: " + ", ".join(f"{k} {v / tot:.3f}" for k, v in agg.most_common()) +
+         " — agrees with the CUDA-event shares above.\n")
 L.append("## Per-shape GEMM (`paths_r1.jsonl`, M = 25,600 token rows)\n\n| shape | N | K | epilogue | us | TFLOP/s | of sustained peak |\n|---|---|---|---|---|---|---|")
 for d in paths:
     if d.get("path") == "gemm_tc_kernel":
         L.append(f"| {d['shape']} | {d['N']} | {d['K']} | {d['epilogue']} | {d['us']:.1f} | {d['tflops']:.0f} | {d['frac_sustained']:.3f} |")
 L.append("\nHistory of this kernel in round 1 (QKV shape): 125 us (first correct version) -> 88 us (vectorised smem transpose, 8 epilogue warps) -> "
-         "78 us (epilogue through TMA stores) -> 73 us (CTA pair, `cta_group::2`).  A K sweep at N = 2304 showed a 62 us floor set by the stores "
+         "78 us (epilogue through TMA stores) -> 72 us (CTA pair, `cta_group::2`).  A K sweep at N = 2304 showed a 62 us floor set by the stores "
          "(32-byte pieces through the LSU); handing full 128-byte boxes to the TMA engine removed it.  The out-proj GEMM (N = K = 768) stays bound by the "
          "rate of the fp32 residual update (tensor reduce-add, 19.7 M elements per launch).\n")
+L.append("## K5 attention (`paths_r1.jsonl`, `attn_l14_r1_ncu.csv`)\n\n| tower | B x S x heads | kernel | us | useful TFLOP/s | G exp2/s | of the SFU exp2 rate |\n|---|---|---|---|---|---|---|")
+for d in paths:
+    if d.get("path") == "K5 attention":
+        L.append(f"| {d['model']} | {d['B']} x {d['S']} x {d['heads']} | {d['kernel']} | {d['us']:.1f} | {d['tflops_useful']:.0f} | {d['gexp_per_s']:.0f} | {d['frac_of_sfu_exp2_peak']:.3f} |")
+L.append("\n`attention_tc_kernel` history (S = 577, per layer): 963 us (mma.sync kernel) -> 525 us (first tcgen05 version, P through shared memory, "
+         "O folded in registers) -> 503 us (O in TMEM, lazy rescale) -> 493 us (P in TMEM as the A operand) -> 487 us (64-key steps, two score buffers, "
+         "pipelined softmax thread).  The softmax is bound by dependent latency, not by a saturated pipe (ncu: SFU pipe 43 %, issue slots 44 %, tensor pipe 19 %); "
+         "see DESIGN.md §7 for what is left.\n")
+L.append("## P0 JPEG decode (`paths_r1.jsonl`)\n\n| source | batch | host threads | ms | images/s | Mpixel/s | Pillow, one core, images/s |\n|---|---|---|---|---|---|---|")
+for d in paths:
+    if d.get("path") == "P0 jpeg decode":
+        L.append(f"| {d['src']} | {d['batch']} | {d['host_threads']} | {d['ms']:.1f} | {d['images_per_s']:.0f} | {d['mpix_per_s']:.0f} | {d['pillow_one_core_images_per_s']:.0f} |")
+L.append("\nWall clock around `b200clip_decode_jpeg`: Huffman decoding on the host threads dominates (the two device kernels and the coefficient upload are "
+         "a few percent of it); output is bit-identical to Pillow (tests/test_jpeg.py).\n")
 L.append("## K1 preprocess against the HBM roofline\n\n| source | batch | ms | images/s | GB/s (algorithmic) | of 6,454 GB/s |\n|---|---|---|---|---|---|")
 for d in paths:
     if d.get("path") == "K1 preprocess":

@@ -4,7 +4,8 @@ KEYS = ["Kernel Name", "Grid Size", "Block Size", "gpu__time_duration.sum", "dra
         "gpu__dram_throughput.avg.pct_of_peak_sustained_elapsed", "sm__throughput.avg.pct_of_peak_sustained_elapsed",
         "sm__pipe_tensor_cycles_active.avg.pct_of_peak_sustained_active", "sm__warps_active.avg.pct_of_peak_sustained_active",
         "launch__registers_per_thread", "sm__pipe_alu_cycles_active.avg.pct_of_peak_sustained_active",
-        "sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active", "sm__inst_executed_pipe_tmem.avg.pct_of_peak_sustained_active"]
+        "sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active", "sm__inst_executed_pipe_tmem.avg.pct_of_peak_sustained_active",
+        "sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active", "smsp__issue_active.avg.pct_of_peak_sustained_active"]
 src = sys.argv[1] if len(sys.argv) > 1 else "gpurun_out"
 out = os.path.dirname(os.path.abspath(__file__))
 for rep in sorted(glob.glob(os.path.join(src, "*_r1.ncu-rep"))):
@@ -21,3 +22,17 @@ for rep in sorted(glob.glob(os.path.join(src, "*_r1.ncu-rep"))):
         for r in rows[2:]:
             w.writerow([r[i][:70] for i in idx])
     print("wrote", name)
+
+# dram bytes per launch of the per-layer GEMM shapes -> gemm_traffic_r1.json (bench.py reports it as roofline.traffic)
+step = os.path.join(out, "step_r1_ncu.csv")
+if os.path.exists(step):
+    import json
+    rows = list(csv.reader(open(step)))
+    h = rows[0]
+    ni, ri, wi = h.index("Kernel Name"), h.index("dram__bytes_read.sum"), h.index("dram__bytes_write.sum")
+    scale = {"Mbyte": 1e6, "Gbyte": 1e9, "Kbyte": 1e3, "byte": 1.0}[rows[1][ri]]
+    per = sorted((float(r[ri]) + float(r[wi])) * scale for r in rows[2:] if "gemm_tc" in r[ni])
+    json.dump({"kernel": "gemm_tc_kernel / gemm_tc2_kernel",
+               "source": "profiles/step_r1_ncu.csv (ncu --set full, one launch each of the per-layer GEMM shapes of ViT-B/32 at batch 512)",
+               "dram_bytes_per_launch_mean": sum(per) / len(per), "per_launch": per}, open(os.path.join(out, "gemm_traffic_r1.json"), "w"), indent=1)
+    print("wrote gemm_traffic_r1.json", [round(x / 1e6) for x in per])

@@ -107,6 +107,12 @@ int b200clip_decode_jpeg(b200clip_handle* h, const void* const* jpegs, const siz
                          int64_t dst_capacity, int64_t* offsets_out, int32_t* hw_out, int32_t* status_out, int64_t* total_out,
                          int32_t host_threads, void* stream);
 
+/* N4 — gallery rows for b200clip_topk: fp32 [rows, D] in device memory -> fp16 at dst_f16_dev (the caller's gallery buffer, already
+ * offset to the first free row), divided by the row's L2 norm when normalize != 0.  Replaces the host-side
+ * `text_embeddings / np.linalg.norm(..., axis=1, keepdims=True)` of BioCLIPModelManager.initialize (expert_bioclip/bioclip_model.py:
+ * 251-256) applied to the fp32 `.npy` that ModelResources loads (lumen-resources loader.py:366). */
+int b200clip_gallery_pack(b200clip_handle* h, const float* src_dev, int64_t rows, int32_t D, int32_t normalize, void* dst_f16_dev, void* stream);
+
 /* Label / gallery upload for classify: replaces ModelResources.label_embeddings (resources/loader.py:366); rows are
  * L2-normalised once on the device (general_clip/clip_model.py:289-291 does it per call). slot 0 = labels, 1 = scenes. */
 int b200clip_set_labels(b200clip_handle* h, int32_t slot, const float* host_labels, int32_t N, int32_t D, void* stream);

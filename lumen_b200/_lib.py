@@ -39,6 +39,7 @@ SIGNATURES = {
     "b200clip_embed_host": (C.c_int, [_P, _P, _I64, _P, _P, _I32, _I32, _P, _P]),
     "b200clip_jpeg_probe": (C.c_int, [_P, C.c_size_t, _P, _P]),
     "b200clip_decode_jpeg": (C.c_int, [_P, _P, _P, _I32, _P, _I64, _P, _P, _P, _P, _I32, _P]),
+    "b200clip_gallery_pack": (C.c_int, [_P, _P, _I64, _I32, _I32, _P, _P]),
     "b200clip_set_labels": (C.c_int, [_P, _I32, _P, _I32, _I32, _P]),
     "b200clip_classify": (C.c_int, [_P, _I32, _P, _I32, _F, _I32, _I32, _P, _P, _P]),
     "b200clip_topk": (C.c_int, [_P, _P, _I32, _P, _I64, _I32, _I32, _I64, _P, _P, _P]),

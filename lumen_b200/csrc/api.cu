@@ -428,6 +428,14 @@ extern "C" int b200clip_set_labels(b200clip_handle* h, int32_t slot, const float
     return B200_OK;
 }
 
+extern "C" int b200clip_gallery_pack(b200clip_handle* h, const float* src_dev, int64_t rows, int32_t D, int32_t normalize, void* dst_f16_dev, void* stream) {
+    int rc = set_device(h); if (rc) return rc;
+    B200_REQUIRE(rows >= 0 && D > 0 && (rows == 0 || (src_dev && dst_f16_dev)), "gallery_pack: bad argument");
+    rc = launch_gallery_pack(src_dev, dst_f16_dev, rows, D, normalize, (cudaStream_t)stream);
+    if (rc == B200_OK && rows > 0) h->launches += 1;
+    return rc;
+}
+
 extern "C" int b200clip_classify(b200clip_handle* h, int32_t slot, const float* emb_dev, int32_t B, float scale, int32_t softmax,
                                  int32_t k, float* out_values_dev, int64_t* out_index_dev, void* stream) {
     int rc = set_device(h); if (rc) return rc;

@@ -22,6 +22,7 @@ int launch_layernorm(const float* x, long long row_stride, const float* g, const
 int launch_embed_preln(const float* patch, const float* cls, const float* pos, const float* g, const float* b, float* xres,
                        int B, int S, int d, float eps, cudaStream_t st);
 int launch_l2_normalize(const float* in, float* out, int rows, int D, cudaStream_t st);
+int launch_gallery_pack(const float* in, void* out_f16, long long rows, int D, int normalize, cudaStream_t st);
 int launch_attention(const void* qkv, void* out, int B, int S, int d, int heads, cudaStream_t st);
 // tcgen05 attention (attention_tc.cu): head_dim 64; S <= 64 packs two heads per tile and needs an even head count
 bool attention_tc_supported(int S, int d, int heads);

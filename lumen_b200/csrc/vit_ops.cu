@@ -91,6 +91,41 @@ __global__ void __launch_bounds__(256) l2_normalize_kernel(const float* __restri
     for (int i = lane; i < D; i += 32) out[(size_t)row * D + i] = r[i] / nrm;
 }
 
+// N4: fp32 embedding rows -> fp16 gallery rows (what K10 reads), optionally divided by their L2 norm first
+// (bioclip_model.py:251-256 normalises label matrices that are not unit length; resources/loader.py:366 loads them as fp32 .npy).
+// One warp per row; HBM-bound: 4 B in + 2 B out per element.
+__global__ void __launch_bounds__(256) gallery_pack_kernel(const float* __restrict__ in, __half* __restrict__ out, long long rows, int D, int normalize) {
+    const long long row = (long long)blockIdx.x * 8 + (threadIdx.x >> 5);
+    const int lane = threadIdx.x & 31;
+    if (row >= rows) return;
+    const float* r = in + row * D;
+    __half* o = out + row * D;
+    float inv = 1.f;
+    if (normalize) {
+        float s = 0.f;
+        for (int i = lane; i < D; i += 32) s += r[i] * r[i];
+        inv = sqrtf(warp_sum(s));
+    }
+    if ((D & 3) == 0 && ((reinterpret_cast<uintptr_t>(r) | reinterpret_cast<uintptr_t>(o)) & 15) == 0 && (D & 7) == 0) {
+        for (int i = lane * 8; i < D; i += 256) {
+            const float4 a = *reinterpret_cast<const float4*>(r + i), b = *reinterpret_cast<const float4*>(r + i + 4);
+            __half2 h0, h1, h2, h3;
+            if (normalize) {
+                h0 = __floats2half2_rn(a.x / inv, a.y / inv); h1 = __floats2half2_rn(a.z / inv, a.w / inv);
+                h2 = __floats2half2_rn(b.x / inv, b.y / inv); h3 = __floats2half2_rn(b.z / inv, b.w / inv);
+            } else {
+                h0 = __floats2half2_rn(a.x, a.y); h1 = __floats2half2_rn(a.z, a.w); h2 = __floats2half2_rn(b.x, b.y); h3 = __floats2half2_rn(b.z, b.w);
+            }
+            uint4 w;
+            w.x = *reinterpret_cast<uint32_t*>(&h0); w.y = *reinterpret_cast<uint32_t*>(&h1);
+            w.z = *reinterpret_cast<uint32_t*>(&h2); w.w = *reinterpret_cast<uint32_t*>(&h3);
+            *reinterpret_cast<uint4*>(o + i) = w;
+        }
+    } else {
+        for (int i = lane; i < D; i += 32) o[i] = __float2half_rn(normalize ? r[i] / inv : r[i]);
+    }
+}
+
 // ------------------------------------------------------------------------------------------ attention
 // softmax(Q K^T / sqrt(64)) V for one (image, head, 64-query tile), head_dim fixed at 64 (all CLIP ViTs here).
 // Flash-style: keys in tiles of 64 with an online softmax, bf16 mma.sync m16n8k16 with fp32 accumulators.
@@ -265,6 +300,12 @@ int launch_embed_preln(const float* patch, const float* cls, const float* pos, c
                        int B, int S, int d, float eps, cudaStream_t st) {
     B200_REQUIRE(d % 128 == 0 && d <= 128 * LN_MAX_V4, "embed: width must be a multiple of 128, at most 1024");
     embed_preln_kernel<<<(B * S + 7) / 8, 256, 0, st>>>(patch, cls, pos, g, b, xres, B, S, d, eps);
+    B200_CUDA_OK(cudaGetLastError());
+    return B200_OK;
+}
+int launch_gallery_pack(const float* in, void* out_f16, long long rows, int D, int normalize, cudaStream_t st) {
+    if (rows <= 0) return B200_OK;
+    gallery_pack_kernel<<<(unsigned)((rows + 7) / 8), 256, 0, st>>>(in, static_cast<__half*>(out_f16), rows, D, normalize);
     B200_CUDA_OK(cudaGetLastError());
     return B200_OK;
 }

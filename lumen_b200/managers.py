@@ -183,18 +183,18 @@ class B200BioCLIPModelManager:
                 t = np.asarray(self.text_embeddings, np.float32)
                 if t.shape[0] != len(self.labels) and t.shape[1] == len(self.labels):
                     t = t.T                                           # bioclip_model.py:294-302
+                from .gallery import DeviceGallery
                 norms = np.linalg.norm(t, axis=1, keepdims=True)
-                if not np.allclose(norms.flatten(), 1.0, atol=1e-6):
-                    t = t / norms
-                dev = f"cuda:{self.backend.engine.device}"
-                self._gallery = ShardedGallery(self.backend.engine, torch.from_numpy(np.ascontiguousarray(t.astype(np.float16))).to(dev))
+                needs = not np.allclose(norms.flatten(), 1.0, atol=1e-6)   # bioclip_model.py:251-256: only then divide
+                self._gallery = DeviceGallery(self.backend.engine, t.shape[1], capacity=t.shape[0], normalized=True)
+                self._gallery.append(t, normalize=needs)                   # fp32 -> (unit norm) -> fp16 on the device
             self.is_initialized = True
         except Exception as e:  # noqa: BLE001
             raise RuntimeError(f"Model initialization failed: {e}") from e
 
     def search_embeddings(self, emb: np.ndarray, top_k: int):
         torch = _torch()
-        q = torch.from_numpy(np.ascontiguousarray(np.atleast_2d(emb).astype(np.float16))).to(self._gallery.shard.device)
+        q = torch.from_numpy(np.ascontiguousarray(np.atleast_2d(emb).astype(np.float16))).to(self._gallery.view().device)
         s, i = self._gallery.search(q, top_k)
         return s.cpu().numpy(), i.cpu().numpy()
 

@@ -52,6 +52,20 @@ typedef struct b200clip_config {
     float   std[3];
 } b200clip_config;
 
+/* N4 — text tower shapes (CLIPTextConfig): ViT-B/32's is context 77, vocab 49408, width 512, 8 heads, 12 layers, mlp 2048, D 512. */
+typedef struct b200clip_text_config {
+    int32_t context_length;  /* tokens per sequence (77); must exceed 64 (the causal mask lives in the tcgen05 attention kernel) */
+    int32_t vocab_size;
+    int32_t width;           /* heads * 64, a multiple of 128, at most 1024 */
+    int32_t layers;
+    int32_t heads;
+    int32_t mlp_dim;
+    int32_t embed_dim;       /* D: must equal the image tower's for classify / search */
+    int32_t activation;      /* 0 = QuickGELU, 1 = exact GELU */
+    int32_t max_batch;       /* sequences per pass; larger requests are chunked */
+    float   ln_eps;
+} b200clip_text_config;
+
 /* lifecycle: BaseClipBackend.initialize()/close(), backends/base.py:126-134 */
 int  b200clip_create(const b200clip_config* cfg, b200clip_handle** out);
 void b200clip_destroy(b200clip_handle* h);
@@ -93,6 +107,17 @@ int b200clip_embed_u8(b200clip_handle* h, const uint8_t* src_dev, const int64_t*
  * synchronises. */
 int b200clip_embed_host(b200clip_handle* h, const uint8_t* src_host, int64_t total_bytes, const int64_t* offsets,
                         const int32_t* hw, int32_t B, int32_t mode, float* emb_host, void* stream);
+
+/* N4 — text tower (label-embedding bootstrap: CLIPModelManager._compute_label_embeddings, general_clip/clip_model.py:145-172, which
+ * calls backend.text_batch_to_vectors -> backends/torch_backend.py text path = CLIPTextModelWithProjection: token + position
+ * embedding, L x [LN1, causal MHA, LN2, MLP], final LN, hidden state at the EOT token (argmax of the ids), text_projection, L2 norm).
+ * b200clip_text_init adds the tower to a handle (the image tower may be absent: cfg.layers == 0); its tensors go through
+ * b200clip_load_weight under their transformers names (text_model.embeddings.token_embedding.weight, text_model.embeddings.
+ * position_embedding.weight, text_model.encoder.layers.N.*, text_model.final_layer_norm.*, text_projection.weight).
+ * b200clip_encode_text: ids_dev int32 [B, context_length] in device memory (tokenisation stays with the caller's tokenizer)
+ * -> emb_dev float32 [B, D] unit vectors. */
+int b200clip_text_init(b200clip_handle* h, const b200clip_text_config* cfg);
+int b200clip_encode_text(b200clip_handle* h, const int32_t* ids_dev, int32_t B, float* emb_dev, void* stream);
 
 /* P0 / N2 — JPEG bytes -> decoded RGB on the device, in front of K1.  Replaces `Image.open(io.BytesIO(b)).convert("RGB")`
  * (backends/onnxrt_backend.py:478,412; backends/torch_backend.py:570,635), i.e. Pillow -> libjpeg-turbo defaults (islow IDCT,
@@ -153,7 +178,7 @@ int b200clip_topk_static(const void* queries_f16_dev, int32_t Q, const void* gal
 int b200clip_gemm_bf16(b200clip_handle* h, const void* A_bf16_dev, const void* W_bf16_dev, int32_t M, int32_t N, int32_t K,
                        const float* bias_dev, void* out_dev, int32_t epilogue, int32_t activation, void* stream);
 int b200clip_attention(b200clip_handle* h, const void* qkv_bf16_dev, void* out_bf16_dev, int32_t B, int32_t S,
-                       int32_t width, int32_t heads, void* stream);
+                       int32_t width, int32_t heads, int32_t causal, void* stream);
 int b200clip_layernorm(b200clip_handle* h, const float* x_dev, const float* gamma_dev, const float* beta_dev,
                        void* out_bf16_dev, int32_t rows, int32_t width, float eps, void* stream);
 

@@ -18,6 +18,12 @@ class Config(C.Structure):
                 ("mean", C.c_float * 3), ("std", C.c_float * 3)]
 
 
+class TextConfig(C.Structure):
+    _fields_ = [("context_length", C.c_int32), ("vocab_size", C.c_int32), ("width", C.c_int32), ("layers", C.c_int32),
+                ("heads", C.c_int32), ("mlp_dim", C.c_int32), ("embed_dim", C.c_int32), ("activation", C.c_int32),
+                ("max_batch", C.c_int32), ("ln_eps", C.c_float)]
+
+
 class B200ClipError(RuntimeError):
     def __init__(self, code: int, message: str):
         super().__init__(f"libb200clip error {code}: {message}")
@@ -37,6 +43,8 @@ SIGNATURES = {
     "b200clip_encode": (C.c_int, [_P, _P, _I32, _P, _P]),
     "b200clip_embed_u8": (C.c_int, [_P, _P, _P, _P, _I32, _I32, _P, _P]),
     "b200clip_embed_host": (C.c_int, [_P, _P, _I64, _P, _P, _I32, _I32, _P, _P]),
+    "b200clip_text_init": (C.c_int, [_P, _P]),
+    "b200clip_encode_text": (C.c_int, [_P, _P, _I32, _P, _P]),
     "b200clip_jpeg_probe": (C.c_int, [_P, C.c_size_t, _P, _P]),
     "b200clip_decode_jpeg": (C.c_int, [_P, _P, _P, _I32, _P, _I64, _P, _P, _P, _P, _I32, _P]),
     "b200clip_gallery_pack": (C.c_int, [_P, _P, _I64, _I32, _I32, _P, _P]),
@@ -46,7 +54,7 @@ SIGNATURES = {
     "b200clip_topk_static": (C.c_int, [_P, _I32, _P, _I64, _I32, _I32, _I64, _P, _P, _P]),
     "b200clip_merge_topk": (C.c_int, [_P, _P, _P, _I32, _I32, _I32, _P, _P, _P]),
     "b200clip_gemm_bf16": (C.c_int, [_P, _P, _P, _I32, _I32, _I32, _P, _P, _I32, _I32, _P]),
-    "b200clip_attention": (C.c_int, [_P, _P, _P, _I32, _I32, _I32, _I32, _P]),
+    "b200clip_attention": (C.c_int, [_P, _P, _P, _I32, _I32, _I32, _I32, _I32, _P]),
     "b200clip_layernorm": (C.c_int, [_P, _P, _P, _P, _P, _I32, _I32, _F, _P]),
     "b200clip_launch_count": (_I64, [_P]),
     "b200clip_profile": (C.c_int, [_P, _I32]),

@@ -68,8 +68,12 @@ def _vit_config_for(resources) -> dict:
 class B200ClipBackend(BaseClipBackend):
     def __init__(self, resources, device_preference: str | None = None, max_batch_size: int | None = None,
                  weights: dict[str, np.ndarray] | None = None, preprocess_mode: str = "squash",
-                 text_backend: BaseClipBackend | None = None) -> None:
+                 text_backend: BaseClipBackend | None = None, text_config: dict | None = None, tokenizer=None) -> None:
+        """text_config (a TEXT_CONFIGS entry) + tokenizer (callable: list[str] -> int ids [B, context_length], e.g. open_clip's
+        tokenizer or a transformers CLIPTokenizer wrapper) put the text tower on the device too; its tensors are the text_model.* /
+        text_projection.weight entries of `weights`."""
         super().__init__(resources, device_preference, max_batch_size)
+        self._text_cfg, self._tokenizer = text_config, tokenizer
         self._weights = weights if weights is not None else getattr(resources, "weights", None)
         self._mode = MODE_SQUASH if preprocess_mode == "squash" else MODE_SHORTEST_CROP
         self._text = text_backend
@@ -107,7 +111,10 @@ class B200ClipBackend(BaseClipBackend):
                 raise ModelLoadingError("no vision-tower weights supplied (pass weights= or resources.weights)")
             self._engine = Engine(cfg, device=self._device_index, max_batch=self._max_batch_size or 512,
                                   mean=stats["mean"], std=stats["std"])
-            self._engine.load_weights(self._weights)
+            has_text = self._text_cfg is not None and any(k.startswith("text_") for k in self._weights)
+            if has_text:
+                self._engine.init_text(self._text_cfg, max_batch=min(self._max_batch_size or 256, 256))
+            self._engine.load_weights({k: v for k, v in self._weights.items() if has_text or not k.startswith("text_")})
             self._cfg = cfg
             self._initialized = True
         except ModelLoadingError:
@@ -181,13 +188,34 @@ class B200ClipBackend(BaseClipBackend):
             raise InferenceError(f"Batch image encoding failed: {e}") from e
 
     # ---------------------------------------------------------------- text (out of scope: delegated or refused)
+    def _device_text(self, texts: Sequence[str]) -> np.ndarray:
+        try:
+            ids = np.asarray(self._tokenizer(list(texts)))
+            with self._lock:
+                return self._engine.encode_text(ids)
+        except Exception as e:  # noqa: BLE001
+            raise InferenceError(f"Text encoding failed: {e}") from e
+
+    def _has_device_text(self) -> bool:
+        return self._engine is not None and self._engine.text_cfg is not None and self._tokenizer is not None
+
     def text_to_vector(self, text: str) -> np.ndarray:
+        if self._has_device_text():
+            self._ensure_initialized()
+            if not text or not text.strip():
+                raise InvalidInputError("text cannot be empty")
+            return self._device_text([text])[0]
         if self._text is not None:
             return self._text.text_to_vector(text)
         raise InferenceError("Text encoding failed: the B200 backend accelerates the image path only; "
                              "supply precomputed label embeddings or a text_backend")
 
     def text_batch_to_vectors(self, texts: Sequence[str]) -> np.ndarray:
+        if self._has_device_text():
+            self._ensure_initialized()
+            if not texts:
+                return np.empty((0, 0), dtype=np.float32)
+            return self._device_text(texts)
         if self._text is not None:
             return self._text.text_batch_to_vectors(texts)
         raise InferenceError("Batch text encoding failed: the B200 backend accelerates the image path only")

@@ -8,6 +8,7 @@
 #include <mutex>
 #include <set>
 #include <string>
+#include <type_traits>
 #include <vector>
 
 namespace b200 {
@@ -28,6 +29,21 @@ struct Layer {
     __nv_bfloat16 *w_qkv = nullptr, *w_o = nullptr, *w_fc1 = nullptr, *w_fc2 = nullptr;
     float *b_qkv = nullptr, *b_o = nullptr, *b_fc1 = nullptr, *b_fc2 = nullptr;
     float *ln1_g = nullptr, *ln1_b = nullptr, *ln2_g = nullptr, *ln2_b = nullptr;
+};
+
+// N4: the CLIP text tower (label-embedding bootstrap, general_clip/clip_model.py:145-172) living next to the image tower on the
+// same handle.  Same Layer weights and the same GEMM / LayerNorm kernels; attention is causal; pooling takes the EOT token.
+struct TextTower {
+    b200clip_text_config cfg{};
+    std::vector<void*> allocs;
+    float *tok = nullptr, *pos = nullptr, *final_g = nullptr, *final_b = nullptr;
+    __nv_bfloat16* w_proj = nullptr;
+    std::vector<Layer> layers;
+    std::set<std::string> loaded;
+    // activations for max_batch sequences
+    float *xres = nullptr, *eot = nullptr, *emb_raw = nullptr;
+    __nv_bfloat16 *hbuf = nullptr, *qkv = nullptr, *mlp = nullptr, *eot_ln = nullptr;
+    size_t want_tensors() const { return 5 + 16 * (size_t)cfg.layers; }
 };
 
 }  // namespace b200
@@ -57,6 +73,7 @@ struct b200clip_handle {
     void* topk_scratch = nullptr; size_t topk_cap = 0;
     PreprocessState* pre = nullptr;
     JpegState* jpeg = nullptr;          // created on first decode
+    TextTower* text = nullptr;          // b200clip_text_init
     DeviceStatus* status = nullptr;
     int64_t launches = 0;
     // optional per-kernel-class timing (bench.py roofline): CUDA events recorded around each launch
@@ -153,6 +170,7 @@ extern "C" void b200clip_destroy(b200clip_handle* h) {
     cudaFree(h->labels[0]); cudaFree(h->labels[1]);
     if (h->pre) preprocess_state_destroy(h->pre);
     jpeg_state_destroy(h->jpeg);
+    if (h->text) { for (void* p : h->text->allocs) cudaFree(p); delete h->text; }
     delete h;
 }
 
@@ -216,12 +234,77 @@ static int put_f32(const float* host, size_t count, float* dst) {
     return B200_OK;
 }
 
+// One tensor of a transformer layer (the image and the text tower share the layout): `t` is the key below "...layers.N."
+static int load_layer_tensor(b200clip_handle* h, Layer& l, const std::string& t, const std::string& nm, const float* data, size_t count,
+                             const int64_t* shape, int ndim, int d, int mlp) {
+    int rc = B200_OK;
+    auto want = [&](std::initializer_list<int64_t> s) {
+        if ((int)s.size() != ndim) return false;
+        int i = 0; for (int64_t v : s) if (shape[i++] != v) return false;
+        return true;
+    };
+#define SHAPE_(...) B200_REQUIRE(want({__VA_ARGS__}), "load_weight: wrong shape for " + nm)
+        const char* qkvn[3] = {"q_proj", "k_proj", "v_proj"};
+        bool done = false;
+        for (int j = 0; j < 3 && !done; ++j) {
+            if (t == std::string("self_attn.") + qkvn[j] + ".weight") { SHAPE_(d, d); rc = put_bf16(h, data, d, d, l.w_qkv + (size_t)j * d * d, d); done = true; }
+            else if (t == std::string("self_attn.") + qkvn[j] + ".bias") { SHAPE_(d); rc = put_f32(data, count, l.b_qkv + j * d); done = true; }
+        }
+        if (done) {}
+        else if (t == "self_attn.out_proj.weight") { SHAPE_(d, d); rc = put_bf16(h, data, d, d, l.w_o, d); }
+        else if (t == "self_attn.out_proj.bias") { SHAPE_(d); rc = put_f32(data, count, l.b_o); }
+        else if (t == "layer_norm1.weight") { SHAPE_(d); rc = put_f32(data, count, l.ln1_g); }
+        else if (t == "layer_norm1.bias") { SHAPE_(d); rc = put_f32(data, count, l.ln1_b); }
+        else if (t == "layer_norm2.weight") { SHAPE_(d); rc = put_f32(data, count, l.ln2_g); }
+        else if (t == "layer_norm2.bias") { SHAPE_(d); rc = put_f32(data, count, l.ln2_b); }
+        else if (t == "mlp.fc1.weight") { SHAPE_(mlp, d); rc = put_bf16(h, data, mlp, d, l.w_fc1, d); }
+        else if (t == "mlp.fc1.bias") { SHAPE_(mlp); rc = put_f32(data, count, l.b_fc1); }
+        else if (t == "mlp.fc2.weight") { SHAPE_(d, mlp); rc = put_bf16(h, data, d, mlp, l.w_fc2, mlp); }
+        else if (t == "mlp.fc2.bias") { SHAPE_(d); rc = put_f32(data, count, l.b_fc2); }
+        else return fail(B200CLIP_EINVAL, "load_weight: unknown tensor " + nm);
+#undef SHAPE_
+    return rc;
+}
+
+// text_model.* / text_projection.weight (transformers CLIPTextModelWithProjection keys)
+static int load_text_weight(b200clip_handle* h, const std::string& nm, const float* data, const int64_t* shape, int ndim) {
+    TextTower* t = h->text;
+    B200_REQUIRE(t != nullptr, "load_weight: text tensor but b200clip_text_init was not called");
+    const int d = t->cfg.width, mlp = t->cfg.mlp_dim, D = t->cfg.embed_dim, V = t->cfg.vocab_size, ctx = t->cfg.context_length;
+    size_t count = 1;
+    for (int i = 0; i < ndim; ++i) count *= (size_t)shape[i];
+    auto want = [&](std::initializer_list<int64_t> s) {
+        if ((int)s.size() != ndim) return false;
+        int i = 0; for (int64_t v : s) if (shape[i++] != v) return false;
+        return true;
+    };
+#define SHAPE_(...) B200_REQUIRE(want({__VA_ARGS__}), "load_weight: wrong shape for " + nm)
+    int rc = B200_OK;
+    const std::string LP = "text_model.encoder.layers.";
+    if (nm == "text_model.embeddings.token_embedding.weight") { SHAPE_(V, d); rc = put_f32(data, count, t->tok); }
+    else if (nm == "text_model.embeddings.position_embedding.weight") { SHAPE_(ctx, d); rc = put_f32(data, count, t->pos); }
+    else if (nm == "text_model.final_layer_norm.weight") { SHAPE_(d); rc = put_f32(data, count, t->final_g); }
+    else if (nm == "text_model.final_layer_norm.bias") { SHAPE_(d); rc = put_f32(data, count, t->final_b); }
+    else if (nm == "text_projection.weight") { SHAPE_(D, d); rc = put_bf16(h, data, D, d, t->w_proj, d); }
+    else if (nm.compare(0, LP.size(), LP) == 0) {
+        const size_t dot = nm.find('.', LP.size());
+        B200_REQUIRE(dot != std::string::npos, "load_weight: malformed layer key " + nm);
+        const int li = std::atoi(nm.substr(LP.size(), dot - LP.size()).c_str());
+        B200_REQUIRE(li >= 0 && li < t->cfg.layers, "load_weight: layer index out of range in " + nm);
+        rc = load_layer_tensor(h, t->layers[li], nm.substr(dot + 1), nm, data, count, shape, ndim, d, mlp);
+    } else return fail(B200CLIP_EINVAL, "load_weight: unknown tensor " + nm);
+#undef SHAPE_
+    if (rc == B200_OK) t->loaded.insert(nm);
+    return rc;
+}
+
 extern "C" int b200clip_load_weight(b200clip_handle* h, const char* name, const float* data, const int64_t* shape, int32_t ndim) {
     int rc = set_device(h); if (rc) return rc;
     B200_REQUIRE(name && data && shape && ndim >= 1 && ndim <= 4, "load_weight: null argument or bad rank");
-    B200_REQUIRE(h->cfg.layers > 0, "load_weight: handle was created without an encoder (layers == 0)");
     std::lock_guard<std::mutex> lk(h->mu);
     const std::string nm(name);
+    if (nm.compare(0, 5, "text_") == 0) return load_text_weight(h, nm, data, shape, ndim);
+    B200_REQUIRE(h->cfg.layers > 0, "load_weight: handle was created without an encoder (layers == 0)");
     const int d = h->cfg.width, P = h->cfg.patch, mlp = h->cfg.mlp_dim, D = h->cfg.embed_dim;
     size_t count = 1;
     for (int i = 0; i < ndim; ++i) count *= (size_t)shape[i];
@@ -245,26 +328,7 @@ extern "C" int b200clip_load_weight(b200clip_handle* h, const char* name, const 
         B200_REQUIRE(dot != std::string::npos, "load_weight: malformed layer key " + nm);
         const int li = std::atoi(nm.substr(LP.size(), dot - LP.size()).c_str());
         B200_REQUIRE(li >= 0 && li < h->cfg.layers, "load_weight: layer index out of range in " + nm);
-        Layer& l = h->layers[li];
-        const std::string t = nm.substr(dot + 1);
-        const char* qkvn[3] = {"q_proj", "k_proj", "v_proj"};
-        bool done = false;
-        for (int j = 0; j < 3 && !done; ++j) {
-            if (t == std::string("self_attn.") + qkvn[j] + ".weight") { SHAPE_(d, d); rc = put_bf16(h, data, d, d, l.w_qkv + (size_t)j * d * d, d); done = true; }
-            else if (t == std::string("self_attn.") + qkvn[j] + ".bias") { SHAPE_(d); rc = put_f32(data, count, l.b_qkv + j * d); done = true; }
-        }
-        if (done) {}
-        else if (t == "self_attn.out_proj.weight") { SHAPE_(d, d); rc = put_bf16(h, data, d, d, l.w_o, d); }
-        else if (t == "self_attn.out_proj.bias") { SHAPE_(d); rc = put_f32(data, count, l.b_o); }
-        else if (t == "layer_norm1.weight") { SHAPE_(d); rc = put_f32(data, count, l.ln1_g); }
-        else if (t == "layer_norm1.bias") { SHAPE_(d); rc = put_f32(data, count, l.ln1_b); }
-        else if (t == "layer_norm2.weight") { SHAPE_(d); rc = put_f32(data, count, l.ln2_g); }
-        else if (t == "layer_norm2.bias") { SHAPE_(d); rc = put_f32(data, count, l.ln2_b); }
-        else if (t == "mlp.fc1.weight") { SHAPE_(mlp, d); rc = put_bf16(h, data, mlp, d, l.w_fc1, d); }
-        else if (t == "mlp.fc1.bias") { SHAPE_(mlp); rc = put_f32(data, count, l.b_fc1); }
-        else if (t == "mlp.fc2.weight") { SHAPE_(d, mlp); rc = put_bf16(h, data, d, mlp, l.w_fc2, mlp); }
-        else if (t == "mlp.fc2.bias") { SHAPE_(d); rc = put_f32(data, count, l.b_fc2); }
-        else return fail(B200CLIP_EINVAL, "load_weight: unknown tensor " + nm);
+        rc = load_layer_tensor(h, h->layers[li], nm.substr(dot + 1), nm, data, count, shape, ndim, d, mlp);
     } else return fail(B200CLIP_EINVAL, "load_weight: unknown tensor " + nm);
 #undef SHAPE_
     if (rc == B200_OK) h->loaded.insert(nm);
@@ -275,6 +339,10 @@ extern "C" int b200clip_finalize_weights(b200clip_handle* h) {
     B200_REQUIRE(h != nullptr, "null handle");
     std::lock_guard<std::mutex> lk(h->mu);
     const size_t want = 8 + 16 * (size_t)h->cfg.layers;
+    if (h->text && h->text->loaded.size() != h->text->want_tensors())
+        return fail(B200CLIP_ESTATE, "finalize_weights: text tower has " + std::to_string(h->text->loaded.size()) + " of " +
+                                     std::to_string(h->text->want_tensors()) + " tensors loaded");
+    if (h->cfg.layers == 0 && h->text) { cudaFree(h->upload_tmp); h->upload_tmp = nullptr; h->upload_cap = 0; return B200_OK; }
     if (h->cfg.layers == 0 || h->loaded.size() != want)
         return fail(B200CLIP_ESTATE, "finalize_weights: " + std::to_string(h->loaded.size()) + " of " + std::to_string(want) + " tensors loaded");
     cudaFree(h->upload_tmp); h->upload_tmp = nullptr; h->upload_cap = 0;
@@ -314,7 +382,7 @@ static int encode_chunk(b200clip_handle* h, const __nv_bfloat16* patches, int B,
     for (const Layer& l : h->layers) {
         R_(timed(2, [&] { return launch_layernorm(h->xres, 1, l.ln1_g, l.ln1_b, h->hbuf, M, d, c.ln_eps, st); }));
         R_(timed(1, [&] { return gemm_bf16_tc(h->hbuf, d, l.w_qkv, d, M, 3 * d, d, l.b_qkv, h->qkv, 3 * d, EPI_BIAS_BF16, 0, h->status, st); }));
-        R_(timed(3, [&] { return attention_tc_supported(S, d, c.heads) ? launch_attention_tc(h->qkv, h->hbuf, B, S, d, c.heads, h->status, st)
+        R_(timed(3, [&] { return attention_tc_supported(S, d, c.heads) ? launch_attention_tc(h->qkv, h->hbuf, B, S, d, c.heads, 0, h->status, st)
                                                                       : launch_attention(h->qkv, h->hbuf, B, S, d, c.heads, st); }));
         R_(timed(1, [&] { return gemm_bf16_tc(h->hbuf, d, l.w_o, d, M, d, d, l.b_o, h->xres, d, EPI_BIAS_RES_F32, 0, h->status, st); }));
         R_(timed(2, [&] { return launch_layernorm(h->xres, 1, l.ln2_g, l.ln2_b, h->hbuf, M, d, c.ln_eps, st); }));
@@ -479,6 +547,86 @@ extern "C" int b200clip_merge_topk(b200clip_handle* h, const float* part_scores,
     return rc;
 }
 
+// ------------------------------------------------------------------------------------------ N4: text tower
+extern "C" int b200clip_text_init(b200clip_handle* h, const b200clip_text_config* cfg) {
+    int rc = set_device(h); if (rc) return rc;
+    B200_REQUIRE(cfg != nullptr, "text_init: null config");
+    std::lock_guard<std::mutex> lk(h->mu);
+    B200_REQUIRE(h->text == nullptr, "text_init: the handle already has a text tower");
+    const int d = cfg->width, mlp = cfg->mlp_dim, D = cfg->embed_dim, ctx = cfg->context_length, V = cfg->vocab_size;
+    B200_REQUIRE(ctx > 64 && ctx <= 4096, "text_init: context_length must be in (64, 4096] (the causal mask lives in the tcgen05 attention kernel)");
+    B200_REQUIRE(d % 128 == 0 && d <= 1024 && d == cfg->heads * 64, "text_init: width must be heads*64, a multiple of 128, at most 1024");
+    B200_REQUIRE(mlp % 64 == 0 && D > 0 && V > 0 && cfg->layers > 0 && cfg->max_batch > 0, "text_init: bad mlp_dim / embed_dim / vocab / layers / max_batch");
+    auto* t = new TextTower();
+    t->cfg = *cfg;
+    t->layers.resize(cfg->layers);
+    auto alloc = [&](auto** p, size_t count, bool zero) -> int {
+        void* q = nullptr;
+        B200_CUDA_OK(cudaMalloc(&q, count * sizeof(**p) + 256));
+        if (zero) B200_CUDA_OK(cudaMemset(q, 0, count * sizeof(**p) + 256));
+        t->allocs.push_back(q);
+        *p = reinterpret_cast<std::remove_reference_t<decltype(*p)>>(q);
+        return B200_OK;
+    };
+    auto bail = [&](int code) { for (void* p : t->allocs) cudaFree(p); delete t; return code; };
+#define A_(call) if ((rc = (call))) return bail(rc)
+    A_(alloc(&t->tok, (size_t)V * d, false)); A_(alloc(&t->pos, (size_t)ctx * d, false));
+    A_(alloc(&t->final_g, d, false)); A_(alloc(&t->final_b, d, false)); A_(alloc(&t->w_proj, (size_t)D * d, false));
+    for (auto& l : t->layers) {
+        A_(alloc(&l.w_qkv, (size_t)3 * d * d, false)); A_(alloc(&l.b_qkv, 3 * d, false));
+        A_(alloc(&l.w_o, (size_t)d * d, false)); A_(alloc(&l.b_o, d, false));
+        A_(alloc(&l.w_fc1, (size_t)mlp * d, false)); A_(alloc(&l.b_fc1, mlp, false));
+        A_(alloc(&l.w_fc2, (size_t)d * mlp, false)); A_(alloc(&l.b_fc2, d, false));
+        A_(alloc(&l.ln1_g, d, false)); A_(alloc(&l.ln1_b, d, false)); A_(alloc(&l.ln2_g, d, false)); A_(alloc(&l.ln2_b, d, false));
+    }
+    const size_t Bm = cfg->max_batch, M = Bm * ctx;
+    A_(alloc(&t->xres, M * d, false)); A_(alloc(&t->hbuf, M * d, true)); A_(alloc(&t->qkv, M * 3 * d, true)); A_(alloc(&t->mlp, M * mlp, true));
+    A_(alloc(&t->eot, Bm * d, false)); A_(alloc(&t->eot_ln, Bm * d, true)); A_(alloc(&t->emb_raw, Bm * D, false));
+#undef A_
+    h->text = t;
+    return B200_OK;
+}
+
+static int encode_text_chunk(b200clip_handle* h, const int32_t* ids_dev, int B, float* emb_out, cudaStream_t st) {
+    TextTower* t = h->text;
+    const b200clip_text_config& c = t->cfg;
+    const int d = c.width, S = c.context_length, M = B * S, mlp = c.mlp_dim, D = c.embed_dim;
+    int rc;
+#define R_(call) if ((rc = (call))) return rc
+    R_(launch_text_embed(ids_dev, t->tok, t->pos, t->xres, M, S, d, c.vocab_size, st));
+    for (const Layer& l : t->layers) {
+        R_(launch_layernorm(t->xres, 1, l.ln1_g, l.ln1_b, t->hbuf, M, d, c.ln_eps, st));
+        R_(gemm_bf16_tc(t->hbuf, d, l.w_qkv, d, M, 3 * d, d, l.b_qkv, t->qkv, 3 * d, EPI_BIAS_BF16, 0, h->status, st));
+        R_(launch_attention_tc(t->qkv, t->hbuf, B, S, d, c.heads, /*causal*/ 1, h->status, st));
+        R_(gemm_bf16_tc(t->hbuf, d, l.w_o, d, M, d, d, l.b_o, t->xres, d, EPI_BIAS_RES_F32, 0, h->status, st));
+        R_(launch_layernorm(t->xres, 1, l.ln2_g, l.ln2_b, t->hbuf, M, d, c.ln_eps, st));
+        R_(gemm_bf16_tc(t->hbuf, d, l.w_fc1, d, M, mlp, d, l.b_fc1, t->mlp, mlp, EPI_BIAS_ACT_BF16, c.activation, h->status, st));
+        R_(gemm_bf16_tc(t->mlp, mlp, l.w_fc2, mlp, M, d, mlp, l.b_fc2, t->xres, d, EPI_BIAS_RES_F32, 0, h->status, st));
+    }
+    R_(launch_text_eot_gather(ids_dev, t->xres, t->eot, B, S, d, st));
+    R_(launch_layernorm(t->eot, 1, t->final_g, t->final_b, t->eot_ln, B, d, c.ln_eps, st));
+    R_(gemm_bf16_tc(t->eot_ln, d, t->w_proj, d, B, D, d, nullptr, t->emb_raw, D, EPI_F32, 0, h->status, st));
+    R_(launch_l2_normalize(t->emb_raw, emb_out, B, D, st));
+#undef R_
+    h->launches += 5 + 7 * (int64_t)t->layers.size();
+    return B200_OK;
+}
+
+extern "C" int b200clip_encode_text(b200clip_handle* h, const int32_t* ids_dev, int32_t B, float* emb_dev, void* stream) {
+    int rc = set_device(h); if (rc) return rc;
+    std::lock_guard<std::mutex> lk(h->mu);
+    B200_REQUIRE(h->text != nullptr, "encode_text: b200clip_text_init was not called");
+    if (h->text->loaded.size() != h->text->want_tensors())
+        return fail(B200CLIP_ESTATE, "encode_text: text tower weights are not fully loaded");
+    B200_REQUIRE(B >= 0 && (B == 0 || (ids_dev && emb_dev)), "encode_text: null buffer");
+    const int mb = h->text->cfg.max_batch, ctx = h->text->cfg.context_length;
+    for (int b0 = 0; b0 < B; b0 += mb) {
+        const int nb = std::min(mb, B - b0);
+        if ((rc = encode_text_chunk(h, ids_dev + (size_t)b0 * ctx, nb, emb_dev + (size_t)b0 * h->text->cfg.embed_dim, (cudaStream_t)stream))) return rc;
+    }
+    return B200_OK;
+}
+
 // ------------------------------------------------------------------------------------------ N2: JPEG decode in front of K1
 extern "C" int b200clip_jpeg_probe(const void* jpeg, size_t len, int32_t* hw, int32_t* ncomp) {
     B200_REQUIRE(jpeg && hw && ncomp, "jpeg_probe: null argument");
@@ -507,10 +655,12 @@ extern "C" int b200clip_gemm_bf16(b200clip_handle* h, const void* A, const void*
     if (rc == B200_OK) h->launches += 1;
     return rc;
 }
-extern "C" int b200clip_attention(b200clip_handle* h, const void* qkv, void* out, int32_t B, int32_t S, int32_t width, int32_t heads, void* stream) {
+extern "C" int b200clip_attention(b200clip_handle* h, const void* qkv, void* out, int32_t B, int32_t S, int32_t width, int32_t heads, int32_t causal,
+                                  void* stream) {
     int rc = set_device(h); if (rc) return rc;
-    rc = attention_tc_supported(S, width, heads) ? launch_attention_tc(qkv, out, B, S, width, heads, h->status, (cudaStream_t)stream)
-                                               : launch_attention(qkv, out, B, S, width, heads, (cudaStream_t)stream);
+    B200_REQUIRE(!causal || (S > 64 && width == heads * 64), "attention: the causal mask needs S > 64 and head_dim 64 (tcgen05 kernel)");
+    rc = (causal || attention_tc_supported(S, width, heads)) ? launch_attention_tc(qkv, out, B, S, width, heads, causal, h->status, (cudaStream_t)stream)
+                                                             : launch_attention(qkv, out, B, S, width, heads, (cudaStream_t)stream);
     if (rc == B200_OK) h->launches += 1;
     return rc;
 }

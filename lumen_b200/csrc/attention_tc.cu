@@ -47,6 +47,7 @@ struct AttnParams {
     int pack;            // heads per tile (1 or 2)
     int n_qt, n_kt;      // query tiles per (image, head group), key steps per item
     int items;
+    int causal;          // 1: key j is visible to query i only when j <= i (text tower); pack == 1 only
     __nv_bfloat16* out;  // [B*S, d]
     DeviceStatus* status;
 };
@@ -309,9 +310,10 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, AttnParams p) {
         };
         // One pipelined step (pack == 1): (lo, hi) hold the masked scores of step g and m is already valid for them; the scores of
         // step g + 1 are fetched into (nlo, nhi) and reduced to the next maximum while the SFUs work through step g.
-        auto step = [&](uint32_t (&lo)[32], uint32_t (&hi)[32], uint32_t (&nlo)[32], uint32_t (&nhi)[32], int kt) -> bool {
+        auto step = [&](uint32_t (&lo)[32], uint32_t (&hi)[32], uint32_t (&nlo)[32], uint32_t (&nhi)[32], int kt, int qrow) -> bool {
             const bool has_next = kt + 1 < p.n_kt;
-            const int nv_next = min(AT_KEYS, p.S - (kt + 1) * AT_KEYS);
+            int nv_next = min(AT_KEYS, p.S - (kt + 1) * AT_KEYS);
+            if (p.causal) nv_next = min(nv_next, qrow + 1 - (kt + 1) * AT_KEYS);   // may be <= 0: the whole step is masked for this row
             const uint32_t t_next = t_lane + AT_TM_S + ((g + 1) & 1) * 64;
             s4[0] = s4[1] = s4[2] = s4[3] = 0.f;
             exp32(lo, g, 0);
@@ -364,14 +366,15 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, AttnParams p) {
                 tmem_ld_32x32(t_s, a_lo);
                 tmem_ld_32x32(t_s + 32, a_hi);
                 tmem_ld_wait();
-                const int nv = min(AT_KEYS, p.S);
+                const int qrow = it.qt * AT_ROWS + r;
+                const int nv = p.causal ? min(min(AT_KEYS, p.S), qrow + 1) : min(AT_KEYS, p.S);
                 mask_tail(a_lo, nv);
                 mask_tail(a_hi, nv - 32);
                 m = fmaxf(max32(a_lo), max32(a_hi)) * sl2;
                 for (int kt = 0; kt < p.n_kt && ok; kt += 2) {
-                    if (!(ok = step(a_lo, a_hi, b_lo, b_hi, kt))) break;
+                    if (!(ok = step(a_lo, a_hi, b_lo, b_hi, kt, qrow))) break;
                     ++g;
-                    if (kt + 1 < p.n_kt) { if (!(ok = step(b_lo, b_hi, a_lo, a_hi, kt + 1))) break; ++g; }
+                    if (kt + 1 < p.n_kt) { if (!(ok = step(b_lo, b_hi, a_lo, a_hi, kt + 1, qrow))) break; ++g; }
                 }
                 if (!ok) break;
             } else {
@@ -446,14 +449,16 @@ bool attention_tc_supported(int S, int d, int heads) {
     return S > 64 || (on >= 2 && (heads % 2) == 0);
 }
 
-int launch_attention_tc(const void* qkv, void* out, int B, int S, int d, int heads, DeviceStatus* status, cudaStream_t st) {
+int launch_attention_tc(const void* qkv, void* out, int B, int S, int d, int heads, int causal, DeviceStatus* status, cudaStream_t st) {
     if (B <= 0) return B200_OK;
+    B200_REQUIRE(!causal || S > AT_KEYS, "attention_tc: the causal mask is implemented for S > 64 only");
     AttnParams p;
     p.S = S; p.d = d; p.heads = heads; p.B = B;
     p.pack = S <= 64 ? 2 : 1;
     p.n_qt = p.pack == 2 ? 1 : (S + AT_ROWS - 1) / AT_ROWS;
     p.n_kt = p.pack == 2 ? 2 : (S + AT_KEYS - 1) / AT_KEYS;
     p.items = B * (heads / p.pack) * p.n_qt;
+    p.causal = causal ? 1 : 0;
     p.out = static_cast<__nv_bfloat16*>(out);
     p.status = status;
     CUtensorMap tm;

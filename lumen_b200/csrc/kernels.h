@@ -22,11 +22,13 @@ int launch_layernorm(const float* x, long long row_stride, const float* g, const
 int launch_embed_preln(const float* patch, const float* cls, const float* pos, const float* g, const float* b, float* xres,
                        int B, int S, int d, float eps, cudaStream_t st);
 int launch_l2_normalize(const float* in, float* out, int rows, int D, cudaStream_t st);
+int launch_text_embed(const int* ids, const float* tok, const float* pos, float* x, int rows, int ctx, int d, int vocab, cudaStream_t st);
+int launch_text_eot_gather(const int* ids, const float* x, float* out, int B, int ctx, int d, cudaStream_t st);
 int launch_gallery_pack(const float* in, void* out_f16, long long rows, int D, int normalize, cudaStream_t st);
 int launch_attention(const void* qkv, void* out, int B, int S, int d, int heads, cudaStream_t st);
 // tcgen05 attention (attention_tc.cu): head_dim 64; S <= 64 packs two heads per tile and needs an even head count
 bool attention_tc_supported(int S, int d, int heads);
-int launch_attention_tc(const void* qkv, void* out, int B, int S, int d, int heads, DeviceStatus* status, cudaStream_t st);
+int launch_attention_tc(const void* qkv, void* out, int B, int S, int d, int heads, int causal, DeviceStatus* status, cudaStream_t st);
 struct TopkPlan { int splits, qtiles, cpl; long long rows_per_split; size_t cand_bytes, part_bytes, qstage_bytes; };
 int topk_plan(int Q, long long N, int k, TopkPlan* plan);
 int topk_run(const void* queries, const void* gallery, int Q, long long N, int D, int k, long long index_base, void* scratch,

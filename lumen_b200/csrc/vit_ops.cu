@@ -4,6 +4,8 @@
 #include "common.cuh"
 #include "kernels.h"
 
+#include <climits>
+
 namespace b200 {
 
 // ------------------------------------------------------------------------------------------ LayerNorm
@@ -89,6 +91,38 @@ __global__ void __launch_bounds__(256) l2_normalize_kernel(const float* __restri
     for (int i = lane; i < D; i += 32) s += r[i] * r[i];
     const float nrm = sqrtf(warp_sum(s));
     for (int i = lane; i < D; i += 32) out[(size_t)row * D + i] = r[i] / nrm;
+}
+
+// N4 text tower (modeling_clip.py:CLIPTextEmbeddings): x[b, s] = token_embedding[ids[b, s]] + position_embedding[s], fp32 residual stream.
+// One warp per token row; ids outside the vocabulary are clamped (the host wrapper validates them).
+__global__ void __launch_bounds__(256) text_embed_kernel(const int* __restrict__ ids, const float* __restrict__ tok, const float* __restrict__ pos,
+                                                         float* __restrict__ x, int rows, int ctx, int d, int vocab) {
+    const int row = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (row >= rows) return;
+    const int id = min(max(ids[row], 0), vocab - 1);
+    const float4* t = reinterpret_cast<const float4*>(tok + (size_t)id * d);
+    const float4* p = reinterpret_cast<const float4*>(pos + (size_t)(row % ctx) * d);
+    float4* o = reinterpret_cast<float4*>(x + (size_t)row * d);
+    for (int i = lane; i < d / 4; i += 32) {
+        const float4 a = __ldg(t + i), b = __ldg(p + i);
+        o[i] = make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w);
+    }
+}
+// Pooling of the text tower: the hidden state at the end-of-text token, i.e. at argmax(ids) (first maximum, as torch.argmax;
+// the EOT id is the largest id of the CLIP vocabulary) -> compact [B, d] rows.  One warp per sequence.
+__global__ void __launch_bounds__(256) text_eot_gather_kernel(const int* __restrict__ ids, const float* __restrict__ x, float* __restrict__ out,
+                                                              int B, int ctx, int d) {
+    const int b = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    if (b >= B) return;
+    int best = INT_MIN, at = 0;
+    for (int s = lane; s < ctx; s += 32) { const int v = ids[b * ctx + s]; if (v > best) { best = v; at = s; } }
+    for (int o = 16; o; o >>= 1) {
+        const int ob = __shfl_xor_sync(0xffffffffu, best, o), oa = __shfl_xor_sync(0xffffffffu, at, o);
+        if (ob > best || (ob == best && oa < at)) { best = ob; at = oa; }
+    }
+    const float4* src = reinterpret_cast<const float4*>(x + ((size_t)b * ctx + at) * d);
+    float4* dst = reinterpret_cast<float4*>(out + (size_t)b * d);
+    for (int i = lane; i < d / 4; i += 32) dst[i] = src[i];
 }
 
 // N4: fp32 embedding rows -> fp16 gallery rows (what K10 reads), optionally divided by their L2 norm first
@@ -300,6 +334,18 @@ int launch_embed_preln(const float* patch, const float* cls, const float* pos, c
                        int B, int S, int d, float eps, cudaStream_t st) {
     B200_REQUIRE(d % 128 == 0 && d <= 128 * LN_MAX_V4, "embed: width must be a multiple of 128, at most 1024");
     embed_preln_kernel<<<(B * S + 7) / 8, 256, 0, st>>>(patch, cls, pos, g, b, xres, B, S, d, eps);
+    B200_CUDA_OK(cudaGetLastError());
+    return B200_OK;
+}
+int launch_text_embed(const int* ids, const float* tok, const float* pos, float* x, int rows, int ctx, int d, int vocab, cudaStream_t st) {
+    if (rows <= 0) return B200_OK;
+    text_embed_kernel<<<(rows + 7) / 8, 256, 0, st>>>(ids, tok, pos, x, rows, ctx, d, vocab);
+    B200_CUDA_OK(cudaGetLastError());
+    return B200_OK;
+}
+int launch_text_eot_gather(const int* ids, const float* x, float* out, int B, int ctx, int d, cudaStream_t st) {
+    if (B <= 0) return B200_OK;
+    text_eot_gather_kernel<<<(B + 7) / 8, 256, 0, st>>>(ids, x, out, B, ctx, d);
     B200_CUDA_OK(cudaGetLastError());
     return B200_OK;
 }

@@ -68,6 +68,7 @@ class Engine:
         self._h = C.c_void_p()
         _lib.check(self.lib.b200clip_create(C.byref(c), C.byref(self._h)))
         self._pin_in = None
+        self.text_cfg = None
         self._jpeg_dev = None
         self._pin_out = None
 
@@ -113,6 +114,36 @@ class Engine:
             shape = (C.c_int64 * a.ndim)(*a.shape)
             _lib.check(self.lib.b200clip_load_weight(self._h, name.encode(), a.ctypes.data_as(C.c_void_p), shape, a.ndim))
         _lib.check(self.lib.b200clip_finalize_weights(self._h))
+
+    # ------------------------------------------------------------------ N4: text tower
+    def init_text(self, cfg: dict, max_batch: int = 256) -> None:
+        """Adds a CLIP text tower (TEXT_CONFIGS entry) to this engine; weights follow through load_weights (text_model.* keys)."""
+        c = _lib.TextConfig()
+        c.context_length, c.vocab_size, c.width, c.layers = cfg["context_length"], cfg["vocab_size"], cfg["width"], cfg["layers"]
+        c.heads, c.mlp_dim, c.embed_dim = cfg["heads"], cfg["mlp_dim"], cfg["embed_dim"]
+        c.activation = 0 if cfg.get("activation", "quick_gelu") == "quick_gelu" else 1
+        c.max_batch, c.ln_eps = int(max_batch), float(cfg.get("ln_eps", 1e-5))
+        _lib.check(self.lib.b200clip_text_init(self._h, C.byref(c)))
+        self.text_cfg = dict(cfg)
+
+    def encode_text(self, ids) -> "np.ndarray":
+        """Token ids int [B, context_length] (numpy or cuda tensor) -> float32 [B, D] unit vectors (numpy)."""
+        torch = _torch()
+        if getattr(self, "text_cfg", None) is None:
+            raise _lib.B200ClipError(-3, "encode_text: init_text was not called")
+        if not isinstance(ids, torch.Tensor):
+            ids = torch.from_numpy(np.ascontiguousarray(ids, dtype=np.int32))
+        if ids.ndim != 2 or ids.shape[1] != self.text_cfg["context_length"]:
+            raise _lib.B200ClipError(-1, f"encode_text: ids must be [B, {self.text_cfg['context_length']}]")
+        if ids.shape[0] == 0:
+            return np.empty((0, self.text_cfg["embed_dim"]), np.float32)
+        if int(ids.min()) < 0 or int(ids.max()) >= self.text_cfg["vocab_size"]:
+            raise _lib.B200ClipError(-1, "encode_text: token id outside the vocabulary")
+        ids = ids.to(device=f"cuda:{self.device}", dtype=torch.int32).contiguous()
+        B = int(ids.shape[0])
+        out = torch.empty((B, self.text_cfg["embed_dim"]), dtype=torch.float32, device=ids.device)
+        _lib.check(self.lib.b200clip_encode_text(self._h, C.c_void_p(ids.data_ptr()), B, C.c_void_p(out.data_ptr()), self._stream()))
+        return out.cpu().numpy()
 
     # ------------------------------------------------------------------ device-buffer API
     def preprocess(self, src_dev, offsets: np.ndarray, hw: np.ndarray, mode: int = MODE_SQUASH, layout: int = LAYOUT_NCHW,
@@ -356,12 +387,12 @@ class Engine:
                                                C.c_void_p(out.data_ptr()), epilogue, activation, self._stream()))
         return out
 
-    def attention(self, qkv_bf16, B: int, S: int, width: int, heads: int, out=None):
+    def attention(self, qkv_bf16, B: int, S: int, width: int, heads: int, out=None, causal: bool = False):
         torch = _torch()
         if out is None:
             out = torch.empty((B * S, width), dtype=torch.bfloat16, device=qkv_bf16.device)
         _lib.check(self.lib.b200clip_attention(self._h, C.c_void_p(qkv_bf16.data_ptr()), C.c_void_p(out.data_ptr()), B, S, width, heads,
-                                               self._stream()))
+                                               int(causal), self._stream()))
         return out
 
     def layernorm(self, x_f32, gamma, beta, eps: float = 1e-5):

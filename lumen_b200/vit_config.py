@@ -66,3 +66,69 @@ def synthetic_weights(cfg: dict, seed: int = 0) -> dict[str, np.ndarray]:
             w = rng.standard_normal(shape) / np.sqrt(fan_in)
         out[name] = w.astype(np.float32)
     return out
+
+
+# ------------------------------------------------------------------------------------------------ text towers (N4)
+TEXT_CONFIGS: dict[str, dict] = {
+    "ViT-B-32": dict(context_length=77, vocab_size=49408, width=512, layers=12, heads=8, mlp_dim=2048, embed_dim=512),
+    "ViT-B-16": dict(context_length=77, vocab_size=49408, width=512, layers=12, heads=8, mlp_dim=2048, embed_dim=512),
+    "ViT-L-14-336": dict(context_length=77, vocab_size=49408, width=768, layers=12, heads=12, mlp_dim=3072, embed_dim=768),
+    "ViT-tiny-test": dict(context_length=77, vocab_size=1000, width=128, layers=2, heads=2, mlp_dim=256, embed_dim=64),
+}
+for _c in TEXT_CONFIGS.values():
+    _c.setdefault("activation", "quick_gelu")
+    _c.setdefault("ln_eps", 1e-5)
+
+
+def text_weight_shapes(cfg: dict) -> dict[str, tuple[int, ...]]:
+    d, L, mlp, D = cfg["width"], cfg["layers"], cfg["mlp_dim"], cfg["embed_dim"]
+    s: dict[str, tuple[int, ...]] = {
+        "text_model.embeddings.token_embedding.weight": (cfg["vocab_size"], d),
+        "text_model.embeddings.position_embedding.weight": (cfg["context_length"], d),
+        "text_model.final_layer_norm.weight": (d,),
+        "text_model.final_layer_norm.bias": (d,),
+        "text_projection.weight": (D, d),
+    }
+    for i in range(L):
+        p = f"text_model.encoder.layers.{i}."
+        for nm in ("q_proj", "k_proj", "v_proj", "out_proj"):
+            s[p + f"self_attn.{nm}.weight"] = (d, d)
+            s[p + f"self_attn.{nm}.bias"] = (d,)
+        for nm in ("layer_norm1", "layer_norm2"):
+            s[p + nm + ".weight"] = (d,)
+            s[p + nm + ".bias"] = (d,)
+        s[p + "mlp.fc1.weight"] = (mlp, d)
+        s[p + "mlp.fc1.bias"] = (mlp,)
+        s[p + "mlp.fc2.weight"] = (d, mlp)
+        s[p + "mlp.fc2.bias"] = (d,)
+    return s
+
+
+def synthetic_text_weights(cfg: dict, seed: int = 0) -> dict[str, np.ndarray]:
+    """Seeded random text-tower weights, same recipe as synthetic_weights."""
+    rng = np.random.default_rng(seed + 1000)
+    out: dict[str, np.ndarray] = {}
+    for name, shape in text_weight_shapes(cfg).items():
+        if "norm" in name and name.endswith(".weight"):
+            w = 1.0 + 0.1 * rng.standard_normal(shape)
+        elif name.endswith(".bias"):
+            w = 0.1 * rng.standard_normal(shape)
+        elif "embedding" in name:
+            w = 0.5 * rng.standard_normal(shape)
+        else:
+            w = rng.standard_normal(shape) / np.sqrt(int(np.prod(shape[1:])))
+        out[name] = w.astype(np.float32)
+    return out
+
+
+def synthetic_token_ids(cfg: dict, B: int, seed: int = 0) -> np.ndarray:
+    """[B, context_length] int32 in CLIP's layout: BOS, a few tokens, EOT (= the largest id), zero padding."""
+    rng = np.random.default_rng(seed)
+    V, ctx = cfg["vocab_size"], cfg["context_length"]
+    ids = np.zeros((B, ctx), np.int32)
+    for b in range(B):
+        n = int(rng.integers(1, ctx - 2)) if b else ctx - 2          # row 0: the longest legal prompt (EOT in the last slot)
+        ids[b, 0] = V - 2
+        ids[b, 1:1 + n] = rng.integers(1, V - 2, n)
+        ids[b, 1 + n] = V - 1
+    return ids

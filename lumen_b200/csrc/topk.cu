@@ -16,6 +16,8 @@
 #include "common.cuh"
 #include "kernels.h"
 
+#include <algorithm>
+#include <cstdlib>
 #include <mutex>
 
 namespace b200 {
@@ -35,6 +37,8 @@ struct TopkParams {
     long long index_base;
     int scatter;                 // queries were spread over the four TMEM lane quarters (see scatter_queries_kernel)
     DeviceStatus* status;
+    int stages;                  // gallery ring depth when the query tile is resident (QRES)
+    unsigned* gtau;              // [Q] best lower bound any split has found for the query's k-th best score (flip_f32 key, 0 = none)
 };
 
 __device__ __forceinline__ uint32_t flip_f32(float s) {
@@ -142,30 +146,38 @@ __device__ __noinline__ int compact_row(unsigned long long* rowptr, int n, int k
     return keep;
 }
 
-template <int CPL>
+// QRES: the CTA's query tile (128 x D fp16, D <= 512: at most 128 KB) is loaded ONCE and stays in shared memory; only gallery
+// tiles go through the ring (3 stages of 32 KB at D = 512).  Without it every gallery tile re-fetches the query tile from L2,
+// a third of the kernel's L2 -> SM traffic, and at Q = 4096 that traffic, not the tensor core, is what bounds the kernel.
+template <int CPL, bool QRES>
 __global__ void __launch_bounds__(192, 1)
 topk_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmG, TopkParams p) {
     constexpr int C = 32 * CPL;
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
-    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + TK_STAGES * TK_STAGE_BYTES);
+    const int kblocks = p.D / TK_BK;
+    const int n_stages = QRES ? p.stages : TK_STAGES;
+    const int stage_bytes = QRES ? TK_B_BYTES : TK_STAGE_BYTES;
+    uint8_t* ring = smem + (QRES ? kblocks * TK_A_BYTES : 0);
+    uint64_t* bars = reinterpret_cast<uint64_t*>(ring + n_stages * stage_bytes);
     uint64_t* full = bars;
     uint64_t* empty = bars + TK_STAGES;
     uint64_t* acc_full = bars + 2 * TK_STAGES;
     uint64_t* acc_empty = acc_full + 2;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(acc_empty + 2);
+    uint64_t* q_full = acc_empty + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(q_full + 1);
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int qt = blockIdx.x, sp = blockIdx.y;
     const long long n_lo = (long long)sp * p.rows_per_split;
     const long long n_hi = min(p.N, n_lo + p.rows_per_split);
     const int tiles = n_hi > n_lo ? (int)((n_hi - n_lo + TK_BN - 1) / TK_BN) : 0;
-    const int kblocks = p.D / TK_BK;
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmQ);
         tma_prefetch_desc(&tmG);
         for (int s = 0; s < TK_STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+        mbar_init(q_full, 1);
         for (int a = 0; a < 2; ++a) { mbar_init(&acc_full[a], 1); mbar_init(&acc_empty[a], 4); }
         fence_mbar_init();
     }
@@ -178,15 +190,19 @@ topk_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
     if (warp == 0) {
         if (lane == 0) {
             int s = 0; uint32_t ph = 0; bool ok = true;
+            if (QRES && tiles > 0) {
+                mbar_arrive_expect_tx(q_full, kblocks * TK_A_BYTES);
+                for (int kb = 0; kb < kblocks; ++kb) tma_load_2d(smem + kb * TK_A_BYTES, &tmQ, q_full, kb * TK_BK, qt * TK_BM);
+            }
             for (int t = 0; t < tiles && ok; ++t) {
                 const int n0 = (int)(n_lo + (long long)t * TK_BN);
                 for (int kb = 0; kb < kblocks; ++kb) {
                     if (!(ok = mbar_wait(&empty[s], ph ^ 1, p.status, 11))) break;
-                    uint8_t* sa = smem + s * TK_STAGE_BYTES;
-                    mbar_arrive_expect_tx(&full[s], TK_STAGE_BYTES);
-                    tma_load_2d(sa, &tmQ, &full[s], kb * TK_BK, qt * TK_BM);
-                    tma_load_2d(sa + TK_A_BYTES, &tmG, &full[s], kb * TK_BK, n0);
-                    if (++s == TK_STAGES) { s = 0; ph ^= 1; }
+                    uint8_t* sa = ring + s * stage_bytes;
+                    mbar_arrive_expect_tx(&full[s], stage_bytes);
+                    if (!QRES) tma_load_2d(sa, &tmQ, &full[s], kb * TK_BK, qt * TK_BM);
+                    tma_load_2d(sa + (QRES ? 0 : TK_A_BYTES), &tmG, &full[s], kb * TK_BK, n0);
+                    if (++s == n_stages) { s = 0; ph ^= 1; }
                 }
             }
         }
@@ -194,6 +210,7 @@ topk_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         if (lane == 0) {
             constexpr uint32_t idesc = umma_idesc(TK_BM, TK_BN, /*f16*/ 0);
             int s = 0; uint32_t ph = 0; bool ok = true;
+            if (QRES && tiles > 0) ok = mbar_wait(q_full, 0, p.status, 14);
             for (int t = 0; t < tiles && ok; ++t) {
                 const int as = t & 1; const uint32_t aph = (t >> 1) & 1;
                 if (!(ok = mbar_wait(&acc_empty[as], aph ^ 1, p.status, 12))) break;
@@ -202,12 +219,13 @@ topk_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
                 for (int kb = 0; kb < kblocks; ++kb) {
                     if (!(ok = mbar_wait(&full[s], ph, p.status, 13))) break;
                     tc_fence_after();
-                    const uint32_t sa = smem_u32(smem + s * TK_STAGE_BYTES);
-                    const uint64_t da = umma_desc_sw128(sa), db = umma_desc_sw128(sa + TK_A_BYTES);
+                    const uint32_t sb = smem_u32(ring + s * stage_bytes);
+                    const uint64_t da = umma_desc_sw128(QRES ? smem_u32(smem + kb * TK_A_BYTES) : sb);
+                    const uint64_t db = umma_desc_sw128(QRES ? sb : sb + TK_A_BYTES);
 #pragma unroll
                     for (int k = 0; k < TK_BK / 16; ++k) umma_f16(d_tmem, da + 2 * k, db + 2 * k, idesc, (kb | k) != 0);
                     umma_commit(&empty[s]);
-                    if (++s == TK_STAGES) { s = 0; ph ^= 1; }
+                    if (++s == n_stages) { s = 0; ph ^= 1; }
                 }
                 if (ok) umma_commit(&acc_full[as]);
             }
@@ -228,6 +246,13 @@ topk_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
             tc_fence_after();
             const long long n0 = n_lo + (long long)t * TK_BN;
             const uint32_t tsrc = tmem_base + ((uint32_t)(q * 32) << 16) + as * TK_BN;
+            // Threshold sharing: the k-th best score another gallery split has already established for this query bounds the global
+            // k-th best from below, so nothing below it can reach the final top-k.  Scores EQUAL to it are kept (key - 1 = the next
+            // float below): the index-ordered tie rule may still prefer them.  Without this every split warms up on its own.
+            if (qrow < p.Q) {
+                const unsigned g = __ldcg(p.gtau + qrow);
+                if (g > 1u) tau = fmaxf(tau, unflip_f32(g - 1u));
+            }
             // Scan 8 chunks of 32 scores; the TMEM load of chunk c+1 is in flight while chunk c is examined.
             // A thread first reduces its 32 scores to their maximum: only if that beats tau (rare once the
             // threshold has settled) does it walk the chunk and append the survivors.
@@ -284,7 +309,10 @@ topk_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
                 const int n = __shfl_sync(0xffffffffu, cnt, src);
                 float tnew;
                 const int keep = compact_row<CPL>(warp_rows + (size_t)src * C, n, p.k, lane, false, C - TK_BN, &tnew, nullptr, nullptr, 0);
-                if (lane == src) { cnt = keep; tau = tnew; }
+                if (lane == src) {
+                    cnt = keep; tau = fmaxf(tau, tnew);
+                    if (qrow < p.Q) atomicMax(p.gtau + qrow, flip_f32(tnew));       // k rows of THIS split score >= tnew
+                }
             }
         }
         // final: every row sorted, best k written as (score, global index) for the merge kernel
@@ -486,6 +514,8 @@ int merge_topk_run(const float* ps, const long long* pi, int P, int Q, int k, fl
 }
 
 // ------------------------------------------------------------------------------------------ host side
+static size_t topk_gtau_bytes(int Q) { return ((size_t)Q * 4 + 255) & ~(size_t)255; }
+
 int topk_plan(int Q, long long N, int k, TopkPlan* plan) {
     B200_REQUIRE(Q > 0 && N > 0 && k > 0, "topk: Q, N and k must be positive");
     B200_REQUIRE(k <= 768, "topk: k larger than 768 is not supported");
@@ -503,7 +533,7 @@ int topk_plan(int Q, long long N, int k, TopkPlan* plan) {
     plan->splits = (int)((ntiles + tiles_per_split - 1) / tiles_per_split);
     plan->cand_bytes = (size_t)plan->splits * plan->qtiles * TK_BM * 32 * plan->cpl * 8;
     plan->part_bytes = (((size_t)plan->splits * Q * k * 4 + 255) & ~(size_t)255) + (size_t)plan->splits * Q * k * 8;
-    plan->part_bytes = (plan->part_bytes + 255) & ~(size_t)255;
+    plan->part_bytes = ((plan->part_bytes + 255) & ~(size_t)255) + topk_gtau_bytes(Q);     // the shared thresholds sit at the end
     plan->qstage_bytes = Q < TK_BM ? (size_t)TK_BM * 1024 * 2 : 0;      // staged, interleaved copy of a small query batch (D <= 1024)
     return B200_OK;
 }
@@ -517,9 +547,18 @@ __global__ void scatter_queries_kernel(const __half* __restrict__ src, __half* _
         *reinterpret_cast<uint4*>(dst + (size_t)r * D + c) = *reinterpret_cast<const uint4*>(src + (size_t)i * D + c);
 }
 
-template <int CPL> static int launch_topk(const CUtensorMap& tq, const CUtensorMap& tg, const TopkParams& p, cudaStream_t st) {
-    B200_CUDA_OK(cudaFuncSetAttribute(topk_tc_kernel<CPL>, cudaFuncAttributeMaxDynamicSharedMemorySize, TK_SMEM));
-    topk_tc_kernel<CPL><<<dim3(p.qtiles, p.splits), 192, TK_SMEM, st>>>(tq, tg, p);
+template <int CPL> static int launch_topk(const CUtensorMap& tq, const CUtensorMap& tg, TopkParams p, cudaStream_t st) {
+    static const int qres_on = [] { const char* e = getenv("B200_TOPK_QRES"); return e ? atoi(e) : 1; }();
+    const int q_bytes = (p.D / TK_BK) * TK_A_BYTES;
+    if (qres_on && p.D <= 512) {
+        p.stages = std::min(TK_STAGES, (227 * 1024 - 256 - 1024 - q_bytes) / TK_B_BYTES);
+        const int smem = q_bytes + p.stages * TK_B_BYTES + 256 + 1024;
+        B200_CUDA_OK(cudaFuncSetAttribute(topk_tc_kernel<CPL, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        topk_tc_kernel<CPL, true><<<dim3(p.qtiles, p.splits), 192, smem, st>>>(tq, tg, p);
+    } else {
+        B200_CUDA_OK(cudaFuncSetAttribute(topk_tc_kernel<CPL, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, TK_SMEM));
+        topk_tc_kernel<CPL, false><<<dim3(p.qtiles, p.splits), 192, TK_SMEM, st>>>(tq, tg, p);
+    }
     B200_CUDA_OK(cudaGetLastError());
     return B200_OK;
 }
@@ -549,8 +588,10 @@ int topk_run(const void* queries, const void* gallery, int Q, long long N, int D
     if (rc) return rc;
     float* part_s = reinterpret_cast<float*>(sc + plan.cand_bytes);
     long long* part_i = reinterpret_cast<long long*>(sc + plan.cand_bytes + (((size_t)plan.splits * Q * k * 4 + 255) & ~(size_t)255));
+    unsigned* gtau = reinterpret_cast<unsigned*>(sc + plan.cand_bytes + plan.part_bytes - topk_gtau_bytes(Q));
+    B200_CUDA_OK(cudaMemsetAsync(gtau, 0, topk_gtau_bytes(Q), st));
     TopkParams p{Q, D, k, N, plan.rows_per_split, plan.splits, plan.qtiles, reinterpret_cast<unsigned long long*>(sc),
-                 part_s, part_i, index_base, scatter, status};
+                 part_s, part_i, index_base, scatter, status, 0, gtau};
     rc = plan.cpl == 16 ? launch_topk<16>(tq, tg, p, st) : launch_topk<32>(tq, tg, p, st);
     if (rc) return rc;
     return merge_topk_run(part_s, part_i, plan.splits, Q, k, out_s, out_i, st);
@@ -600,7 +641,7 @@ extern "C" int b200clip_topk_static(const void* queries_f16_dev, int32_t Q, cons
     const size_t budget = kStaticScratchBytes - 256;
     auto need = [&](long long splits) {
         return (size_t)splits * plan.qtiles * TK_BM * 32 * 16 * 8 + (((size_t)splits * Q * k * 4 + 255) & ~(size_t)255) +
-               (size_t)splits * Q * k * 8 + 256;
+               (((size_t)splits * Q * k * 8 + 255) & ~(size_t)255) + topk_gtau_bytes(Q) + 256;
     };
     long long splits = (2LL * kNumSMs) / plan.qtiles;
     if (splits < 1) splits = 1;
@@ -615,7 +656,8 @@ extern "C" int b200clip_topk_static(const void* queries_f16_dev, int32_t Q, cons
     plan.rows_per_split = tiles_per_split * TK_BN;
     plan.splits = (int)((ntiles + tiles_per_split - 1) / tiles_per_split);
     plan.cand_bytes = (size_t)plan.splits * plan.qtiles * TK_BM * 32 * 16 * 8;
-    plan.part_bytes = (((size_t)plan.splits * Q * k * 4 + 255) & ~(size_t)255) + (size_t)plan.splits * Q * k * 8;
+    plan.part_bytes = (((size_t)plan.splits * Q * k * 4 + 255) & ~(size_t)255) + (((size_t)plan.splits * Q * k * 8 + 255) & ~(size_t)255) +
+                      topk_gtau_bytes(Q);
     plan.qstage_bytes = 0;
     cudaStream_t st = (cudaStream_t)stream;
     // The array keeps whatever the previous call left.  Only the watchdog words have to start at zero: candidate

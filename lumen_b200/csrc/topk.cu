@@ -339,7 +339,7 @@ topk_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
 __device__ __forceinline__ bool better(float sa, long long ia, float sb, long long ib) {
     return sa > sb || (sa == sb && ia < ib);
 }
-constexpr int MERGE_THREADS = 256;
+// one CTA per query: 1024 threads when the queries are few (the kernel is a latency chain then and gets every warp an SM has), 256 otherwise
 constexpr int MERGE_KMAX = 1024;
 
 // hist[digit] += 1 for every participating lane, one shared-memory atomic per distinct digit in the warp
@@ -351,26 +351,38 @@ __device__ __forceinline__ void hist_add(int* hist, bool active, int digit) {
     if ((threadIdx.x & 31) == __ffs(peers) - 1) atomicAdd(&hist[digit], __popc(peers));
 }
 
-// Finds the digit d (scanning from `hi_first ? 255 : 0`) where the running count reaches kk; returns it and
-// the count before it.  Called by all threads after the histogram is complete; thread 0 scans.
-__device__ __forceinline__ void scan_hist(const int* hist, int kk, bool hi_first, int* sh_digit, int* sh_before) {
-    if (threadIdx.x == 0) {
-        int acc = 0, d = hi_first ? 255 : 0;
-        for (int s = 0; s < 256; ++s) {
-            d = hi_first ? 255 - s : s;
-            if (acc + hist[d] >= kk) break;
-            acc += hist[d];
+// Finds the digit d (scanning from `hi_first ? 255 : 0`) where the running count reaches kk; returns it and the count before
+// it, plus the histogram total.  Called by all threads after the histogram is complete; warp 0 scans (8 bins per lane + a
+// shuffle prefix sum: a single thread walking 256 shared-memory words was a fifth of this kernel's time at Q = 1).
+__device__ __forceinline__ void scan_hist(const int* hist, int kk, bool hi_first, int* sh_digit, int* sh_before, int* sh_total) {
+    if (threadIdx.x < 32) {
+        const int lane = threadIdx.x;
+        int loc[8], sum = 0;
+#pragma unroll
+        for (int i = 0; i < 8; ++i) { const int s = lane * 8 + i; loc[i] = hist[hi_first ? 255 - s : s]; sum += loc[i]; }
+        int inc = sum;
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { const int n = __shfl_up_sync(0xffffffffu, inc, o); if (lane >= o) inc += n; }
+        const unsigned hit = __ballot_sync(0xffffffffu, inc >= kk);
+        const int src = hit ? __ffs(hit) - 1 : 31;
+        const int total = __shfl_sync(0xffffffffu, inc, 31);
+        if (lane == src) {
+            int acc = inc - sum, i = 0;
+            for (; i < 7; ++i) { if (acc + loc[i] >= kk) break; acc += loc[i]; }
+            if (!hit) acc = total;                            // never reached (callers exclude it): same answer as a full walk
+            const int s = lane * 8 + i;
+            *sh_digit = hi_first ? 255 - s : s; *sh_before = acc; *sh_total = total;
         }
-        *sh_digit = d; *sh_before = acc;
     }
 }
 
-__global__ void __launch_bounds__(MERGE_THREADS) merge_topk_kernel(const float* __restrict__ ps, const long long* __restrict__ pi, int P,
+template <int NT>
+__global__ void __launch_bounds__(NT) merge_topk_kernel(const float* __restrict__ ps, const long long* __restrict__ pi, int P,
                                                                    int Q, int k, int cache_keys, float* __restrict__ out_s,
                                                                    long long* __restrict__ out_i) {
     extern __shared__ __align__(16) uint32_t key_cache[];     // [T] order-preserving score keys (0 = empty slot) when cache_keys
     __shared__ int hist[256];
-    __shared__ int sh_digit, sh_before, sh_count, sh_gt, sh_eq;
+    __shared__ int sh_digit, sh_before, sh_total, sh_count, sh_gt, sh_eq;
     __shared__ float ss[MERGE_KMAX];
     __shared__ long long si[MERGE_KMAX];
     const int qi = blockIdx.x, T = P * k, tid = threadIdx.x;
@@ -383,17 +395,17 @@ __global__ void __launch_bounds__(MERGE_THREADS) merge_topk_kernel(const float* 
     };
     if (tid == 0) { sh_count = 0; sh_gt = 0; sh_eq = 0; }
     if (cache_keys) {                                          // one pass over global memory, four loads in flight per thread
-        for (int e0 = 0; e0 < T; e0 += 4 * MERGE_THREADS) {
+        for (int e0 = 0; e0 < T; e0 += 4 * NT) {
             float s[4]; long long id[4];
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
-                const int e = e0 + u * MERGE_THREADS + tid;
+                const int e = e0 + u * NT + tid;
                 id[u] = -1; s[u] = 0.f;
                 if (e < T) { const size_t o = offset(e); id[u] = pi[o]; s[u] = ps[o]; }
             }
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
-                const int e = e0 + u * MERGE_THREADS + tid;
+                const int e = e0 + u * NT + tid;
                 if (e < T) key_cache[e] = id[u] < 0 ? 0u : flip_f32(s[u] + 0.0f);
             }
         }
@@ -404,22 +416,18 @@ __global__ void __launch_bounds__(MERGE_THREADS) merge_topk_kernel(const float* 
     uint32_t prefix = 0; int kk = k; bool all = false;
     for (int pass = 0; pass < 4; ++pass) {
         const int shift = 24 - 8 * pass;
-        hist[tid] = 0;
+        if (tid < 256) hist[tid] = 0;
         __syncthreads();
-        for (int e0 = 0; e0 < T; e0 += MERGE_THREADS) {          // whole warps iterate together (hist_add votes)
+        for (int e0 = 0; e0 < T; e0 += NT) {          // whole warps iterate together (hist_add votes)
             const int e = e0 + tid;
             const uint32_t key = e < T ? key_of(e) : 0u;
             const bool act = key != 0u && (pass == 0 || (key >> (shift + 8)) == (prefix >> (shift + 8)));
             hist_add(hist, act, (key >> shift) & 255);
         }
         __syncthreads();
-        if (pass == 0) {                                   // fewer valid candidates than k: keep them all
-            int tot = 0;
-            for (int d = 0; d < 256; ++d) tot += hist[d];
-            if (tot <= k) { all = true; break; }
-        }
-        scan_hist(hist, kk, true, &sh_digit, &sh_before);
+        scan_hist(hist, kk, true, &sh_digit, &sh_before, &sh_total);
         __syncthreads();
+        if (pass == 0 && sh_total <= k) { all = true; break; }   // fewer valid candidates than k: keep them all
         prefix |= (uint32_t)sh_digit << shift;
         kk -= sh_before;
         __syncthreads();
@@ -428,7 +436,7 @@ __global__ void __launch_bounds__(MERGE_THREADS) merge_topk_kernel(const float* 
     long long idx_cut = 0x7fffffffffffffffLL;
     if (!all) {
         int gt = 0, eq = 0;
-        for (int e = tid; e < T; e += MERGE_THREADS) {
+        for (int e = tid; e < T; e += NT) {
             const uint32_t key = key_of(e);
             gt += (key != 0u && key > prefix); eq += key == prefix;
         }
@@ -440,9 +448,9 @@ __global__ void __launch_bounds__(MERGE_THREADS) merge_topk_kernel(const float* 
             for (int pass = 0; pass < 8; ++pass) {
                 const int shift = 56 - 8 * pass;
                 __syncthreads();
-                hist[tid] = 0;
+                if (tid < 256) hist[tid] = 0;
                 __syncthreads();
-                for (int e0 = 0; e0 < T; e0 += MERGE_THREADS) {
+                for (int e0 = 0; e0 < T; e0 += NT) {
                     const int e = e0 + tid;
                     bool act = e < T && key_of(e) == prefix;
                     unsigned long long u = 0;
@@ -450,7 +458,7 @@ __global__ void __launch_bounds__(MERGE_THREADS) merge_topk_kernel(const float* 
                     hist_add(hist, act, (int)((u >> shift) & 255));
                 }
                 __syncthreads();
-                scan_hist(hist, kn, false, &sh_digit, &sh_before);
+                scan_hist(hist, kn, false, &sh_digit, &sh_before, &sh_total);
                 __syncthreads();
                 ip |= (unsigned long long)sh_digit << shift;
                 kn -= sh_before;
@@ -460,7 +468,7 @@ __global__ void __launch_bounds__(MERGE_THREADS) merge_topk_kernel(const float* 
     }
     __syncthreads();
     // ---- gather survivors, sort them, write
-    for (int e = tid; e < T; e += MERGE_THREADS) {
+    for (int e = tid; e < T; e += NT) {
         const uint32_t key = key_of(e);
         if (key == 0u) continue;
         if (all || key > prefix || key == prefix) {
@@ -476,11 +484,11 @@ __global__ void __launch_bounds__(MERGE_THREADS) merge_topk_kernel(const float* 
     const int cnt = min(sh_count, k);
     int np2 = 1;
     while (np2 < cnt) np2 <<= 1;
-    for (int e = cnt + tid; e < np2; e += MERGE_THREADS) { ss[e] = -INFINITY; si[e] = 0x7fffffffffffffffLL; }
+    for (int e = cnt + tid; e < np2; e += NT) { ss[e] = -INFINITY; si[e] = 0x7fffffffffffffffLL; }
     __syncthreads();
     for (int kk2 = 2; kk2 <= np2; kk2 <<= 1)
         for (int j = kk2 >> 1; j > 0; j >>= 1) {
-            for (int e = tid; e < np2; e += MERGE_THREADS) {
+            for (int e = tid; e < np2; e += NT) {
                 const int o = e ^ j;
                 if (o > e) {
                     const bool desc = (e & kk2) == 0;
@@ -491,7 +499,7 @@ __global__ void __launch_bounds__(MERGE_THREADS) merge_topk_kernel(const float* 
             }
             __syncthreads();
         }
-    for (int e = tid; e < k; e += MERGE_THREADS) {
+    for (int e = tid; e < k; e += NT) {
         const bool valid = e < cnt;
         out_s[(size_t)qi * k + e] = valid ? ss[e] : -INFINITY;
         out_i[(size_t)qi * k + e] = valid ? si[e] : -1;
@@ -506,9 +514,13 @@ int merge_topk_run(const float* ps, const long long* pi, int P, int Q, int k, fl
     const size_t T = (size_t)P * k;
     const int cache = T * 4 <= 160 * 1024;                 // keys fit in shared memory next to the sort buffers
     const size_t smem = cache ? T * 4 : 0;
-    if (smem > 32 * 1024)
-        B200_CUDA_OK(cudaFuncSetAttribute(merge_topk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    merge_topk_kernel<<<Q, MERGE_THREADS, smem, st>>>(ps, pi, P, Q, k, cache, out_s, out_i);
+    if (Q <= 2 * kNumSMs) {
+        if (smem > 32 * 1024) B200_CUDA_OK(cudaFuncSetAttribute(merge_topk_kernel<1024>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        merge_topk_kernel<1024><<<Q, 1024, smem, st>>>(ps, pi, P, Q, k, cache, out_s, out_i);
+    } else {
+        if (smem > 32 * 1024) B200_CUDA_OK(cudaFuncSetAttribute(merge_topk_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        merge_topk_kernel<256><<<Q, 256, smem, st>>>(ps, pi, P, Q, k, cache, out_s, out_i);
+    }
     B200_CUDA_OK(cudaGetLastError());
     return B200_OK;
 }

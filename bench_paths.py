@@ -122,7 +122,7 @@ def bench_models(args):
     import torch
     from lumen_b200.engine import Engine, pack_images
     pk = peaks()
-    for name, B in (("ViT-B-16", 256), ("ViT-L-14-336", 256), ("ViT-B-32", 1)):
+    for name, B in (("ViT-B-16", 256), ("ViT-L-14", 256), ("ViT-L-14-336", 256), ("ViT-B-32", 1)):
         cfg = VIT_CONFIGS[name]
         eng = Engine(cfg, device=0, max_batch=B)
         eng.load_weights(synthetic_weights(cfg, 0))
@@ -166,7 +166,7 @@ def bench_attention(args):
     from lumen_b200.engine import Engine
     pk = peaks()
     eng = Engine({}, device=0)
-    for name, B, S, heads in (("ViT-B-32", 512, 50, 12), ("ViT-B-16", 256, 197, 12), ("ViT-L-14-336", 128, 577, 16)):
+    for name, B, S, heads in (("ViT-B-32", 512, 50, 12), ("ViT-B-16", 256, 197, 12), ("ViT-L-14", 256, 257, 16), ("ViT-L-14-336", 128, 577, 16)):
         d = heads * 64
         qkv = torch.randn(B * S, 3 * d, device="cuda").to(torch.bfloat16)
         out = torch.empty((B * S, d), dtype=torch.bfloat16, device="cuda")

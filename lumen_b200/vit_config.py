@@ -8,6 +8,7 @@ import numpy as np
 VIT_CONFIGS: dict[str, dict] = {
     "ViT-B-32": dict(image_size=224, patch=32, width=768, layers=12, heads=12, mlp_dim=3072, embed_dim=512),
     "ViT-B-16": dict(image_size=224, patch=16, width=768, layers=12, heads=12, mlp_dim=3072, embed_dim=512),
+    "ViT-L-14": dict(image_size=224, patch=14, width=1024, layers=24, heads=16, mlp_dim=4096, embed_dim=768),       # CN-CLIP_ViT-L-14, bioclip-2
     "ViT-L-14-336": dict(image_size=336, patch=14, width=1024, layers=24, heads=16, mlp_dim=4096, embed_dim=768),
     # small shapes for fast parity tests (same code path, every dimension a legal tile multiple)
     "ViT-tiny-test": dict(image_size=64, patch=16, width=128, layers=2, heads=2, mlp_dim=256, embed_dim=64),
@@ -72,6 +73,7 @@ def synthetic_weights(cfg: dict, seed: int = 0) -> dict[str, np.ndarray]:
 TEXT_CONFIGS: dict[str, dict] = {
     "ViT-B-32": dict(context_length=77, vocab_size=49408, width=512, layers=12, heads=8, mlp_dim=2048, embed_dim=512),
     "ViT-B-16": dict(context_length=77, vocab_size=49408, width=512, layers=12, heads=8, mlp_dim=2048, embed_dim=512),
+    "ViT-L-14": dict(context_length=77, vocab_size=49408, width=768, layers=12, heads=12, mlp_dim=3072, embed_dim=768),
     "ViT-L-14-336": dict(context_length=77, vocab_size=49408, width=768, layers=12, heads=12, mlp_dim=3072, embed_dim=768),
     "ViT-tiny-test": dict(context_length=77, vocab_size=1000, width=128, layers=2, heads=2, mlp_dim=256, embed_dim=64),
 }

@@ -34,6 +34,7 @@ struct HuffTable {
     int32_t first_index[17];
     uint32_t first_code[17];
     uint16_t fast[512];                  // (length << 8) | symbol, 0 = not a short code
+    int16_t fast_ac[512];                // AC tables: (value << 8) | (run << 4) | (code + value bits) when both fit in 9 bits, else 0
 
     void finish() {
         uint32_t code = 0;
@@ -49,6 +50,18 @@ struct HuffTable {
             code <<= 1;
         }
         max_code[17] = INT32_MAX;
+        // run/size symbol and the coefficient's value bits resolved by ONE 9-bit lookup when they are short enough
+        // (most AC coefficients of a photograph are: small magnitudes have short codes)
+        for (int i = 0; i < 512; ++i) {
+            fast_ac[i] = 0;
+            const uint16_t f = fast[i];
+            if (!f) continue;
+            const int len = f >> 8, rs = f & 0xFF, run = rs >> 4, mag = rs & 15;
+            if (mag == 0 || len + mag > 9) continue;
+            int v = ((i << len) & 511) >> (9 - mag);
+            if (v < (1 << (mag - 1))) v += (int)((~0u) << mag) + 1;
+            if (v >= -128 && v <= 127) fast_ac[i] = (int16_t)(v * 256 + run * 16 + len + mag);
+        }
         present = true;
     }
 };
@@ -72,6 +85,21 @@ public:
     }
 private:
     void refill() {
+        // fast path: eight plain bytes ahead (no 0xFF anywhere: neither stuffing nor a marker) -> take as many as fit at once
+        if (!at_marker_ && end_ - p_ >= 8) {
+            uint64_t w;
+            std::memcpy(&w, p_, 8);
+            const uint64_t inv = ~w;
+            if (((inv - 0x0101010101010101ull) & ~inv & 0x8080808080808080ull) == 0) {      // no byte of w equals 0xFF
+                const int take = (64 - have_) >> 3;                                          // whole bytes that fit (1..8)
+                w = __builtin_bswap64(w);
+                if (take == 8) acc_ = w;                                                     // have_ == 0
+                else acc_ |= (w >> (64 - 8 * take)) << (64 - have_ - 8 * take);
+                p_ += take;
+                have_ += 8 * take;
+                return;
+            }
+        }
         while (have_ <= 56) {
             uint64_t byte = 0;
             if (!at_marker_ && p_ < end_) {
@@ -279,6 +307,15 @@ bool decode_entropy(Parsed& P, int16_t* coef) {
                         if (s) pred[c] += sign_extend(bs.bits(s), s);
                         blk[0] = (int16_t)pred[c];
                         for (int k = 1; k < 64;) {
+                            bs.need(32);
+                            const int fa = ac.fast_ac[bs.peek(9)];
+                            if (fa) {                         // symbol and value bits in one lookup
+                                k += (fa >> 4) & 15;
+                                if (k > 63) return fail_parse(P, 2, "AC run past the block");
+                                bs.drop(fa & 15);
+                                blk[kZigzag[k++]] = (int16_t)(fa >> 8);
+                                continue;
+                            }
                             const int rs = decode_symbol(bs, ac);
                             if (rs < 0) return fail_parse(P, 2, "bad AC code");
                             const int run = rs >> 4, size = rs & 15;

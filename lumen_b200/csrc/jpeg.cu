@@ -560,8 +560,12 @@ int jpeg_decode_batch(JpegState* s, const void* const* bufs, const size_t* lens,
     if ((rc = grow_dev(&s->plane_dev, &s->plane_dev_cap, plane_total))) return rc;
     if ((rc = grow_dev(&s->desc_dev, &s->desc_dev_cap, (size_t)n))) return rc;
 
-    // entropy decoding: one image per task, tasks pulled by a small pool of host threads
+    // entropy decoding: one image per task, tasks pulled in index order by a small pool of host threads.  The calling thread
+    // follows behind them and uploads the coefficients of finished images in runs of >= 8 MB, so the H2D copy (2 bytes per
+    // padded sample: as large as the decoded image) overlaps the decoding instead of following it.
     std::atomic<int> next{0}, bad{-1};
+    std::vector<std::atomic<unsigned char>> done(n);
+    for (int i = 0; i < n; ++i) done[i].store(status_out[i] != 0 ? 1 : 0, std::memory_order_relaxed);
     auto worker = [&] {
         for (int i; (i = next.fetch_add(1)) < n;) {
             Parsed& P = parsed[i];
@@ -569,7 +573,17 @@ int jpeg_decode_batch(JpegState* s, const void* const* bufs, const size_t* lens,
             const JpegDesc& d = P.d;
             std::memset(s->coef_host + d.coef_off[0], 0, (size_t)d.block_begin[d.ncomp] * 64 * sizeof(int16_t));
             if (!decode_entropy(P, s->coef_host)) { int e = -1; bad.compare_exchange_strong(e, i); }
+            done[i].store(1, std::memory_order_release);
         }
+    };
+    // coefficient range [elements) of image i inside the arena (images the decoder does not cover own none)
+    auto coef_end = [&](int i) { const JpegDesc& d = parsed[i].d; return (size_t)d.coef_off[0] + (size_t)d.block_begin[d.ncomp] * 64; };
+    size_t sent = 0;                                              // arena elements already queued for upload
+    cudaError_t copy_err = cudaSuccess;
+    auto upload_upto = [&](size_t upto) {
+        if (upto > sent && copy_err == cudaSuccess)
+            copy_err = cudaMemcpyAsync(s->coef_dev + sent, s->coef_host + sent, (upto - sent) * sizeof(int16_t), cudaMemcpyHostToDevice, st);
+        if (upto > sent) sent = upto;
     };
     int T = threads > 0 ? threads : (int)std::thread::hardware_concurrency();
     T = std::max(1, std::min(std::min(T, 32), ok_count));
@@ -578,14 +592,24 @@ int jpeg_decode_batch(JpegState* s, const void* const* bufs, const size_t* lens,
     } else {
         std::vector<std::thread> pool;
         for (int t = 0; t < T; ++t) pool.emplace_back(worker);
+        size_t ready = 0;
+        for (int i = 0; i < n; ++i) {
+            while (!done[i].load(std::memory_order_acquire)) std::this_thread::yield();
+            if (status_out[i] == 0) ready = coef_end(i);
+            if ((ready - sent) * sizeof(int16_t) >= (8u << 20)) upload_upto(ready);
+        }
         for (auto& th : pool) th.join();
     }
-    if (bad.load() >= 0) return fail(B200_EINVAL, "jpeg: image " + std::to_string(bad.load()) + ": " + parsed[bad.load()].error);
+    if (bad.load() >= 0) {
+        cudaStreamSynchronize(st);                                // queued uploads read the pinned arena: let them finish before it is reused
+        return fail(B200_EINVAL, "jpeg: image " + std::to_string(bad.load()) + ": " + parsed[bad.load()].error);
+    }
     for (int i = 0; i < n; ++i) {
         s->desc_host[i] = parsed[i].d;
         if (status_out[i] != 0) { s->desc_host[i].ncomp = 0; s->desc_host[i].block_begin[0] = 0; s->desc_host[i].width = s->desc_host[i].height = 0; }
     }
-    B200_CUDA_OK(cudaMemcpyAsync(s->coef_dev, s->coef_host, coef_total * sizeof(int16_t), cudaMemcpyHostToDevice, st));
+    upload_upto(coef_total);
+    B200_CUDA_OK(copy_err);
     B200_CUDA_OK(cudaMemcpyAsync(s->desc_dev, s->desc_host, (size_t)n * sizeof(JpegDesc), cudaMemcpyHostToDevice, st));
     B200_CUDA_OK(cudaEventRecord(s->uploaded, st));
     jpeg_idct_kernel<<<dim3((max_blocks + 127) / 128, n), 128, 0, st>>>(s->desc_dev, s->coef_dev, s->plane_dev);

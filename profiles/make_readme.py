@@ -75,14 +75,23 @@ for d in paths:
     if d.get("path", "").startswith("K10"):
         q = d["roofline"]
         L.append(f"| {d['Q']} | {d['ms']:.3f} | {d['queries_per_s']:.0f} | {q['tensor_tflops']:.1f} | {q['tensor_frac']:.3f} | {q['hbm_gbs']:.0f} | {q['hbm_frac']:.3f} |")
-L.append("\nSmall Q is the HBM-bound regime (gallery read once), large Q the tensor-bound one. On 8 GPUs (`search_c5_n8.json`) the C5 case "
-         "(10 M rows, Q = 4096) takes 6.8 ms including the NCCL all-gather and the merge. What is left on the table: every gallery split warms its own "
-         "per-row threshold and the warp-cooperative radix-select compactions stall the epilogue in bursts; see DESIGN.md §7.\n")
+c5 = json.loads((P / "search_c5_n8.json").read_text())
+n8 = json.loads((P / "bench_r1_n8.json").read_text())
+n2 = json.loads((P / "bench_r1_n2.json").read_text())
+L.append(f"\nSmall Q is the HBM-bound regime (gallery read once), large Q the tensor-bound one. On 8 GPUs (`search_c5_n8.json`) the C5 case "
+         f"({c5['N_total'] / 1e6:.0f} M rows, Q = {c5['Q']}) takes {c5['ms']:.2f} ms including the NCCL all-gather and the merge "
+         f"({c5['roofline']['tensor_frac']:.2f} of the burst tensor peak per GPU). History at Q = 4096 on one GPU: 6.35 ms -> 4.95 ms when the gallery splits started "
+         "sharing their k-th-best lower bound per query (each split used to warm up its own threshold); Q = 1: 0.334 -> 0.278 ms with the 1024-thread merge.\n")
+L.append("## Multi-GPU (`bench_r1_n2.json`, `bench_r1_n8.json`)\n")
+L.append(f"* 2 GPUs: {n2['value']:.0f} images/s ({n2['ms_per_step']:.2f} ms per step); 8 GPUs: **{n8['value']:.0f} images/s** ({n8['ms_per_step']:.2f} ms per step, "
+         f"{n8['value'] / 8:.0f} per GPU): image shards, replicated weights, no collective on the data path.\n")
 L.append("## Other models / classify\n")
 for d in paths:
     if d.get("path") == "embed (K1..K9)":
         L.append(f"* {d['model']} batch {d['batch']}: {d['images_per_s']:.0f} images/s ({d['ms']:.2f} ms), {d['frac_of_tensor_peak_sustained']:.3f} of sustained tensor peak at {d['gflop_per_image']:.1f} GFLOP/image")
     if d.get("path", "").startswith("K11"):
         L.append(f"* classify 256 x 1000 labels, k=5: {d['us']:.0f} us per batch")
+    if d.get("path", "").startswith("P0+K1"):
+        L.append(f"* JPEG bytes -> embeddings ({d['model']}, {d['src']}, batch {d['batch']}): {d['images_per_s']:.0f} images/s, bound by the host's Huffman decoding")
 (P / "README.md").write_text("\n".join(L) + "\n")
 print("\n".join(L)[:1500])

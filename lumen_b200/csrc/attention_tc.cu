@@ -179,6 +179,8 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, AttnParams p) {
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();
+    pdl_trigger();
 
     if (warp == 0 || warp == 10) {
         // ---- TMA producer of one slot: Q (two 64-row boxes) once per item, K and V of a step through the ring
@@ -467,7 +469,7 @@ int launch_attention_tc(const void* qkv, void* out, int B, int S, int d, int hea
     B200_CUDA_OK(cudaFuncSetAttribute(attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM));
     const int n_pairs = (p.items + 1) / 2;
     const int grid = n_pairs < kNumSMs ? n_pairs : kNumSMs;
-    attention_tc_kernel<<<grid, AT_THREADS, AT_SMEM, st>>>(tm, p);
+    B200_CUDA_OK(launch_pdl(attention_tc_kernel, dim3(grid), dim3(AT_THREADS), AT_SMEM, st, tm, p));
     B200_CUDA_OK(cudaGetLastError());
     return B200_OK;
 }

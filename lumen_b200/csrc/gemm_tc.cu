@@ -172,6 +172,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
     __syncthreads();
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();                              // everything above overlapped the previous kernel's tail; operands and outputs are touched below
+    pdl_trigger();
 
     if (warp == 0) {
         if (lane == 0) {
@@ -286,6 +288,8 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
     cluster_sync_all();                      // barriers of both CTAs initialised before any remote arrive / TMA credit
     tc_fence_after();
     const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();                              // everything above overlapped the previous kernel's tail; operands and outputs are touched below
+    pdl_trigger();
 
     if (warp == 0) {
         if (lane == 0) {
@@ -391,7 +395,7 @@ template <int BN, int EPI, int ACT> static int launch_gemm(const CUtensorMap& ta
     B200_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<BN, EPI, ACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
     const int tiles = ((p.M + BM - 1) / BM) * ((p.N + BN - 1) / BN);
     const int grid = tiles < kNumSMs ? tiles : kNumSMs;
-    gemm_tc_kernel<BN, EPI, ACT><<<grid, GEMM_THREADS, Cfg::SMEM_BYTES, st>>>(ta, tb, tc, p);
+    B200_CUDA_OK(launch_pdl(gemm_tc_kernel<BN, EPI, ACT>, dim3(grid), dim3(GEMM_THREADS), Cfg::SMEM_BYTES, st, ta, tb, tc, p));
     B200_CUDA_OK(cudaGetLastError());
     return B200_OK;
 }
@@ -400,7 +404,7 @@ template <int BN, int EPI, int ACT> static int launch_gemm2(const CUtensorMap& t
     B200_CUDA_OK(cudaFuncSetAttribute(gemm_tc2_kernel<BN, EPI, ACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
     const int tiles = ((p.M + 2 * BM - 1) / (2 * BM)) * ((p.N + BN - 1) / BN);
     const int pairs = tiles < kNumSMs / 2 ? tiles : kNumSMs / 2;
-    gemm_tc2_kernel<BN, EPI, ACT><<<2 * pairs, GEMM_THREADS, Cfg::SMEM_BYTES, st>>>(ta, tb, tc, p);   // cluster dims are compiled in
+    B200_CUDA_OK(launch_pdl(gemm_tc2_kernel<BN, EPI, ACT>, dim3(2 * pairs), dim3(GEMM_THREADS), Cfg::SMEM_BYTES, st, ta, tb, tc, p));   // cluster dims are compiled in
     B200_CUDA_OK(cudaGetLastError());
     return B200_OK;
 }

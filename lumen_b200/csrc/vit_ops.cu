@@ -30,6 +30,8 @@ __device__ __forceinline__ void ln_row(float4 (&v)[LN_MAX_V4], int nv, int d, fl
 __global__ void __launch_bounds__(256) layernorm_bf16_kernel(const float* __restrict__ x, long long row_stride,
                                                              const float* __restrict__ gamma, const float* __restrict__ beta,
                                                              __nv_bfloat16* __restrict__ out, int rows, int d, float eps) {
+    pdl_wait();
+    pdl_trigger();
     // rows are walked from the end: the GEMM that just updated x finished with the last row blocks, so those are the
     // lines most likely still in L2
     const int row = rows - 1 - (blockIdx.x * 8 + (threadIdx.x >> 5)), lane = threadIdx.x & 31;
@@ -58,6 +60,8 @@ __global__ void __launch_bounds__(256) embed_preln_kernel(const float* __restric
                                                           const float* __restrict__ pos, const float* __restrict__ gamma,
                                                           const float* __restrict__ beta, float* __restrict__ xres,
                                                           int B, int S, int d, float eps) {
+    pdl_wait();
+    pdl_trigger();
     const int row = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (row >= B * S) return;
     const int b = row / S, s = row - b * S;
@@ -84,6 +88,8 @@ __global__ void __launch_bounds__(256) embed_preln_kernel(const float* __restric
 
 // v / ||v||_2 per row, no epsilon (onnxrt_backend.py:545-546).  One warp per row.
 __global__ void __launch_bounds__(256) l2_normalize_kernel(const float* __restrict__ in, float* __restrict__ out, int rows, int D) {
+    pdl_wait();
+    pdl_trigger();
     const int row = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
     if (row >= rows) return;
     const float* r = in + (size_t)row * D;
@@ -206,6 +212,8 @@ constexpr int ATT_SMEM = 6 * ATT_TILE * 2;        // Q, K, V double buffered
 
 __global__ void __launch_bounds__(128, 4) attention_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict__ out,
                                                            int S, int d, int heads, int n_qt, int total_items) {
+    pdl_wait();
+    pdl_trigger();
     extern __shared__ __align__(16) __nv_bfloat16 att_sm[];
     __nv_bfloat16* sQ = att_sm;                    // [2][ATT_TILE]
     __nv_bfloat16* sK = att_sm + 2 * ATT_TILE;
@@ -326,14 +334,14 @@ __global__ void __launch_bounds__(128, 4) attention_kernel(const __nv_bfloat16* 
 // ------------------------------------------------------------------------------------------ launchers
 int launch_layernorm(const float* x, long long row_stride, const float* g, const float* b, void* out, int rows, int d, float eps, cudaStream_t st) {
     B200_REQUIRE(d % 128 == 0 && d <= 128 * LN_MAX_V4, "layernorm: width must be a multiple of 128, at most 1024");
-    layernorm_bf16_kernel<<<(rows + 7) / 8, 256, 0, st>>>(x, row_stride, g, b, reinterpret_cast<__nv_bfloat16*>(out), rows, d, eps);
+    B200_CUDA_OK(launch_pdl(layernorm_bf16_kernel, dim3((rows + 7) / 8), dim3(256), 0, st, x, row_stride, g, b, reinterpret_cast<__nv_bfloat16*>(out), rows, d, eps));
     B200_CUDA_OK(cudaGetLastError());
     return B200_OK;
 }
 int launch_embed_preln(const float* patch, const float* cls, const float* pos, const float* g, const float* b, float* xres,
                        int B, int S, int d, float eps, cudaStream_t st) {
     B200_REQUIRE(d % 128 == 0 && d <= 128 * LN_MAX_V4, "embed: width must be a multiple of 128, at most 1024");
-    embed_preln_kernel<<<(B * S + 7) / 8, 256, 0, st>>>(patch, cls, pos, g, b, xres, B, S, d, eps);
+    B200_CUDA_OK(launch_pdl(embed_preln_kernel, dim3((B * S + 7) / 8), dim3(256), 0, st, patch, cls, pos, g, b, xres, B, S, d, eps));
     B200_CUDA_OK(cudaGetLastError());
     return B200_OK;
 }
@@ -357,7 +365,7 @@ int launch_gallery_pack(const float* in, void* out_f16, long long rows, int D, i
 }
 int launch_l2_normalize(const float* in, float* out, int rows, int D, cudaStream_t st) {
     if (rows == 0) return B200_OK;
-    l2_normalize_kernel<<<(rows + 7) / 8, 256, 0, st>>>(in, out, rows, D);
+    B200_CUDA_OK(launch_pdl(l2_normalize_kernel, dim3((rows + 7) / 8), dim3(256), 0, st, in, out, rows, D));
     B200_CUDA_OK(cudaGetLastError());
     return B200_OK;
 }
@@ -369,8 +377,8 @@ int launch_attention(const void* qkv, void* out, int B, int S, int d, int heads,
     B200_REQUIRE(items < (1LL << 30), "attention: too many (image, head, tile) items");
     B200_CUDA_OK(cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_SMEM));
     const int grid = (int)(items < 4LL * kNumSMs ? items : 4LL * kNumSMs);
-    attention_kernel<<<grid, 128, ATT_SMEM, st>>>(reinterpret_cast<const __nv_bfloat16*>(qkv), reinterpret_cast<__nv_bfloat16*>(out),
-                                                  S, d, heads, n_qt, (int)items);
+    B200_CUDA_OK(launch_pdl(attention_kernel, dim3(grid), dim3(128), ATT_SMEM, st, reinterpret_cast<const __nv_bfloat16*>(qkv),
+                            reinterpret_cast<__nv_bfloat16*>(out), S, d, heads, n_qt, (int)items));
     B200_CUDA_OK(cudaGetLastError());
     return B200_OK;
 }

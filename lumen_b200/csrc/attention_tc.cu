@@ -360,6 +360,19 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, AttnParams p) {
             const int qi = li & 1;
             uint32_t a_lo[32], a_hi[32], b_lo[32], b_hi[32];
             l = 0.f;
+            // A warp whose 32 rows all lie past the end of the sequence (the last query tile of S = 257 holds ONE real row) has
+            // nothing to compute: it only keeps the barrier protocol going, paced by the score barriers so that it can never arrive
+            // twice in one phase.  Its SFU and issue slots go to the other slot's warps.
+            if (p.pack == 1 && it.qt * AT_ROWS + q * 32 >= p.S) {
+                for (int kt = 0; kt < p.n_kt; ++kt, ++g) {
+                    if (!(ok = mbar_wait_parked(&b[S_FULL + (g & 1)], (g >> 1) & 1, p.status, 37))) break;
+                    tc_fence_after();
+                    publish(g);
+                }
+                if (!ok) break;
+                if (lane == 0) { mbar_arrive(&b[O_FREE]); mbar_arrive(&b[Q_EMPTY + qi]); }
+                continue;
+            }
             if (p.pack == 1) {
                 // first step of the item: load, mask, take the maximum as the reference
                 if (!(ok = mbar_wait_parked(&b[S_FULL + (g & 1)], (g >> 1) & 1, p.status, 37))) break;

@@ -12,6 +12,7 @@ larger than L2 unless noted."""
 from __future__ import annotations
 
 import argparse
+import ctypes
 import json
 import os
 import sys
@@ -24,6 +25,7 @@ sys.path.insert(0, str(ROOT))
 
 from bench import gemm_flops_per_image, peaks, total_flops_per_image  # noqa: E402
 from lumen_b200.vit_config import VIT_CONFIGS, synthetic_weights  # noqa: E402
+from lumen_b200._lib import check as _lib_check  # noqa: E402
 
 
 def timed(fn, iters, warm=3):
@@ -229,12 +231,61 @@ def bench_decode(args):
     eng.close()
 
 
+def bench_n4(args):
+    """N4: text tower (label-embedding bootstrap) and gallery store (fp32 rows -> unit-norm fp16 rows on the device)."""
+    import tempfile
+    import time
+    import torch
+    from lumen_b200.engine import Engine
+    from lumen_b200.gallery import DeviceGallery
+    from lumen_b200.vit_config import TEXT_CONFIGS, synthetic_text_weights, synthetic_token_ids
+    pk = peaks()
+    cfg = TEXT_CONFIGS["ViT-B-32"]
+    d, L, mlp, D, S = cfg["width"], cfg["layers"], cfg["mlp_dim"], cfg["embed_dim"], cfg["context_length"]
+    flops_per_text = L * (2 * S * d * 3 * d + 2 * S * d * d + 4 * S * d * mlp + 4 * S * S * d) + 2 * d * D
+    eng = Engine({}, device=0)
+    eng.init_text(cfg, max_batch=1024)
+    eng.load_weights(synthetic_text_weights(cfg, 0))
+    for B in (1, 64, 1024):
+        ids = torch.from_numpy(synthetic_token_ids(cfg, B, seed=1)).cuda()
+        out = torch.empty((B, D), dtype=torch.float32, device="cuda")
+        def run():
+            _lib_check(eng.lib.b200clip_encode_text(eng._h, ctypes.c_void_p(ids.data_ptr()), B, ctypes.c_void_p(out.data_ptr()), eng._stream()))
+        ms = timed(run, 10 if B >= 64 else 50)
+        tps = B / ms * 1e3
+        print(json.dumps({"path": "N4 text tower (encode_text)", "model": "ViT-B-32 text", "batch": B, "ms": ms, "texts_per_s": tps,
+                          "gflop_per_text": flops_per_text / 1e9, "frac_of_tensor_peak_sustained": flops_per_text * tps / 1e12 / pk["bf16_sustained"]}), flush=True)
+    # gallery pack: HBM-bound, 4 B in + 2 B out per element
+    N, Dg = 2_000_000, 512
+    src = torch.randn((N, Dg), device="cuda")
+    g = DeviceGallery(eng, Dg, capacity=N)
+    def pack():
+        g.rows = 0
+        g.append(src, normalize=True)
+    ms = timed(pack, 10)
+    gbs = N * Dg * 6 / ms / 1e6
+    print(json.dumps({"path": "N4 gallery_pack (device fp32 -> unit-norm fp16)", "rows": N, "dim": Dg, "ms": ms, "rows_per_s": N / ms * 1e3,
+                      "roofline": {"bound": "hbm", "achieved": gbs, "peak": pk["hbm_gbs"], "unit": "GB/s", "frac": gbs / pk["hbm_gbs"]}}), flush=True)
+    # the whole path from the reference's file format: fp32 .npy (mmap) -> pinned staging -> device shard
+    with tempfile.TemporaryDirectory() as td:
+        path = os.path.join(td, "g.npy")
+        host = np.random.default_rng(0).standard_normal((500_000, Dg)).astype(np.float32)
+        np.save(path, host)
+        DeviceGallery.from_npy(eng, path); torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        DeviceGallery.from_npy(eng, path); torch.cuda.synchronize()
+        ms = (time.perf_counter() - t0) * 1e3
+        print(json.dumps({"path": "N4 gallery from_npy (fp32 .npy mmap -> device fp16)", "rows": host.shape[0], "dim": Dg, "ms": ms,
+                          "host_gbs": host.nbytes / ms / 1e6, "note": "bound by the host copy into pinned staging and PCIe"}), flush=True)
+    eng.close()
+
+
 if __name__ == "__main__":
     ap = argparse.ArgumentParser()
-    ap.add_argument("what", choices=["preprocess", "search", "classify", "models", "gemm", "attention", "decode"])
+    ap.add_argument("what", choices=["preprocess", "search", "classify", "models", "gemm", "attention", "decode", "n4"])
     ap.add_argument("--gallery", type=int, default=1_250_000, help="total gallery rows (all GPUs)")
     ap.add_argument("--sharded", action="store_true")
     ap.add_argument("--qs", default="", help="comma-separated query counts for the search sweep")
     a = ap.parse_args()
     {"preprocess": bench_preprocess, "search": bench_search, "classify": bench_classify, "models": bench_models, "gemm": bench_gemm,
-     "attention": bench_attention, "decode": bench_decode}[a.what](a)
+     "attention": bench_attention, "decode": bench_decode, "n4": bench_n4}[a.what](a)

@@ -5,7 +5,7 @@ mkdir -p gpurun_out
 python -m pytest tests -m gpu -q --timeout 600 -p no:cacheprovider 2>&1 | tail -3 > gpurun_out/pytest_gpu.txt
 python bench.py > gpurun_out/bench_r1.json 2> gpurun_out/bench_r1.err
 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/bench_r1_reference.json 2>/dev/null
-for w in preprocess search classify models gemm attention decode; do python bench_paths.py $w 2>/dev/null; done > gpurun_out/paths_r1.jsonl
+for w in preprocess search classify models gemm attention decode n4; do python bench_paths.py $w 2>/dev/null; done > gpurun_out/paths_r1.jsonl
 python bench.py --steps 2 --warmup 3 --cpu-seconds 1 > gpurun_out/plain.log 2>&1 && \
 ncu --metrics gpu__time_duration.sum --clock-control none -s 273 -c 91 --csv --log-file gpurun_out/launches_r1.csv \
     python bench.py --steps 2 --warmup 3 --cpu-seconds 1 > gpurun_out/ncu_launches.log 2>&1

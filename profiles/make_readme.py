@@ -93,5 +93,15 @@ for d in paths:
         L.append(f"* classify 256 x 1000 labels, k=5: {d['us']:.0f} us per batch")
     if d.get("path", "").startswith("P0+K1"):
         L.append(f"* JPEG bytes -> embeddings ({d['model']}, {d['src']}, batch {d['batch']}): {d['images_per_s']:.0f} images/s, bound by the host's Huffman decoding")
+n4 = [d for d in paths if d.get("path", "").startswith("N4")]
+if n4:
+    L.append("\n## N4: text tower and gallery store (`paths_r1.jsonl`)\n")
+    for d in n4:
+        if "texts_per_s" in d:
+            L.append(f"* text tower ({d['model']}), batch {d['batch']}: {d['ms']:.2f} ms, {d['texts_per_s']:.0f} texts/s, {d['frac_of_tensor_peak_sustained']:.3f} of the sustained tensor peak at {d['gflop_per_text']:.2f} GFLOP/text")
+        elif "roofline" in d:
+            L.append(f"* `b200clip_gallery_pack`, {d['rows']} x {d['dim']}: {d['ms']:.2f} ms = {d['roofline']['achieved']:.0f} GB/s (algorithmic 6 B per element), **{d['roofline']['frac']:.2f} of the HBM peak**")
+        else:
+            L.append(f"* `DeviceGallery.from_npy`, {d['rows']} x {d['dim']} fp32 file: {d['ms']:.0f} ms ({d['host_gbs']:.1f} GB/s of file data; host copy into pinned staging + PCIe)")
 (P / "README.md").write_text("\n".join(L) + "\n")
 print("\n".join(L)[:1500])

@@ -35,6 +35,26 @@ def test_oracle_rejects_corrupt_stream(golden_jpeg):
         O.decode_jpeg(data[:len(data) - 40])              # entropy-coded data cut: no EOI (Pillow: "image file is truncated")
 
 
+def test_oracle_matches_live_pillow_on_random_cases():
+    """Beyond the committed fixtures: when Pillow is importable (it is in this image), fresh random sizes / qualities / samplings."""
+    Image = pytest.importorskip("PIL.Image")
+    from oracle import clip_oracle as O
+    rng = np.random.default_rng(123)
+    for case in range(40):
+        h, w = int(rng.integers(1, 200)), int(rng.integers(1, 200))
+        yy, xx = np.mgrid[0:h, 0:w]
+        a = np.stack([(xx * int(rng.integers(1, 9)) + yy) % 256, rng.integers(0, 256, (h, w)), 128 + 100 * np.sin((xx + yy) / float(rng.uniform(2, 30)))], -1)
+        kw = dict(quality=int(rng.integers(5, 101)), subsampling=int(rng.integers(0, 3)))
+        if case % 5 == 0:
+            kw["optimize"] = True
+        if case % 7 == 0:
+            kw["restart_marker_blocks"] = int(rng.integers(1, 9))
+        buf = io.BytesIO()
+        Image.fromarray(a.clip(0, 255).astype(np.uint8)).save(buf, "JPEG", **kw)
+        want = np.asarray(Image.open(io.BytesIO(buf.getvalue())).convert("RGB"))
+        assert np.array_equal(O.decode_jpeg(buf.getvalue()), want), (case, h, w, kw)
+
+
 def test_probe_is_host_only_and_matches_headers(golden_jpeg):
     """b200clip_jpeg_probe parses headers on the host: callable without a GPU."""
     from lumen_b200.engine import Engine

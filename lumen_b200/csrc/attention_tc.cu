@@ -479,7 +479,13 @@ int launch_attention_tc(const void* qkv, void* out, int B, int S, int d, int hea
     CUtensorMap tm;
     int rc = make_tmap_2d(&tm, qkv, (uint64_t)B * S, (uint64_t)3 * d, (uint64_t)3 * d * 2, 64, false);
     if (rc) return rc;
-    B200_CUDA_OK(cudaFuncSetAttribute(attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM));
+    static bool attr_set[64] = {false};
+    int dev = 0;
+    B200_CUDA_OK(cudaGetDevice(&dev));
+    if (dev >= 64 || !attr_set[dev]) {
+        B200_CUDA_OK(cudaFuncSetAttribute(attention_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM));
+        if (dev < 64) attr_set[dev] = true;
+    }
     const int n_pairs = (p.items + 1) / 2;
     const int grid = n_pairs < kNumSMs ? n_pairs : kNumSMs;
     B200_CUDA_OK(launch_pdl(attention_tc_kernel, dim3(grid), dim3(AT_THREADS), AT_SMEM, st, tm, p));

@@ -39,7 +39,7 @@ template <int BN> struct GemmCfg {
     static constexpr int A_BYTES = BM * BK * 2;
     static constexpr int B_BYTES = BN * BK * 2;
     static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-    static constexpr int TMEM_COLS = BN == 128 ? 256 : 512;   // two accumulators, allocation must be a power of two
+    static constexpr int TMEM_COLS = BN == 64 ? 128 : BN == 128 ? 256 : 512;   // two accumulators, allocation must be a power of two
     static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 2 * 16384 + 256 + 1024;
 };
 
@@ -378,6 +378,18 @@ int make_tmap_2d_ex(CUtensorMap* out, const void* base, uint64_t rows, uint64_t 
     if (!g_encode) return fail(B200_EDEVICE, "cuTensorMapEncodeTiled is not available from the CUDA driver");
     if ((reinterpret_cast<uintptr_t>(base) & 15) || (row_pitch_bytes & 15))
         return fail(B200_EINVAL, "TMA operands need 16-byte aligned base and row pitch");
+    // A pass re-encodes the same ~200 descriptors (fixed activation buffers and weights); at small batch the encoder calls were a
+    // third of the host time per pass, and the host is what bounds that regime.  Encoding is a pure function of the key.
+    struct Key {
+        const void* base; uint64_t rows, cols, pitch; uint32_t box_rows; int dtype;
+        bool operator==(const Key& o) const { return base == o.base && rows == o.rows && cols == o.cols && pitch == o.pitch && box_rows == o.box_rows && dtype == o.dtype; }
+    };
+    struct Slot { Key k; CUtensorMap m; bool used = false; };
+    static thread_local Slot cache[1024];
+    const Key key{base, rows, cols, row_pitch_bytes, box_rows, dtype};
+    uint64_t hsh = reinterpret_cast<uintptr_t>(base) * 0x9E3779B97F4A7C15ull ^ (rows * 0xC2B2AE3D27D4EB4Full) ^ (cols << 20) ^ (row_pitch_bytes << 7) ^ box_rows ^ ((uint64_t)dtype << 40);
+    Slot& slot = cache[(hsh >> 32) & 1023];
+    if (slot.used && slot.k == key) { *out = slot.m; return B200_OK; }
     cuuint64_t dims[2] = {cols, rows};
     cuuint64_t strides[1] = {row_pitch_bytes};
     cuuint32_t box[2] = {dtype == 2 ? 32u : 64u, box_rows};
@@ -387,12 +399,19 @@ int make_tmap_2d_ex(CUtensorMap* out, const void* base, uint64_t rows, uint64_t 
                           const_cast<void*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                           CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
     if (r != CUDA_SUCCESS) return fail(B200_ECUDA, "cuTensorMapEncodeTiled failed with CUresult " + std::to_string((int)r));
+    slot.k = key; slot.m = *out; slot.used = true;
     return B200_OK;
 }
 
 template <int BN, int EPI, int ACT> static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const GemmParams& p, cudaStream_t st) {
     using Cfg = GemmCfg<BN>;
-    B200_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<BN, EPI, ACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+    static bool attr_set[64] = {false};
+    int dev = 0;
+    B200_CUDA_OK(cudaGetDevice(&dev));
+    if (dev >= 64 || !attr_set[dev]) {
+        B200_CUDA_OK(cudaFuncSetAttribute(gemm_tc_kernel<BN, EPI, ACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+        if (dev < 64) attr_set[dev] = true;
+    }
     const int tiles = ((p.M + BM - 1) / BM) * ((p.N + BN - 1) / BN);
     const int grid = tiles < kNumSMs ? tiles : kNumSMs;
     B200_CUDA_OK(launch_pdl(gemm_tc_kernel<BN, EPI, ACT>, dim3(grid), dim3(GEMM_THREADS), Cfg::SMEM_BYTES, st, ta, tb, tc, p));
@@ -401,7 +420,13 @@ template <int BN, int EPI, int ACT> static int launch_gemm(const CUtensorMap& ta
 }
 template <int BN, int EPI, int ACT> static int launch_gemm2(const CUtensorMap& ta, const CUtensorMap& tb, const CUtensorMap& tc, const GemmParams& p, cudaStream_t st) {
     using Cfg = Gemm2Cfg<BN>;
-    B200_CUDA_OK(cudaFuncSetAttribute(gemm_tc2_kernel<BN, EPI, ACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+    static bool attr_set[64] = {false};
+    int dev = 0;
+    B200_CUDA_OK(cudaGetDevice(&dev));
+    if (dev >= 64 || !attr_set[dev]) {
+        B200_CUDA_OK(cudaFuncSetAttribute(gemm_tc2_kernel<BN, EPI, ACT>, cudaFuncAttributeMaxDynamicSharedMemorySize, Cfg::SMEM_BYTES));
+        if (dev < 64) attr_set[dev] = true;
+    }
     const int tiles = ((p.M + 2 * BM - 1) / (2 * BM)) * ((p.N + BN - 1) / BN);
     const int pairs = tiles < kNumSMs / 2 ? tiles : kNumSMs / 2;
     B200_CUDA_OK(launch_pdl(gemm_tc2_kernel<BN, EPI, ACT>, dim3(2 * pairs), dim3(GEMM_THREADS), Cfg::SMEM_BYTES, st, ta, tb, tc, p));   // cluster dims are compiled in
@@ -439,7 +464,11 @@ int gemm_bf16_tc(const void* A, int lda, const void* W, int ldw, int M, int N, i
         return (double)((t + kNumSMs - 1) / kNumSMs) * bn;
     };
     int bn = 256;
-    if (N <= 128) bn = 128;
+    // one or two row tiles (single-image requests, small micro-batches): the pass is a chain of short weight-streaming kernels, and
+    // how many SMs pull on the weights is what counts: 64-wide tiles put four times as many CTAs on them as 256-wide ones
+    static const int small_bn = [] { const char* e = getenv("B200_GEMM_SMALL_BN"); return e ? atoi(e) : 64; }();
+    if (M <= 2 * BM && small_bn == 64 && N % 64 == 0) bn = 64;
+    else if (N <= 128) bn = 128;
     else {
         // measured on B200: 192- and 128-wide tiles only pay off when they save well over 5 % of the tile rounds
         const double c256 = rounds(256), c192 = rounds(192) * 1.08, c128 = rounds(128) * 1.15;
@@ -466,7 +495,8 @@ int gemm_bf16_tc(const void* A, int lda, const void* W, int ldw, int M, int N, i
     rc = make_tmap_2d(&tb, W, N, K, (uint64_t)ldw * 2, bn, false);
     if (rc) return rc;
     GemmParams p{M, N, K, bias, out, ldc, epi, act, status};
-    return bn == 128 ? dispatch_gemm<128>(ta, tb, tc, p, st) : bn == 192 ? dispatch_gemm<192>(ta, tb, tc, p, st) : dispatch_gemm<256>(ta, tb, tc, p, st);
+    return bn == 64 ? dispatch_gemm<64>(ta, tb, tc, p, st) : bn == 128 ? dispatch_gemm<128>(ta, tb, tc, p, st) :
+           bn == 192 ? dispatch_gemm<192>(ta, tb, tc, p, st) : dispatch_gemm<256>(ta, tb, tc, p, st);
 }
 
 }  // namespace b200

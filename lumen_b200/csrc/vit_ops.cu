@@ -375,7 +375,13 @@ int launch_attention(const void* qkv, void* out, int B, int S, int d, int heads,
     const int n_qt = (S + 63) / 64;
     const long long items = (long long)B * heads * n_qt;
     B200_REQUIRE(items < (1LL << 30), "attention: too many (image, head, tile) items");
-    B200_CUDA_OK(cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_SMEM));
+    static bool attr_set[64] = {false};
+    int dev = 0;
+    B200_CUDA_OK(cudaGetDevice(&dev));
+    if (dev >= 64 || !attr_set[dev]) {
+        B200_CUDA_OK(cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_SMEM));
+        if (dev < 64) attr_set[dev] = true;
+    }
     const int grid = (int)(items < 4LL * kNumSMs ? items : 4LL * kNumSMs);
     B200_CUDA_OK(launch_pdl(attention_kernel, dim3(grid), dim3(128), ATT_SMEM, st, reinterpret_cast<const __nv_bfloat16*>(qkv),
                             reinterpret_cast<__nv_bfloat16*>(out), S, d, heads, n_qt, (int)items));

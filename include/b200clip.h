@@ -124,9 +124,11 @@ int b200clip_encode_text(b200clip_handle* h, const int32_t* ids_dev, int32_t B, 
  * fancy chroma upsampling, fixed-point YCbCr->RGB), bit for bit.  jpegs[i] / lens[i]: n byte strings in host memory.  Huffman
  * decoding runs on `host_threads` host threads (0 = all cores); IDCT, upsampling and colour conversion run on the device and
  * write image i as H x W x 3 uint8 at dst_dev + offsets_out[i] (16-byte aligned, the layout b200clip_preprocess reads);
- * hw_out[2i], hw_out[2i+1] = H, W; *total_out = bytes used.  status_out[i] = 0 decoded, 1 = a flavour this decoder does not
- * cover (progressive, CMYK, 4:1:1, not a JPEG ...): nothing is written for it, hw_out is 0 and the caller decodes that image
- * itself.  A corrupt baseline stream fails the whole call.  b200clip_jpeg_probe reads only the headers (no device work). */
+ * hw_out[2i], hw_out[2i+1] = H, W; *total_out = bytes used.  status_out[i] = 0 decoded, 1 = left to the caller's own decoder:
+ * a flavour this one does not cover (progressive, CMYK, 4:1:1, not a JPEG, more pixels than PIL's MAX_IMAGE_PIXELS ...) or a
+ * stream it found damaged; nothing usable is written for it and hw_out is 0.  One bad image never fails the batch: whether a
+ * damaged file still decodes (with a warning) or raises stays the decision of the reference's PIL call.  b200clip_jpeg_probe
+ * reads only the headers (no device work). */
 int b200clip_jpeg_probe(const void* jpeg, size_t len, int32_t* hw, int32_t* ncomp);
 int b200clip_decode_jpeg(b200clip_handle* h, const void* const* jpegs, const size_t* lens, int32_t n, uint8_t* dst_dev,
                          int64_t dst_capacity, int64_t* offsets_out, int32_t* hw_out, int32_t* status_out, int64_t* total_out,
@@ -166,13 +168,18 @@ int b200clip_merge_topk(b200clip_handle* h, const float* part_scores_dev, const 
  * a real-time serving loop that must not hit the allocator's locks, or a plug-in living inside another framework's
  * memory pool.  Same kernels, arguments and results as b200clip_topk, but no handle: the scratch (candidate lists and
  * per-split results) is a fixed 32 MiB array compiled into the library, which every GPU that loads the library keeps
- * until exit.  It runs on the CURRENT device.  Limits: k <= 256 and Q*k small enough for the array (roughly 7000
+ * until exit.  It runs on the CURRENT device.  Limits: k <= 256 and Q*k small enough for the array (roughly 6200
  * queries at k = 100); larger requests fail with B200CLIP_EINVAL and a message naming the limit.  The first call on
  * each device resolves the array's device address (cudaGetSymbolAddress) — make that first call outside any stream
  * capture.  All calls share the one array, so two calls whose kernels overlap on the GPU (different streams or
  * threads) race; serialise them.  It calls neither cudaMalloc nor cudaFree nor any allocating library routine. */
 int b200clip_topk_static(const void* queries_f16_dev, int32_t Q, const void* gallery_f16_dev, int64_t N, int32_t D,
                          int32_t k, int64_t index_base, float* out_scores_dev, int64_t* out_index_dev, void* stream);
+/* The handle-less call above has no b200clip_sync to report a tripped device-side watchdog, so this does it (no counterpart in the
+ * reference either): synchronises `stream`, reads the watchdog words at the head of the built-in array on the CURRENT device and
+ * returns B200CLIP_EKERNEL (clearing them) if the last b200clip_topk_static there gave up on a pipeline barrier - its results
+ * are then garbage.  Allocates nothing; 8 bytes device -> host. */
+int b200clip_topk_static_status(void* stream);
 
 /* Building blocks exported for the parity tests (same kernels the calls above use). */
 int b200clip_gemm_bf16(b200clip_handle* h, const void* A_bf16_dev, const void* W_bf16_dev, int32_t M, int32_t N, int32_t K,

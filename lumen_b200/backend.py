@@ -160,8 +160,19 @@ class B200ClipBackend(BaseClipBackend):
         """Pipelined embed_packed over an iterable of (pinned_u8, total_bytes, offsets, hw): the upload of the next batch
         overlaps the encoding of the current one; yields one float32 [B, D] array per batch, in order."""
         self._ensure_initialized()
-        with self._lock:
-            yield from self._engine.embed_stream(batches, self._mode)
+        # the lock is taken per batch, never across a yield: other threads' requests interleave between batches, and a consumer
+        # that abandons the generator leaves nothing locked
+        gen = self._engine.embed_stream(batches, self._mode)
+        try:
+            while True:
+                with self._lock:
+                    try:
+                        out = next(gen)
+                    except StopIteration:
+                        return
+                yield out
+        finally:
+            gen.close()
 
     def image_to_vector(self, image_bytes: bytes) -> np.ndarray:
         self._ensure_initialized()

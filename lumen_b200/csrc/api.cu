@@ -77,6 +77,19 @@ struct b200clip_handle {
     TextTower* text = nullptr;          // b200clip_text_init
     DeviceStatus* status = nullptr;
     int64_t launches = 0;
+    // The workspace (activations, descriptors, decode arenas, search scratch) is one per handle.  The mutex orders the host side of
+    // two calls; when they name different streams, the later one also has to wait on the device for the earlier one's kernels.
+    cudaStream_t ws_stream = nullptr; cudaEvent_t ws_done = nullptr; bool ws_used = false;
+    int ws_begin(cudaStream_t st) {
+        if (ws_used && st != ws_stream) B200_CUDA_OK(cudaStreamWaitEvent(st, ws_done, 0));
+        return B200_OK;
+    }
+    int ws_end(cudaStream_t st) {
+        if (!ws_done) B200_CUDA_OK(cudaEventCreateWithFlags(&ws_done, cudaEventDisableTiming));
+        B200_CUDA_OK(cudaEventRecord(ws_done, st));
+        ws_stream = st; ws_used = true;
+        return B200_OK;
+    }
     // optional per-kernel-class timing (bench.py roofline): CUDA events recorded around each launch
     bool prof = false;
     std::vector<cudaEvent_t> ev_pool; size_t ev_used = 0;
@@ -183,6 +196,7 @@ extern "C" void b200clip_destroy(b200clip_handle* h) {
     cudaDeviceSynchronize();
     for (void* p : h->allocs) cudaFree(p);
     for (cudaEvent_t e : h->ev_pool) cudaEventDestroy(e);
+    if (h->ws_done) cudaEventDestroy(h->ws_done);
     cudaFree(h->upload_tmp); cudaFree(h->img_dev); cudaFree(h->emb_dev); cudaFree(h->topk_scratch);
     cudaFree(h->labels[0]); cudaFree(h->labels[1]);
     if (h->pre) preprocess_state_destroy(h->pre);
@@ -374,9 +388,11 @@ extern "C" int b200clip_preprocess(b200clip_handle* h, const uint8_t* src_dev, c
     std::lock_guard<std::mutex> lk(h->mu);
     const int P = h->cfg.patch;
     const int kpad = P > 0 ? (3 * P * P + 63) / 64 * 64 : 0;
+    if ((rc = h->ws_begin((cudaStream_t)stream))) return rc;
     rc = preprocess_run(h->pre, src_dev, reinterpret_cast<const long long*>(offsets), hw, B, h->cfg.image_size, mode, layout,
                         out_bf16, P, kpad, out_dev, (cudaStream_t)stream);
     if (rc == B200_OK && B > 0) h->launches += 1;
+    if (rc == B200_OK) rc = h->ws_end((cudaStream_t)stream);
     return rc;
 }
 
@@ -428,11 +444,12 @@ extern "C" int b200clip_encode(b200clip_handle* h, const void* patches_dev, int3
     if ((rc = require_encoder(h))) return rc;
     B200_REQUIRE(B >= 0 && (B == 0 || (patches_dev && emb_dev)), "encode: null buffer");
     const __nv_bfloat16* p = reinterpret_cast<const __nv_bfloat16*>(patches_dev);
+    if ((rc = h->ws_begin((cudaStream_t)stream))) return rc;
     for (int b0 = 0; b0 < B; b0 += h->cfg.max_batch) {
         const int nb = std::min(h->cfg.max_batch, B - b0);
         if ((rc = encode_chunk(h, p + (size_t)b0 * h->n * h->kpad, nb, emb_dev + (size_t)b0 * h->cfg.embed_dim, (cudaStream_t)stream))) return rc;
     }
-    return B200_OK;
+    return h->ws_end((cudaStream_t)stream);
 }
 
 static int embed_u8_locked(b200clip_handle* h, const uint8_t* src_dev, const int64_t* offsets, const int32_t* hw, int B, int mode,
@@ -440,6 +457,7 @@ static int embed_u8_locked(b200clip_handle* h, const uint8_t* src_dev, const int
     int rc;
     if ((rc = require_encoder(h))) return rc;
     B200_REQUIRE((reinterpret_cast<uintptr_t>(src_dev) & 15) == 0, "embed: src_dev must be 16-byte aligned");
+    if ((rc = h->ws_begin(st))) return rc;
     for (int b0 = 0; b0 < B; b0 += h->cfg.max_batch) {
         const int nb = std::min(h->cfg.max_batch, B - b0);
         cudaEvent_t pa = nullptr, pb = nullptr;
@@ -451,7 +469,7 @@ static int embed_u8_locked(b200clip_handle* h, const uint8_t* src_dev, const int
         h->launches += 1;
         if ((rc = encode_chunk(h, h->patches, nb, emb_dev + (size_t)b0 * h->cfg.embed_dim, st))) return rc;
     }
-    return B200_OK;
+    return h->ws_end(st);
 }
 
 extern "C" int b200clip_embed_u8(b200clip_handle* h, const uint8_t* src_dev, const int64_t* offsets, const int32_t* hw, int32_t B,
@@ -484,6 +502,7 @@ extern "C" int b200clip_embed_host(b200clip_handle* h, const uint8_t* src_host, 
         B200_CUDA_OK(cudaMalloc(&h->emb_dev, eneed * sizeof(float)));
         h->emb_cap = eneed;
     }
+    if ((rc = h->ws_begin(st))) return rc;                 // img_dev / emb_dev are part of the shared workspace too
     B200_CUDA_OK(cudaMemcpyAsync(h->img_dev, src_host, (size_t)total_bytes, cudaMemcpyHostToDevice, st));
     if ((rc = embed_u8_locked(h, h->img_dev, offsets, hw, B, mode, h->emb_dev, st))) return rc;
     B200_CUDA_OK(cudaMemcpyAsync(emb_host, h->emb_dev, eneed * sizeof(float), cudaMemcpyDeviceToHost, st));
@@ -549,9 +568,11 @@ extern "C" int b200clip_topk(b200clip_handle* h, const void* queries, int32_t Q,
         B200_CUDA_OK(cudaMalloc(&h->topk_scratch, need));
         h->topk_cap = need;
     }
+    if ((rc = h->ws_begin(st))) return rc;
     rc = topk_run(queries, gallery, Q, N, D, k, index_base, h->topk_scratch, plan, out_scores, reinterpret_cast<long long*>(out_index),
                   h->status, st);
     if (rc == B200_OK) h->launches += plan.qstage_bytes ? 3 : 2;
+    if (rc == B200_OK) rc = h->ws_end(st);
     return rc;
 }
 
@@ -639,11 +660,12 @@ extern "C" int b200clip_encode_text(b200clip_handle* h, const int32_t* ids_dev, 
         return fail(B200CLIP_ESTATE, "encode_text: text tower weights are not fully loaded");
     B200_REQUIRE(B >= 0 && (B == 0 || (ids_dev && emb_dev)), "encode_text: null buffer");
     const int mb = h->text->cfg.max_batch, ctx = h->text->cfg.context_length;
+    if ((rc = h->ws_begin((cudaStream_t)stream))) return rc;
     for (int b0 = 0; b0 < B; b0 += mb) {
         const int nb = std::min(mb, B - b0);
         if ((rc = encode_text_chunk(h, ids_dev + (size_t)b0 * ctx, nb, emb_dev + (size_t)b0 * h->text->cfg.embed_dim, (cudaStream_t)stream))) return rc;
     }
-    return B200_OK;
+    return h->ws_end((cudaStream_t)stream);
 }
 
 // ------------------------------------------------------------------------------------------ N2: JPEG decode in front of K1
@@ -659,9 +681,11 @@ extern "C" int b200clip_decode_jpeg(b200clip_handle* h, const void* const* jpegs
     std::lock_guard<std::mutex> lock(h->mu);
     if (!h->jpeg) { h->jpeg = jpeg_state_create(&rc); if (!h->jpeg) return rc; }
     int launches = 0;
+    if ((rc = h->ws_begin((cudaStream_t)stream))) return rc;
     rc = jpeg_decode_batch(h->jpeg, jpegs, lens, n, dst_dev, (size_t)dst_capacity, offsets_out, hw_out, status_out, total_out, host_threads,
                            (cudaStream_t)stream, &launches);
     h->launches += launches;
+    if (rc == B200_OK) rc = h->ws_end((cudaStream_t)stream);
     return rc;
 }
 

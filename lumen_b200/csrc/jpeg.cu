@@ -30,15 +30,26 @@ constexpr uint8_t kZigzag[64] = {0,  1,  8,  16, 9,  2,  3,  10, 17, 24, 32, 25,
 struct HuffTable {
     bool present = false;
     uint8_t counts[17] = {0}, symbols[256] = {0};
+    int total = 0;                       // number of symbols
     int32_t max_code[18];
     int32_t first_index[17];
     uint32_t first_code[17];
     uint16_t fast[512];                  // (length << 8) | symbol, 0 = not a short code
     int16_t fast_ac[512];                // AC tables: (value << 8) | (run << 4) | (code + value bits) when both fit in 9 bits, else 0
 
-    void finish() {
+    // Builds the lookup tables; false when the code-length counts do not describe a prefix code (libjpeg's
+    // jpeg_make_d_derived_tbl refuses those too): a length that is over-subscribed would index past `fast` / `symbols`.
+    bool finish() {
         uint32_t code = 0;
         int k = 0;
+        present = false;
+        for (int len = 1; len <= 16; ++len) {
+            if (code + counts[len] > (1u << len)) return false;
+            code = (code + counts[len]) << 1;
+            k += counts[len];
+        }
+        if (k > 256) return false;
+        code = 0; k = 0;
         std::memset(fast, 0, sizeof fast);
         for (int len = 1; len <= 16; ++len) {
             first_index[len] = k;
@@ -62,7 +73,9 @@ struct HuffTable {
             if (v < (1 << (mag - 1))) v += (int)((~0u) << mag) + 1;
             if (v >= -128 && v <= 127) fast_ac[i] = (int16_t)(v * 256 + run * 16 + len + mag);
         }
+        total = k;
         present = true;
+        return true;
     }
 };
 
@@ -131,7 +144,12 @@ inline int decode_symbol(BitStream& bs, const HuffTable& t) {
     const uint32_t w = bs.peek(16);
     for (int len = 10; len <= 16; ++len) {
         const int32_t c = (int32_t)(w >> (16 - len));
-        if (c <= t.max_code[len]) { bs.drop(len); return t.symbols[t.first_index[len] + (c - (int32_t)t.first_code[len])]; }
+        if (c <= t.max_code[len]) {
+            const int at = t.first_index[len] + (c - (int32_t)t.first_code[len]);
+            if (at < 0 || at >= t.total) return -1;
+            bs.drop(len);
+            return t.symbols[at];
+        }
     }
     return -1;
 }
@@ -211,7 +229,7 @@ bool parse_headers(const uint8_t* data, size_t len, Parsed& P) {
                 if (total > 256 || s + total > se) return fail_parse(P, 2, "bad DHT");
                 std::memcpy(t.symbols, s, total);
                 s += total;
-                t.finish();
+                if (!t.finish()) return fail_parse(P, 2, "bad DHT (code lengths are not a prefix code)");
             }
             break;
         case 0xC0: case 0xC1:
@@ -220,6 +238,9 @@ bool parse_headers(const uint8_t* data, size_t len, Parsed& P) {
             P.d.width = (s[3] << 8) | s[4];
             ncomp = s[5];
             if (P.d.width <= 0 || P.d.height <= 0) return fail_parse(P, 1, "zero-sized frame");
+            // Pillow warns above Image.MAX_IMAGE_PIXELS (89,478,485) and raises DecompressionBombError above twice that; a header
+            // may claim 65535 x 65535.  Such frames are left to the caller's PIL call, which applies exactly that policy.
+            if ((int64_t)P.d.width * P.d.height > 89478485LL) return fail_parse(P, 1, "frame larger than PIL's MAX_IMAGE_PIXELS");
             if (ncomp != 1 && ncomp != 3) return fail_parse(P, 1, "only 1 or 3 components");
             if (L < 8 + 3 * ncomp) return fail_parse(P, 2, "bad SOF");
             for (int c = 0; c < ncomp; ++c) {
@@ -237,6 +258,7 @@ bool parse_headers(const uint8_t* data, size_t len, Parsed& P) {
         case 0xEE: if (L >= 14 && !std::memcmp(s, "Adobe", 5)) { adobe = true; adobe_transform = s[11]; } break;
         case 0xDA: {
             if (!have_frame) return fail_parse(P, 2, "SOS before SOF");
+            if (L < 3) return fail_parse(P, 2, "bad SOS");
             const int ns = s[0];
             if (ns != ncomp || L < 6 + 2 * ns) return fail_parse(P, 1, "components split over several scans");
             for (int i = 0; i < ns; ++i) {
@@ -519,7 +541,9 @@ template <class T> static int grow_host(T** p, size_t* cap, size_t need) {
     return B200_OK;
 }
 
-// status_out[i]: 0 decoded, 1 unsupported flavour (left for the caller's host decoder; hw_out = 0), corrupt streams fail the call.
+// status_out[i]: 0 decoded; 1 = left for the caller's host decoder (hw_out = 0): a flavour this decoder does not cover, or a stream it
+// found damaged (bad tables, bad codes, missing restart markers, no EOI).  Pillow / libjpeg decode many slightly damaged files with a
+// warning and refuse others, so that verdict stays with the reference's own PIL call, per image: one bad file never fails the batch.
 int jpeg_decode_batch(JpegState* s, const void* const* bufs, const size_t* lens, int n, void* dst, size_t dst_capacity,
                       int64_t* offsets_out, int32_t* hw_out, int32_t* status_out, int64_t* total_out, int threads, cudaStream_t st, int* launches) {
     *launches = 0;
@@ -530,8 +554,7 @@ int jpeg_decode_batch(JpegState* s, const void* const* bufs, const size_t* lens,
     int max_blocks = 0, max_groups = 0, ok_count = 0;
     for (int i = 0; i < n; ++i) {
         Parsed& P = parsed[i];
-        if (!parse_headers(static_cast<const uint8_t*>(bufs[i]), lens[i], P)) {
-            if (P.code == 2) return fail(B200_EINVAL, "jpeg: image " + std::to_string(i) + ": " + P.error);
+        if (bufs[i] == nullptr || !parse_headers(static_cast<const uint8_t*>(bufs[i]), lens[i], P)) {
             status_out[i] = 1; offsets_out[i] = 0; hw_out[2 * i] = hw_out[2 * i + 1] = 0;
             continue;
         }
@@ -563,7 +586,8 @@ int jpeg_decode_batch(JpegState* s, const void* const* bufs, const size_t* lens,
     // entropy decoding: one image per task, tasks pulled in index order by a small pool of host threads.  The calling thread
     // follows behind them and uploads the coefficients of finished images in runs of >= 8 MB, so the H2D copy (2 bytes per
     // padded sample: as large as the decoded image) overlaps the decoding instead of following it.
-    std::atomic<int> next{0}, bad{-1};
+    std::atomic<int> next{0};
+    std::vector<unsigned char> damaged(n, 0);                     // written by the worker that owns image i, read after the join
     std::vector<std::atomic<unsigned char>> done(n);
     for (int i = 0; i < n; ++i) done[i].store(status_out[i] != 0 ? 1 : 0, std::memory_order_relaxed);
     auto worker = [&] {
@@ -572,7 +596,7 @@ int jpeg_decode_batch(JpegState* s, const void* const* bufs, const size_t* lens,
             if (status_out[i] != 0) continue;
             const JpegDesc& d = P.d;
             std::memset(s->coef_host + d.coef_off[0], 0, (size_t)d.block_begin[d.ncomp] * 64 * sizeof(int16_t));
-            if (!decode_entropy(P, s->coef_host)) { int e = -1; bad.compare_exchange_strong(e, i); }
+            if (!decode_entropy(P, s->coef_host)) damaged[i] = 1;
             done[i].store(1, std::memory_order_release);
         }
     };
@@ -600,10 +624,8 @@ int jpeg_decode_batch(JpegState* s, const void* const* bufs, const size_t* lens,
         }
         for (auto& th : pool) th.join();
     }
-    if (bad.load() >= 0) {
-        cudaStreamSynchronize(st);                                // queued uploads read the pinned arena: let them finish before it is reused
-        return fail(B200_EINVAL, "jpeg: image " + std::to_string(bad.load()) + ": " + parsed[bad.load()].error);
-    }
+    for (int i = 0; i < n; ++i)
+        if (damaged[i]) { status_out[i] = 1; offsets_out[i] = 0; hw_out[2 * i] = hw_out[2 * i + 1] = 0; }   // its slot in dst stays unused
     for (int i = 0; i < n; ++i) {
         s->desc_host[i] = parsed[i].d;
         if (status_out[i] != 0) { s->desc_host[i].ncomp = 0; s->desc_host[i].block_begin[0] = 0; s->desc_host[i].width = s->desc_host[i].height = 0; }

@@ -250,8 +250,13 @@ topk_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
             // k-th best from below, so nothing below it can reach the final top-k.  Scores EQUAL to it are kept (key - 1 = the next
             // float below): the index-ordered tie rule may still prefer them.  Without this every split warms up on its own.
             if (qrow < p.Q) {
-                const unsigned g = __ldcg(p.gtau + qrow);
-                if (g > 1u) tau = fmaxf(tau, unflip_f32(g - 1u));
+                unsigned g = __ldcg(p.gtau + qrow);
+                if (g > 1u) {
+                    // the float just below the shared bound.  Below +0.0 that is the negative denormal, not -0.0 (key - 1), which
+                    // compares EQUAL to +0.0 and would drop exact-zero scores (zero or padding rows) the tie rule may still prefer.
+                    g = g == 0x80000000u ? 0x7ffffffeu : g - 1u;
+                    tau = fmaxf(tau, unflip_f32(g));
+                }
             }
             // Scan 8 chunks of 32 scores; the TMEM load of chunk c+1 is in flight while chunk c is examined.
             // A thread first reduces its 32 scores to their maximum: only if that beats tau (rare once the
@@ -663,7 +668,7 @@ extern "C" int b200clip_topk_static(const void* queries_f16_dev, int32_t Q, cons
     if (need(splits) > budget)
         return fail(B200_EINVAL, "topk_static: Q=" + std::to_string(Q) + ", k=" + std::to_string(k) + " needs " + std::to_string(need(splits)) +
                                  " bytes of scratch, the built-in array holds " + std::to_string(budget) +
-                                 " (about 7000 queries at k=100); use b200clip_topk with a handle instead");
+                                 " (about 6200 queries at k=100); use b200clip_topk with a handle instead");
     const long long tiles_per_split = (ntiles + splits - 1) / splits;
     plan.rows_per_split = tiles_per_split * TK_BN;
     plan.splits = (int)((ntiles + tiles_per_split - 1) / tiles_per_split);
@@ -677,4 +682,27 @@ extern "C" int b200clip_topk_static(const void* queries_f16_dev, int32_t Q, cons
     B200_CUDA_OK(cudaMemsetAsync(base, 0, 256, st));
     return topk_run(queries_f16_dev, gallery_f16_dev, Q, N, D, k, index_base, reinterpret_cast<unsigned char*>(base) + 256, plan,
                     out_scores_dev, reinterpret_cast<long long*>(out_index_dev), reinterpret_cast<DeviceStatus*>(base), st);
+}
+
+extern "C" int b200clip_topk_static_status(void* stream) {
+    using namespace b200;
+    int dev = -1;
+    B200_CUDA_OK(cudaGetDevice(&dev));
+    B200_REQUIRE(dev >= 0 && dev < 64, "topk_static_status: unsupported device ordinal");
+    void* base = nullptr;
+    {
+        std::lock_guard<std::mutex> lk(g_static_mu);
+        base = g_static_ptr[dev];
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    B200_CUDA_OK(cudaStreamSynchronize(st));
+    if (base == nullptr) return B200_OK;             // b200clip_topk_static has not run on this device yet
+    DeviceStatus ds;
+    B200_CUDA_OK(cudaMemcpyAsync(&ds, base, sizeof(ds), cudaMemcpyDeviceToHost, st));
+    B200_CUDA_OK(cudaStreamSynchronize(st));
+    if (ds.code != 0) {
+        B200_CUDA_OK(cudaMemsetAsync(base, 0, 256, st));
+        return fail(-5, "device watchdog: a pipeline barrier of b200clip_topk_static never completed (site " + std::to_string(ds.where) + ")");
+    }
+    return B200_OK;
 }

@@ -227,6 +227,19 @@ class Engine:
             raise _lib.B200ClipError(-1, "embed_bytes: an image is not a baseline JPEG and no host decoder was given")
         extra = sum(((a.size + 15) & ~15) for a in others.values())
         dev, offsets, hw, status, used = self.decode_jpeg(images, host_threads, extra)
+        # streams the device decoder found damaged after a clean header (status 1): the host decoder decides, per image, whether
+        # they still decode (PIL accepts many slightly damaged files with a warning) or raise
+        late = [i for i in range(n) if status[i] != 0 and i not in others]
+        if late:
+            if not host_decode:
+                raise _lib.B200ClipError(-1, f"embed_bytes: image {late[0]} is damaged and no host decoder was given")
+            for i in late:
+                others[i] = np.array(host_decode(images[i]), dtype=np.uint8, order="C")
+            need = used + sum(((a.size + 15) & ~15) for a in others.values()) + 16
+            if dev.numel() < need:
+                grown = torch.empty(int(need * 1.25), dtype=torch.uint8, device=dev.device)
+                grown[:used].copy_(dev[:used])
+                self._jpeg_dev = dev = grown
         for i, a in others.items():
             if a.ndim != 3 or a.shape[2] != 3:
                 raise _lib.B200ClipError(-1, "embed_bytes: host decoder must return H x W x 3 uint8")

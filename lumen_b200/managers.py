@@ -151,15 +151,24 @@ class ShardedGallery:
 
 
 class B200BioCLIPModelManager:
-    """Raw-cosine top-k over a large label matrix (bioclip_model.py:219-335).  The matrix is unit-normalised if it
-    is not already (:251-256), stored fp16 on the device, and searched with the fused kernel."""
+    """Raw-cosine top-k over a large label matrix (bioclip_model.py:219-335), stored fp16 on the device and searched with the
+    fused kernel.
 
-    def __init__(self, backend: B200ClipBackend, resources) -> None:
+    Like the reference, the dot product runs on the label matrix AS GIVEN: `classify_image` there builds a unit-length copy
+    (bioclip_model.py:251-256) but only logs it (:280-283); `similarities` is `np.dot(img, self.text_embeddings.T)` on the raw rows
+    (:293, :313).  `normalize_gallery=True` is an opt-in extension (true cosine for label files that are not unit length), not the
+    reference's behaviour.  Two stated deviations, both inside the 1e-3 score tolerance of the parity tests: the rows are kept as
+    fp16 and the query is rounded to fp16 before the tensor-core dot product (fp32 accumulation)."""
+
+    def __init__(self, backend: B200ClipBackend, resources, normalize_gallery: bool = False) -> None:
         self.backend = backend
         self.resources = resources
         self.labels = resources.labels.tolist() if resources.labels is not None else []
         self.text_embeddings = resources.label_embeddings
+        self.model_id = f"{resources.model_name}_{resources.runtime}"
         self.supports_classification = resources.has_classification_support()
+        self.normalize_gallery = bool(normalize_gallery)
+        self._load_time = None
         self.is_initialized = False
         self._gallery = None
 
@@ -176,35 +185,53 @@ class B200BioCLIPModelManager:
     def initialize(self) -> None:
         if self.is_initialized:
             return
-        torch = _torch()
+        t0 = time.time()
         try:
             self.backend.initialize()
+            if self.supports_classification and self.text_embeddings is None and self.labels:
+                prompts = [f"a photo of {name}" for name in self.labels]          # bioclip_model.py:135-143
+                self.text_embeddings = self.backend.text_batch_to_vectors(prompts).astype(np.float32, copy=False)
             if self.text_embeddings is not None:
                 t = np.asarray(self.text_embeddings, np.float32)
-                if t.shape[0] != len(self.labels) and t.shape[1] == len(self.labels):
-                    t = t.T                                           # bioclip_model.py:294-302
+                dim = int(self.backend.engine.embed_dim)
+                if t.ndim == 2 and t.shape[0] == len(self.labels) and t.shape[1] == dim:
+                    pass
+                elif t.ndim == 2 and t.shape[1] == len(self.labels) and t.shape[0] == dim:
+                    t = t.T                                           # bioclip_model.py:294-302: wrong axis order, transposed
+                else:
+                    raise RuntimeError(f"Text embeddings shape incompatible: {t.shape}")      # :303-309
                 from .gallery import DeviceGallery
-                norms = np.linalg.norm(t, axis=1, keepdims=True)
-                needs = not np.allclose(norms.flatten(), 1.0, atol=1e-6)   # bioclip_model.py:251-256: only then divide
-                self._gallery = DeviceGallery(self.backend.engine, t.shape[1], capacity=t.shape[0], normalized=True)
-                self._gallery.append(t, normalize=needs)                   # fp32 -> (unit norm) -> fp16 on the device
+                self._gallery = DeviceGallery(self.backend.engine, t.shape[1], capacity=t.shape[0], normalized=self.normalize_gallery)
+                self._gallery.append(t, normalize=self.normalize_gallery)      # fp32 rows -> fp16 on the device
             self.is_initialized = True
+            self._load_time = time.time() - t0
         except Exception as e:  # noqa: BLE001
             raise RuntimeError(f"Model initialization failed: {e}") from e
 
+    def _ensure_initialized(self) -> None:
+        if not self.is_initialized:
+            raise RuntimeError("Model manager not initialized. Call initialize() first.")
+
+    def encode_image(self, image_bytes: bytes) -> np.ndarray:
+        self._ensure_initialized()
+        return self.backend.image_to_vector(image_bytes)
+
     def search_embeddings(self, emb: np.ndarray, top_k: int):
+        """Batched form of the search inside classify_image: float32 [Q, D] (or [D]) -> (scores [Q, k], indices [Q, k])."""
+        self._ensure_initialized()
+        if self._gallery is None:
+            raise RuntimeError("Text embeddings are not available")
         torch = _torch()
         q = torch.from_numpy(np.ascontiguousarray(np.atleast_2d(emb).astype(np.float16))).to(self._gallery.view().device)
         s, i = self._gallery.search(q, top_k)
         return s.cpu().numpy(), i.cpu().numpy()
 
     def classify_image(self, image_bytes: bytes, top_k: int = 3) -> list[tuple[str, float]]:
-        if not self.is_initialized:
-            raise RuntimeError("Model manager not initialized. Call initialize() first.")
+        self._ensure_initialized()
         if not self.supports_classification:
             raise RuntimeError("Classification not supported: no dataset loaded. "
                                "Ensure TreeOfLife dataset exists in the model directory.")
         if self._gallery is None:
             raise RuntimeError("Text embeddings are not available")
-        s, i = self.search_embeddings(self.backend.image_to_vector(image_bytes), top_k)
+        s, i = self.search_embeddings(self.encode_image(image_bytes), top_k)
         return [(self.extract_name(self.labels[int(j)]), float(v)) for v, j in zip(s[0], i[0]) if j >= 0]

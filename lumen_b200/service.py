@@ -22,9 +22,11 @@ from .interface import BaseClipBackend
 class MicroBatcher:
     """Thread-safe coalescer in front of any backend with `image_batch_to_vectors`.
 
-    A caller blocks in `image_to_vector`; the first caller of a window becomes the leader, waits up to
-    `max_wait_ms` for companions (or until `max_batch` requests are queued), runs ONE batched call and hands every
-    caller its own row.  An exception of the batched call is re-raised in every caller of that batch."""
+    A caller blocks in `image_to_vector`.  Whoever finds no batch in flight leads ONE batch: it waits until the oldest queued
+    request is `max_wait_ms` old (or `max_batch` requests are queued), runs one batched call, hands every caller of that batch its
+    own row and gives the lead away; a caller whose request is still queued takes over.  So no caller serves other callers' batches
+    after its own result is ready, however steady the traffic.  When a batched call fails, its requests are retried one by one, so
+    only the caller whose image is at fault sees the error (the reference handles every request on its own)."""
 
     def __init__(self, backend, max_batch: int = 64, max_wait_ms: float = 2.0) -> None:
         self.backend, self.max_batch, self.max_wait = backend, int(max_batch), max_wait_ms / 1e3
@@ -32,49 +34,61 @@ class MicroBatcher:
         self._queue: list[dict] = []
         self._leader_active = False
         self.batches_run = 0
+        self.retried_singly = 0
 
     def image_to_vector(self, image_bytes: bytes) -> np.ndarray:
-        slot = {"bytes": image_bytes, "out": None, "err": None, "done": False}
+        slot = {"bytes": image_bytes, "out": None, "err": None, "done": False, "t": time.monotonic()}
         with self._cv:
             self._queue.append(slot)
             self._cv.notify_all()
-            lead = not self._leader_active
-            if lead:
-                self._leader_active = True
-        if lead:
-            self._lead()
-        with self._cv:
-            while not slot["done"]:
-                self._cv.wait()
+        while True:
+            with self._cv:
+                while not slot["done"] and self._leader_active:
+                    self._cv.wait()
+                if slot["done"]:
+                    break
+                self._leader_active = True                      # nobody is leading and this request is still queued
+            try:
+                self._lead_one_batch()
+            finally:
+                with self._cv:
+                    self._leader_active = False
+                    self._cv.notify_all()
         if slot["err"] is not None:
             raise slot["err"]
         return slot["out"]
 
-    def _lead(self) -> None:
-        while True:
-            deadline = time.monotonic() + self.max_wait
-            with self._cv:
-                while len(self._queue) < self.max_batch:
-                    left = deadline - time.monotonic()
-                    if left <= 0:
-                        break
-                    self._cv.wait(left)
-                batch, self._queue = self._queue[: self.max_batch], self._queue[self.max_batch:]
-            try:
-                out = self.backend.image_batch_to_vectors([s["bytes"] for s in batch])
-                for s, row in zip(batch, out):
-                    s["out"] = np.ascontiguousarray(row, dtype=np.float32)
-            except Exception as e:  # noqa: BLE001 - every waiter of this batch sees the failure
+    def _lead_one_batch(self) -> None:
+        with self._cv:
+            while len(self._queue) < self.max_batch:
+                left = self._queue[0]["t"] + self.max_wait - time.monotonic() if self._queue else 0.0
+                if left <= 0:
+                    break
+                self._cv.wait(left)
+            batch, self._queue = self._queue[: self.max_batch], self._queue[self.max_batch:]
+        if not batch:
+            return
+        try:
+            out = self.backend.image_batch_to_vectors([s["bytes"] for s in batch])
+            if len(out) != len(batch):
+                raise RuntimeError(f"backend returned {len(out)} vectors for {len(batch)} images")
+            for s, row in zip(batch, out):
+                s["out"] = np.ascontiguousarray(row, dtype=np.float32)
+        except Exception as e:  # noqa: BLE001
+            if len(batch) == 1:
+                batch[0]["err"] = e
+            else:                                               # find the offender(s): everyone else still gets a result
+                self.retried_singly += 1
                 for s in batch:
-                    s["err"] = e
-            with self._cv:
-                self.batches_run += 1
-                for s in batch:
-                    s["done"] = True
-                self._cv.notify_all()
-                if not self._queue:
-                    self._leader_active = False
-                    return
+                    try:
+                        s["out"] = np.ascontiguousarray(self.backend.image_batch_to_vectors([s["bytes"]])[0], dtype=np.float32)
+                    except Exception as e1:  # noqa: BLE001
+                        s["err"] = e1
+        with self._cv:
+            self.batches_run += 1
+            for s in batch:
+                s["done"] = True
+            self._cv.notify_all()
 
 
 class BatchedBackendView(BaseClipBackend):

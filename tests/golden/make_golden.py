@@ -127,8 +127,18 @@ def gen_classify():
         be.vec = q[r].copy()
         res = bio.classify_image(b"x", top_k=10)
         bio_idx[r] = [int(l.split("_")[1]) for l, _ in res]; bio_s[r] = [s for _, s in res]
-    np.savez_compressed(OUT / "classify.npz", seeds=np.array([7, 8, 9, 10]), queries=q, cls_idx=cls_idx, cls_p=cls_p,
-                        scene_idx=sc_idx, scene_p=sc_p, bio_idx=bio_idx, bio_s=bio_s)
+    # BioCLIP on a gallery that is NOT unit length: the reference computes a normalised copy (bioclip_model.py:251-256) but the dot
+    # product at :313 runs on the raw rows (:293), so ranking and scores follow the raw matrix.  Rows scaled by 0.5 .. 2.
+    g_raw = (g * np.random.default_rng(12).uniform(0.5, 2.0, (NG, 1))).astype(np.float32)
+    bio2 = BioCLIPModelManager(be, Res(glabels, g_raw)); bio2.initialize()
+    braw_idx = np.zeros((NQ, 10), np.int64); braw_s = np.zeros((NQ, 10), np.float32)
+    for r in range(NQ):
+        be.vec = q[r].copy()
+        res = bio2.classify_image(b"x", top_k=10)
+        braw_idx[r] = [int(l.split("_")[1]) for l, _ in res]; braw_s[r] = [s for _, s in res]
+    assert not np.array_equal(braw_idx, bio_idx)
+    np.savez_compressed(OUT / "classify.npz", seeds=np.array([7, 8, 9, 10, 12]), queries=q, cls_idx=cls_idx, cls_p=cls_p,
+                        scene_idx=sc_idx, scene_p=sc_p, bio_idx=bio_idx, bio_s=bio_s, bio_raw_idx=braw_idx, bio_raw_s=braw_s)
     print("classify.npz ok")
 
 
@@ -137,7 +147,9 @@ def gen_encoder():
     from transformers import CLIPVisionConfig, CLIPVisionModelWithProjection
 
     out = {}
-    for name, B in (("ViT-tiny-test", 4), ("ViT-B-32", 4)):
+    # ViT-B/16 (BASELINE config C3) and ViT-L/14@336 (C4): two images each keep the fixture small; 24 layers at d = 1024 is where a
+    # bf16 tower drifts furthest from fp32, so that is the depth the 0.999 gate has to be shown at
+    for name, B in (("ViT-tiny-test", 4), ("ViT-B-32", 4), ("ViT-B-16", 2), ("ViT-L-14-336", 2)):
         cfg = VIT_CONFIGS[name]
         hf = CLIPVisionConfig(hidden_size=cfg["width"], intermediate_size=cfg["mlp_dim"], projection_dim=cfg["embed_dim"],
                               num_hidden_layers=cfg["layers"], num_attention_heads=cfg["heads"], image_size=cfg["image_size"],

@@ -195,14 +195,16 @@ def test_attention_tc_short_sequences():
 
 
 # ------------------------------------------------------------------------------------------ encoder end to end
-@pytest.mark.parametrize("name,B", [("ViT-tiny-test", 5), ("ViT-B-32", 4)])
-def test_encoder_cosine_vs_oracle_and_golden(golden_enc, name, B):
+@pytest.mark.parametrize("name,B,max_batch", [("ViT-tiny-test", 5, 3), ("ViT-B-32", 4, 3), ("ViT-B-16", 6, 4), ("ViT-L-14-336", 2, 2)])
+def test_encoder_cosine_vs_oracle_and_golden(golden_enc, name, B, max_batch):
+    """Every tower BASELINE.json's configs name (B/32: C1-C2, B/16: C3, L/14@336: C4), composed end to end in bf16 against the fp32
+    oracle and against transformers' own output (golden)."""
     from lumen_b200 import VIT_CONFIGS, synthetic_weights
     from lumen_b200.engine import Engine
     from oracle import clip_oracle as O
     cfg = VIT_CONFIGS[name]
     w = synthetic_weights(cfg, seed=0)
-    eng = Engine(cfg, device=0, max_batch=3)                     # max_batch < B exercises chunking
+    eng = Engine(cfg, device=0, max_batch=max_batch)             # max_batch < B exercises chunking
     eng.load_weights(w)
     rng = np.random.default_rng(12)
     imgs = [rng.integers(0, 256, (cfg["image_size"] + 13 * i, cfg["image_size"] + 7 * i, 3), dtype=np.uint8) for i in range(B)]
@@ -212,13 +214,14 @@ def test_encoder_cosine_vs_oracle_and_golden(golden_enc, name, B):
     assert cos.min() >= 0.999, cos                                  # BASELINE.json tolerance
     np.testing.assert_allclose(np.linalg.norm(emb, axis=1), 1.0, atol=1e-5)
     # golden (transformers' CLIPVisionModelWithProjection on seeded Gaussian pixels): feed the same pixels as patches
-    px = np.random.default_rng(11).standard_normal((4, 3, cfg["image_size"], cfg["image_size"])).astype(np.float32)
+    gold = golden_enc[f"{name}/image_embeds"]
+    G = gold.shape[0]
+    px = np.random.default_rng(11).standard_normal((G, 3, cfg["image_size"], cfg["image_size"])).astype(np.float32)
     P, n_side = cfg["patch"], cfg["image_size"] // cfg["patch"]
-    pm = px.reshape(4, 3, n_side, P, n_side, P).transpose(0, 2, 4, 1, 3, 5).reshape(4 * n_side * n_side, 3 * P * P)
+    pm = px.reshape(G, 3, n_side, P, n_side, P).transpose(0, 2, 4, 1, 3, 5).reshape(G * n_side * n_side, 3 * P * P)
     kpad = (3 * P * P + 63) // 64 * 64
     pmp = np.zeros((pm.shape[0], kpad), np.float32); pmp[:, :pm.shape[1]] = pm
-    e2 = eng.encode(torch.from_numpy(pmp).to(torch.bfloat16).cuda(), 4).cpu().numpy()
-    gold = golden_enc[f"{name}/image_embeds"]
+    e2 = eng.encode(torch.from_numpy(pmp).to(torch.bfloat16).cuda(), G).cpu().numpy()
     gold = gold / np.linalg.norm(gold, axis=1, keepdims=True)
     assert (e2 * gold).sum(1).min() >= 0.999
     eng.sync()
@@ -330,6 +333,26 @@ def test_topk_adversarial_ascending_and_merge():
     eng.close()
 
 
+def test_topk_exact_zero_scores_across_splits():
+    """Scores of exactly +0.0 (zero / padding rows, a zero query) tie across the gallery splits that share a threshold: the
+    k smallest indices must win, every run (the shared bound must not exclude scores equal to it)."""
+    from lumen_b200.engine import Engine
+    from oracle import clip_oracle as O
+    eng = Engine({}, device=0)
+    N, D, k = 400_000, 64, 100
+    g = np.zeros((N, D), np.float16)
+    g[::7, 1] = -1.0                                     # some rows score below zero for query 0, above for query 2
+    q = np.zeros((3, D), np.float16); q[0, 1] = 1.0; q[2, 1] = -1.0          # query 1 is all zero: every score is +0.0
+    gt, qt = torch.from_numpy(g).cuda(), torch.from_numpy(q).cuda()
+    so, io = O.topk_cosine(q, g, k)
+    for _ in range(5):                                   # which split publishes its bound first is a race: repeat
+        s, i = eng.topk(qt, gt, k)
+        eng.sync()
+        assert np.array_equal(i.cpu().numpy(), io) and np.array_equal(s.cpu().numpy(), so)
+    assert io[1].tolist() == list(range(k))
+    eng.close()
+
+
 def test_full_size_properties_c2_and_search():
     """BASELINE sizes: batch 512 of 224x224 (C2) — determinism and batch-independence; 1M x 512 gallery, Q=256,
     k=100 — every returned score is the true dot product, sorted, and no better row was missed (spot rows)."""
@@ -344,6 +367,13 @@ def test_full_size_properties_c2_and_search():
     e3 = eng.embed_host(imgs[100:108])
     assert ((e1[100:108] * e3).sum(1) > 0.99999).all()
     np.testing.assert_allclose(np.linalg.norm(e1, axis=1), 1.0, atol=1e-5)
+    # the batch-512 pass is the one bench.py times (CTA-pair GEMMs, M = 25,600): 16 of its rows against the oracle
+    from oracle import clip_oracle as O
+    pick = list(range(0, 512, 32))
+    w = synthetic_weights(cfg, 0)
+    ref = O.vit_encode(w, O.preprocess_batch([imgs[j] for j in pick], 224, 0), cfg)
+    cos = (e1[pick] * ref).sum(1)
+    assert cos.min() >= 0.999, cos                                  # BASELINE.json tolerance
     gen = torch.Generator(device="cuda").manual_seed(42)
     N, Q, k = 1_000_000, 256, 100
     g = torch.nn.functional.normalize(torch.randn(N, 512, device="cuda", generator=gen), dim=1).half()
@@ -358,6 +388,39 @@ def test_full_size_properties_c2_and_search():
     for r, row in enumerate(rows):
         assert len(set(i[row].tolist()) ^ set(ti[r].tolist())) <= 4
     eng.close()
+
+
+_GEMM_VARIANT = r"""
+import sys, numpy as np
+sys.path.insert(0, ".")
+from lumen_b200 import VIT_CONFIGS, synthetic_weights
+from lumen_b200.engine import Engine
+from oracle import clip_oracle as O
+cfg = VIT_CONFIGS["ViT-B-32"]; w = synthetic_weights(cfg, 0)
+eng = Engine(cfg, device=0, max_batch=64); eng.load_weights(w)
+imgs = list(np.random.default_rng(77).integers(0, 256, (64, 224, 224, 3), dtype=np.uint8))
+e = eng.embed_host(imgs)
+ref = O.vit_encode(w, O.preprocess_batch(imgs[:8], 224, 0), cfg)
+cos = (e[:8] * ref).sum(1)
+assert cos.min() >= 0.999, cos
+np.save(sys.argv[1], e)
+print("ok")
+"""
+
+
+def test_encoder_both_gemm_variants_vs_oracle(tmp_path):
+    """The single-CTA and the CTA-pair (cta_group::2) GEMM kernels each carry a whole tower to cosine >= 0.999 against the oracle
+    (B200_GEMM_PAIR is read once per process, hence the subprocesses), and agree with each other."""
+    import os, subprocess, sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    outs = []
+    for pair in ("0", "1"):
+        f = str(tmp_path / f"emb_pair{pair}.npy")
+        r = subprocess.run([sys.executable, "-c", _GEMM_VARIANT, f], cwd=root, env=dict(os.environ, B200_GEMM_PAIR=pair),
+                           capture_output=True, text=True, timeout=600)
+        assert r.returncode == 0 and r.stdout.strip().endswith("ok"), r.stdout[-2000:] + r.stderr[-2000:]
+        outs.append(np.load(f))
+    assert (outs[0] * outs[1]).sum(1).min() > 0.9999
 
 
 def test_encoder_exact_gelu_variant():

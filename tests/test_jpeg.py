@@ -67,6 +67,44 @@ def test_probe_is_host_only_and_matches_headers(golden_jpeg):
             assert info[2] == (1 if "gray" in name else 3), name
 
 
+def _dht_segment(cls_id: int, counts, symbols=b"") -> bytes:
+    body = bytes([cls_id]) + bytes(counts) + bytes(symbols)
+    return b"\xff\xc4" + (len(body) + 2).to_bytes(2, "big") + body
+
+
+def test_probe_survives_malformed_headers(golden_jpeg):
+    """Client bytes reach the header parser unfiltered (image_to_vector -> embed_bytes -> jpeg_probe): crafted or damaged segments
+    must be refused, never crash.  The first case is a 280-byte file whose DHT over-subscribes length 1 (255 codes of one bit)."""
+    from lumen_b200.engine import Engine
+    soi = b"\xff\xd8"
+    counts = [0] * 16; counts[0] = 255
+    assert Engine.jpeg_probe(soi + _dht_segment(0x00, counts, bytes(255)) + b"\xff\xd9") is None
+    for bad_len in range(1, 17):                                 # every single over-subscribed length, DC and AC tables
+        counts = [0] * 16; counts[bad_len - 1] = min(255, (1 << bad_len) + 1)
+        for cls_id in (0x00, 0x10, 0x03, 0x13):
+            assert Engine.jpeg_probe(soi + _dht_segment(cls_id, counts, bytes(counts[bad_len - 1]))) is None
+    counts = [16] * 16                                           # 256 symbols but not a prefix code
+    assert Engine.jpeg_probe(soi + _dht_segment(0x00, counts, bytes(256))) is None
+    name, data, rgb = next(c for c in golden_jpeg if c[0].startswith("64x48") and "420" in c[0])
+    assert Engine.jpeg_probe(data)[:2] == rgb.shape[:2]
+    sos = data.index(b"\xff\xda")
+    assert Engine.jpeg_probe(data[:sos] + b"\xff\xda\x00\x02") is None          # SOS with no payload at the end of the buffer
+    assert Engine.jpeg_probe(data[:sos] + b"\xff\xda\x00\x03\x07") is None      # ... and with a component count only
+    sof = data.index(b"\xff\xc0")
+    huge = bytearray(data); huge[sof + 5:sof + 9] = b"\xff\xff\xff\xff"        # 65535 x 65535: beyond PIL's pixel limit
+    assert Engine.jpeg_probe(bytes(huge)) is None
+    rng = np.random.default_rng(2024)
+    hdr = sos + 14
+    for it in range(3000):                                       # random damage confined to the header segments
+        b = bytearray(data)
+        for _ in range(int(rng.integers(1, 6))):
+            b[int(rng.integers(2, hdr))] = int(rng.integers(0, 256))
+        if it % 3 == 0:
+            b = b[:int(rng.integers(2, hdr))]
+        info = Engine.jpeg_probe(bytes(b))
+        assert info is None or (0 < info[0] <= 65535 and 0 < info[1] <= 65535 and info[2] in (1, 3))
+
+
 # ------------------------------------------------------------------------------------------------ GPU
 @pytest.mark.gpu
 def test_device_decode_bit_exact_vs_goldens(golden_jpeg):
@@ -114,10 +152,37 @@ def test_device_decode_large_images_vs_oracle_and_pillow():
     dev, off, hw, status, used = eng.decode_jpeg(datas[:1])
     eng.sync()
     assert np.array_equal(dev[off[0]:off[0] + refs[0].size].cpu().numpy().reshape(refs[0].shape), refs[0])
-    # corrupt baseline stream: the call fails loudly
-    from lumen_b200 import _lib
-    with pytest.raises(_lib.B200ClipError):
-        eng.decode_jpeg([datas[0][:len(datas[0]) // 2]])       # cut in the middle of the entropy-coded data: no EOI
+    # a damaged baseline stream (cut in the middle of the entropy-coded data: no EOI) is handed back to the caller's decoder,
+    # per image; its neighbours in the batch are decoded as usual
+    dev, off, hw, status, used = eng.decode_jpeg([datas[0], datas[0][:len(datas[0]) // 2], datas[3]])
+    eng.sync()
+    assert status.tolist() == [0, 1, 0] and tuple(hw[1]) == (0, 0)
+    host = dev[:used].cpu().numpy()
+    for i, ref in ((0, refs[0]), (2, refs[3])):
+        assert np.array_equal(host[off[i]:off[i] + ref.size].reshape(ref.shape), ref), i
+    eng.close()
+
+
+@pytest.mark.gpu
+def test_device_decode_survives_damaged_streams(golden_jpeg):
+    """Random damage anywhere in the file (headers, tables, entropy-coded data): every image comes back as decoded or as
+    'left to the host decoder', the batch call itself never fails and nothing crashes."""
+    from lumen_b200.engine import Engine
+    eng = Engine({}, device=0)
+    rng = np.random.default_rng(99)
+    base = [c[1] for c in golden_jpeg if not c[0].startswith("refuse")]
+    datas = []
+    for it in range(400):
+        b = bytearray(base[it % len(base)])
+        for _ in range(int(rng.integers(1, 8))):
+            b[int(rng.integers(2, len(b)))] = int(rng.integers(0, 256))
+        if it % 5 == 0:
+            b = b[:int(rng.integers(2, len(b)))]
+        datas.append(bytes(b))
+    datas.append(base[0])
+    dev, off, hw, status, used = eng.decode_jpeg(datas)
+    eng.sync()
+    assert set(status.tolist()) <= {0, 1} and status[-1] == 0 and (status[:-1] == 1).sum() > 20
     eng.close()
 
 
@@ -139,4 +204,11 @@ def test_bytes_to_embeddings_equals_decoded_path(golden_jpeg):
     from lumen_b200 import _lib
     with pytest.raises(_lib.B200ClipError):
         eng.embed_bytes([pick[-1][1]], mode=0)               # not a JPEG and no host decoder given
+    # a JPEG cut short: the device decoder hands it back, PIL refuses it ("image file is truncated") -> the call raises, as the
+    # reference's Image.open(...).convert("RGB") does
+    cut = pick[0][1][:len(pick[0][1]) - 40]
+    with pytest.raises(Exception):
+        eng.embed_bytes([pick[1][1], cut], mode=0, host_decode=B200ClipBackend._decode)
+    with pytest.raises(_lib.B200ClipError):
+        eng.embed_bytes([cut], mode=0)
     eng.close()

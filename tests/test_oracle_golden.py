@@ -74,13 +74,13 @@ def test_topk_tie_order_and_merge():
     assert i2[0].tolist() == [0, 2, 3, 1, -1, -1] and np.isneginf(s2[0, 4:]).all()
 
 
-@pytest.mark.parametrize("name", ["ViT-tiny-test", "ViT-B-32"])
+@pytest.mark.parametrize("name", ["ViT-tiny-test", "ViT-B-32", "ViT-B-16", "ViT-L-14-336"])
 def test_encoder_matches_transformers(golden_enc, name):
     cfg = VIT_CONFIGS[name]
     w = synthetic_weights(cfg, seed=0)
-    px = np.random.default_rng(11).standard_normal((4, 3, cfg["image_size"], cfg["image_size"])).astype(np.float32)
-    emb = O.vit_encode(w, px, cfg, normalize=False)
     want = golden_enc[f"{name}/image_embeds"]
+    px = np.random.default_rng(11).standard_normal((want.shape[0], 3, cfg["image_size"], cfg["image_size"])).astype(np.float32)
+    emb = O.vit_encode(w, px, cfg, normalize=False)
     np.testing.assert_allclose(emb, want, rtol=2e-4, atol=2e-4)
     cos = np.sum(O.l2_normalize(emb) * O.l2_normalize(want), axis=1)
     assert cos.min() > 0.999999

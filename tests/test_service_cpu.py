@@ -47,20 +47,46 @@ def test_micro_batcher_coalesces_concurrent_requests():
     assert v[0] == 3.0
 
 
-def test_micro_batcher_propagates_errors_to_the_whole_batch():
+def test_micro_batcher_leader_returns_under_steady_load():
+    """A caller must get its answer after the batch that holds its request, however many requests keep arriving behind it."""
+    be = FakeBackend(delay=0.02)
+    mb = MicroBatcher(be, max_batch=4, max_wait_ms=1)
+    stop = threading.Event()
+    lat = []
+
+    def client():
+        while not stop.is_set():
+            t0 = time.monotonic()
+            mb.image_to_vector(b"abcd")
+            lat.append(time.monotonic() - t0)
+
+    th = [threading.Thread(target=client) for _ in range(10)]
+    [t.start() for t in th]
+    time.sleep(1.0)
+    stop.set()
+    [t.join(timeout=5) for t in th]
+    assert not any(t.is_alive() for t in th)
+    # 10 clients, batches of 4, 20 ms per batch: a request waits for at most ~3 batches; a leader that kept serving others would
+    # stay inside for the whole second
+    assert len(lat) > 50 and max(lat) < 0.5, (len(lat), max(lat))
+
+
+def test_micro_batcher_isolates_the_failing_request():
+    """One damaged image must not fail the requests it was coalesced with (the reference serves every request on its own)."""
     be = FakeBackend()
     mb = MicroBatcher(be, max_batch=4, max_wait_ms=50)
-    errs = []
+    errs, oks = [], {}
 
     def work(payload):
         try:
-            mb.image_to_vector(payload)
+            oks[payload] = mb.image_to_vector(payload)
         except InferenceError as e:
-            errs.append(str(e))
+            errs.append((payload, str(e)))
 
     th = [threading.Thread(target=work, args=(p,)) for p in (b"ok", b"boom", b"ok2")]
     [t.start() for t in th]; [t.join() for t in th]
-    assert len(errs) >= 1 and all("boom" in e for e in errs)
+    assert [p for p, _ in errs] == [b"boom"] and "boom" in errs[0][1]
+    assert oks[b"ok"][0] == 2.0 and oks[b"ok2"][0] == 3.0
     assert mb.image_to_vector(b"fine")[0] == 4.0                                          # the batcher keeps working
 
 

@@ -40,14 +40,21 @@ def test_static_scratch_topk_matches_handle_path_twice():
     g2 = rng.standard_normal((70001, 512)).astype(np.float32); g2 /= np.linalg.norm(g2, axis=1, keepdims=True)
     q2 = rng.standard_normal((37, 512)).astype(np.float32); q2 /= np.linalg.norm(q2, axis=1, keepdims=True)
     cases = [(q1, g1, 100, 5), (q2.astype(np.float16), g2.astype(np.float16), 64, 0)]
-    for q, g, k, base in cases:
+    from oracle import clip_oracle as O
+    stream = C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    assert lib.b200clip_topk_static_status(stream) == 0            # nothing has run yet on this device, or nothing tripped
+    for n, (q, g, k, base) in enumerate(cases):
         qd, gd = torch.from_numpy(q).cuda(), torch.from_numpy(g).cuda()
         rc, s, i = _static_topk(lib, qd, gd, k, base)
         assert rc == 0, lib.b200clip_last_error()
+        assert lib.b200clip_topk_static_status(stream) == 0, lib.b200clip_last_error()    # the watchdog words of the array are clean
         rs, ri = eng.topk(qd, gd, k, index_base=base)
         torch.cuda.synchronize()
         assert torch.equal(i, ri)
         assert torch.equal(s, rs)           # same kernels, same per-element arithmetic: identical bits
+        if n == 0:                          # exact arithmetic: the oracle's answer, bit for bit, ties in index order
+            so, io = O.topk_cosine(q, g, k, index_base=base)
+            assert np.array_equal(i.cpu().numpy(), io) and np.array_equal(s.cpu().numpy(), so)
     eng.close()
 
 

@@ -19,6 +19,7 @@
 #include "common.cuh"
 #include "kernels.h"
 
+#include <algorithm>
 #include <cmath>
 #include <map>
 #include <vector>
@@ -32,7 +33,8 @@ struct ImgDesc {
     int ksize_h, ksize_v;
     const int* bounds_h; const int* kk_h;   // per output x of the resized width: (xmin, count), coefficients
     const int* bounds_v; const int* kk_v;
-    int identity;                      // resized size == source size: pure crop + convert
+    int identity;                      // 0 = resize in preprocess_kernel, 1 = resized size == source size (pure crop + convert in
+                                       // convert_kernel), 2 = too wide / too tall for a shared-memory tile (the two global-memory kernels)
     int pad_[3];                       // sizeof == 80: pulled to the device as five 16-byte words
 };
 
@@ -191,7 +193,7 @@ __global__ void __launch_bounds__(256) preprocess_kernel(PreParams p) {
     const bool vec8 = p.layout == 0 || (p.P & 7) == 0;
     const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
 
-    if (d.identity) return;                                     // handled by convert_kernel
+    if (d.identity) return;                                     // handled by convert_kernel (1) or the global-memory pair (2)
 
     // ---- rows of the source this tile needs (vertical taps of its first and last output row)
     const int r_lo = d.bounds_v[2 * (d.top + y0)];
@@ -286,7 +288,7 @@ __global__ void __launch_bounds__(256, 4) convert_kernel(PreParams p, int B, int
         const int b = item / tiles, y0 = (item - b * tiles) * p.TR;
         const ImgDesc& d = p.desc[b];
         int prefix = 0;
-        if (d.identity) {
+        if (d.identity == 1) {
             const int rowbytes = d.w_in * 3, nr = min(S, y0 + p.TR) - y0;
             prefix = stage_span(stage + buf * p.stage_bytes, p.src, d.src_off + (long long)(d.top + y0) * rowbytes, nr * rowbytes);
         }
@@ -303,7 +305,7 @@ __global__ void __launch_bounds__(256, 4) convert_kernel(PreParams p, int B, int
         __syncthreads();
         const int b = item / tiles, y0 = (item - b * tiles) * p.TR;
         const ImgDesc& d = p.desc[b];
-        if (d.identity) {
+        if (d.identity == 1) {
             const int rowbytes = d.w_in * 3, nr = min(S, y0 + p.TR) - y0;
             const uint8_t* base = stage + (it & 1) * p.stage_bytes + prefix + d.left * 3;
             for (int r = wid; r < nr; r += 8)
@@ -326,8 +328,57 @@ __global__ void __launch_bounds__(256, 4) convert_kernel(PreParams p, int B, int
     }
 }
 
+// Images no shared-memory tile can hold (a source row wider than a staging buffer, or a vertical reduction whose taps span more rows
+// than fit): the same two integer passes through a global-memory intermediate, one thread per intermediate / output pixel.  Rare by
+// construction (panoramas, 20k-pixel scans), so simple rather than fast; the arithmetic is identical, tap for tap.
+__global__ void __launch_bounds__(256) hpass_global_kernel(const uint8_t* __restrict__ src, ImgDesc d, int S, int r_lo, int nrows,
+                                                           uint8_t* __restrict__ inter) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (long long)nrows * S) return;
+    const int r = (int)(i / S), x = (int)(i - (long long)r * S), xo = d.left + x;
+    const int xmin = d.bounds_h[2 * xo], cnt = d.bounds_h[2 * xo + 1];
+    const int* k = d.kk_h + (size_t)xo * d.ksize_h;
+    const uint8_t* px = src + d.src_off + ((long long)(r_lo + r) * d.w_in + xmin) * 3;
+    int a0 = 1 << (PRECISION_BITS - 1), a1 = a0, a2 = a0;
+    for (int j = 0; j < cnt; ++j) {
+        const int w = k[j];
+        a0 += px[3 * j] * w; a1 += px[3 * j + 1] * w; a2 += px[3 * j + 2] * w;
+    }
+    uint8_t* o = inter + ((size_t)r * S + x) * 3;
+    o[0] = (uint8_t)clip8(a0); o[1] = (uint8_t)clip8(a1); o[2] = (uint8_t)clip8(a2);
+}
+template <bool BF16>
+__global__ void __launch_bounds__(256) vpass_global_kernel(PreParams p, ImgDesc d, int b, int r_lo, const uint8_t* __restrict__ inter) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x, S = p.S;
+    if (i >= S * S) return;
+    const int y = i / S, x = i - y * S, yo = d.top + y;
+    const int ymin = d.bounds_v[2 * yo], cnt = d.bounds_v[2 * yo + 1];
+    const int* k = d.kk_v + (size_t)yo * d.ksize_v;
+    const uint8_t* col = inter + ((size_t)(ymin - r_lo) * S + x) * 3;
+    int a0 = 1 << (PRECISION_BITS - 1), a1 = a0, a2 = a0;
+    for (int t = 0; t < cnt; ++t) {
+        const int w = k[t];
+        const uint8_t* q = col + (size_t)t * S * 3;
+        a0 += q[0] * w; a1 += q[1] * w; a2 += q[2] * w;
+    }
+    int cstride;
+    const size_t idx = out_index(p, b, y, x, cstride);
+    const float f0 = p.lut[clip8(a0)], f1 = p.lut[256 + clip8(a1)], f2 = p.lut[512 + clip8(a2)];
+    if (BF16) {
+        __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out);
+        o[idx] = __float2bfloat16_rn(f0); o[idx + cstride] = __float2bfloat16_rn(f1); o[idx + 2 * (size_t)cstride] = __float2bfloat16_rn(f2);
+    } else {
+        float* o = reinterpret_cast<float*>(p.out);
+        o[idx] = f0; o[idx + cstride] = f1; o[idx + 2 * (size_t)cstride] = f2;
+    }
+}
+
 // ------------------------------------------------------------------------------------------ host side
-struct AxisTable { int ksize = 0; int* d_bounds = nullptr; int* d_kk = nullptr; double scale = 1.0; };
+struct AxisTable {
+    int ksize = 0; int* d_bounds = nullptr; int* d_kk = nullptr; double scale = 1.0;   // both arrays live in one allocation (d_bounds)
+    unsigned long long last_use = 0;
+    std::vector<int> h_bounds;          // host copy of (xmin, count) per output position: the driver needs the rows a crop window touches
+};
 
 // Pillow's precompute_coeffs + normalize_coeffs_8bpc for the bicubic filter (a = -0.5, support 2), in double.
 static double keys_cubic(double x) {
@@ -361,25 +412,33 @@ static int build_axis_table(int in_size, int out_size, AxisTable* t, cudaStream_
         }
         bounds[2 * xx] = xmin; bounds[2 * xx + 1] = xmax;
     }
-    B200_CUDA_OK(cudaMalloc(&t->d_bounds, bounds.size() * sizeof(int)));
-    B200_CUDA_OK(cudaMalloc(&t->d_kk, kk.size() * sizeof(int)));
-    B200_CUDA_OK(cudaMemcpyAsync(t->d_bounds, bounds.data(), bounds.size() * sizeof(int), cudaMemcpyHostToDevice, st));
-    B200_CUDA_OK(cudaMemcpyAsync(t->d_kk, kk.data(), kk.size() * sizeof(int), cudaMemcpyHostToDevice, st));
-    B200_CUDA_OK(cudaStreamSynchronize(st));   // host vectors die at return
+    // one allocation, one copy per table (bounds first, coefficients behind them, 16-byte aligned)
+    const size_t nb = (bounds.size() + 3) & ~(size_t)3;
+    std::vector<int> blob(nb + kk.size(), 0);
+    std::copy(bounds.begin(), bounds.end(), blob.begin());
+    std::copy(kk.begin(), kk.end(), blob.begin() + nb);
+    B200_CUDA_OK(cudaMalloc(&t->d_bounds, blob.size() * sizeof(int)));
+    t->d_kk = t->d_bounds + nb;
+    const cudaError_t e = cudaMemcpyAsync(t->d_bounds, blob.data(), blob.size() * sizeof(int), cudaMemcpyHostToDevice, st);
+    const cudaError_t e2 = e == cudaSuccess ? cudaStreamSynchronize(st) : e;   // the host vector dies at return
+    if (e2 != cudaSuccess) { cudaFree(t->d_bounds); t->d_bounds = t->d_kk = nullptr; B200_CUDA_OK(e2); }
     t->ksize = ksize; t->scale = scale;
+    t->h_bounds = std::move(bounds);
     return B200_OK;
 }
 
 struct PreprocessState {
     std::map<std::pair<int, int>, AxisTable> tables;
+    unsigned long long call_id = 0;     // stamps the tables a call uses (least-recently-used eviction)
+    uint8_t* d_inter = nullptr; size_t inter_cap = 0;   // global-memory intermediate of the oversize path
     float* d_lut = nullptr;
     // descriptors: filled in one of four pinned host buffers, pulled into d_desc by a small kernel (zero-copy
     // reads).  No copy-engine transfer, so a caller's large uploads on another stream cannot delay this call.
     ImgDesc* d_desc = nullptr; ImgDesc* h_desc[4] = {nullptr, nullptr, nullptr, nullptr}; int desc_cap = 0; int desc_slot = 0;
     cudaEvent_t desc_free[4] = {nullptr, nullptr, nullptr, nullptr};
     ~PreprocessState() {
-        for (auto& kv : tables) { cudaFree(kv.second.d_bounds); cudaFree(kv.second.d_kk); }
-        cudaFree(d_lut); cudaFree(d_desc);
+        for (auto& kv : tables) cudaFree(kv.second.d_bounds);
+        cudaFree(d_lut); cudaFree(d_desc); cudaFree(d_inter);
         for (int i = 0; i < 4; ++i) { if (h_desc[i]) cudaFreeHost(h_desc[i]); if (desc_free[i]) cudaEventDestroy(desc_free[i]); }
     }
 };
@@ -398,16 +457,34 @@ PreprocessState* preprocess_state_create(const float* mean, const float* stdv, i
 }
 void preprocess_state_destroy(PreprocessState* s) { delete s; }
 
+// A long-running service meets an unbounded number of (source, target) sizes; the cache holds the most recently used ones.  When it
+// is full, the older half is dropped - after a device synchronise, because a kernel still in flight may be reading those tables -
+// except the tables the current call has already picked up.  (std::map nodes are stable: pointers handed out stay valid.)
+constexpr size_t kMaxAxisTables = 4096;
 static int get_table(PreprocessState* s, int in_size, int out_size, const AxisTable** out, cudaStream_t st) {
     auto key = std::make_pair(in_size, out_size);
     auto it = s->tables.find(key);
     if (it == s->tables.end()) {
-        if (s->tables.size() >= 4096) return fail(B200_ESTATE, "preprocess: more than 4096 distinct (source, target) sizes cached");
+        if (s->tables.size() >= kMaxAxisTables) {
+            std::vector<std::pair<unsigned long long, std::pair<int, int>>> old;
+            for (auto& kv : s->tables) if (kv.second.last_use != s->call_id) old.push_back({kv.second.last_use, kv.first});
+            std::sort(old.begin(), old.end());
+            const size_t drop = std::min(old.size(), s->tables.size() - kMaxAxisTables / 2);
+            if (drop > 0) {
+                B200_CUDA_OK(cudaDeviceSynchronize());
+                for (size_t i = 0; i < drop; ++i) {
+                    auto victim = s->tables.find(old[i].second);
+                    cudaFree(victim->second.d_bounds);
+                    s->tables.erase(victim);
+                }
+            }
+        }
         AxisTable t;
         int rc = build_axis_table(in_size, out_size, &t, st);
         if (rc) return rc;
-        it = s->tables.emplace(key, t).first;
+        it = s->tables.emplace(key, std::move(t)).first;
     }
+    it->second.last_use = s->call_id;
     *out = &it->second;
     return B200_OK;
 }
@@ -441,10 +518,14 @@ int preprocess_run(PreprocessState* s, const uint8_t* src_dev, const long long* 
         s->desc_cap = cap;
     }
     s->desc_slot = (s->desc_slot + 1) & 3;
+    s->call_id += 1;
     ImgDesc* hdesc = s->h_desc[s->desc_slot];
     B200_CUDA_OK(cudaEventSynchronize(s->desc_free[s->desc_slot]));   // the call four back has pulled its descriptors
     const int inter_pitch = (S * 3 + 15) & ~15;
-    double max_vscale = 1.0; int max_rowbytes = 0; bool any_resize = false; int max_ident_rowbytes = 0;
+    constexpr int kMaxStage = 65536;                       // largest staging buffer of the tiled kernel
+    auto rows_needed_for = [&](double vs, int tr) { return (int)std::ceil(vs * tr + 4.0 * (vs < 1 ? 1 : vs)) + 3; };
+    std::vector<const AxisTable*> vtab(B, nullptr);
+    int max_rowbytes = 0, max_ident_rowbytes = 0;
     for (int i = 0; i < B; ++i) {
         const int h = hw[2 * i], w = hw[2 * i + 1];
         B200_REQUIRE(h > 0 && w > 0, "preprocess: image with non-positive size");
@@ -465,12 +546,23 @@ int preprocess_run(PreprocessState* s, const uint8_t* src_dev, const long long* 
             rc = get_table(s, h, new_h, &tv, st); if (rc) return rc;
             d.bounds_h = th->d_bounds; d.kk_h = th->d_kk; d.ksize_h = th->ksize;
             d.bounds_v = tv->d_bounds; d.kk_v = tv->d_kk; d.ksize_v = tv->ksize;
-            if (tv->scale > max_vscale) max_vscale = tv->scale;
-            any_resize = true;
-            if (w * 3 > max_rowbytes) max_rowbytes = w * 3;
+            vtab[i] = tv;
+            if (w * 3 + 32 + 128 > kMaxStage) d.identity = 2;      // a source row does not fit a staging buffer
+            else if (w * 3 > max_rowbytes) max_rowbytes = w * 3;
         } else if (w * 3 > max_ident_rowbytes) max_ident_rowbytes = w * 3;
     }
-    // Tile height: as many output rows as keep the uint8 intermediate within ~64 KB (whole tile within 200 KB).
+    // Staging: two buffers of `stage_bytes` (>= one source row + slack for the zero-weight over-reads of the register-tiled
+    // horizontal pass); what is left of ~200 KB holds the uint8 intermediate rows of one tile.
+    int stage_bytes = 16384;
+    while (stage_bytes < max_rowbytes + 32 + 128) stage_bytes *= 2;
+    const size_t budget = 200 * 1024 - 3072 - 2 * (size_t)stage_bytes;
+    double max_vscale = 1.0; bool any_resize = false, any_oversize = false;
+    for (int i = 0; i < B; ++i) {
+        ImgDesc& d = hdesc[i];
+        if (d.identity == 0 && (size_t)rows_needed_for(vtab[i]->scale, 1) * inter_pitch > budget) d.identity = 2;   // taps of ONE output row do not fit
+        if (d.identity == 0) { any_resize = true; if (vtab[i]->scale > max_vscale) max_vscale = vtab[i]->scale; }
+        any_oversize |= d.identity == 2;
+    }
     pull_desc_kernel<<<(B * 5 + 255) / 256, 256, 0, st>>>(reinterpret_cast<const uint4*>(hdesc), reinterpret_cast<uint4*>(s->d_desc), B * 5);
     B200_CUDA_OK(cudaGetLastError());
     B200_CUDA_OK(cudaEventRecord(s->desc_free[s->desc_slot], st));
@@ -479,11 +571,11 @@ int preprocess_run(PreprocessState* s, const uint8_t* src_dev, const long long* 
         // identity images: TR rows per item, one staging buffer per item (double buffered)
         int TR = 16;
         while (TR > 1 && (size_t)TR * max_ident_rowbytes + 48 > 48 * 1024) TR /= 2;
-        const int stage_bytes = (TR * max_ident_rowbytes + 48 + 15) & ~15;
-        B200_REQUIRE(stage_bytes <= 96 * 1024, "preprocess: source rows too wide");
-        const size_t smem = 3072 + 2 * (size_t)stage_bytes;
+        const int ident_stage = (TR * max_ident_rowbytes + 48 + 15) & ~15;
+        B200_REQUIRE(ident_stage <= 96 * 1024, "preprocess: source rows too wide");
+        const size_t smem = 3072 + 2 * (size_t)ident_stage;
         const int tiles = (S + TR - 1) / TR;
-        PreParams p{src_dev, s->d_desc, s->d_lut, out_dev, S, TR, layout, out_bf16, P, layout ? S / P : 0, kpad, inter_pitch, stage_bytes};
+        PreParams p{src_dev, s->d_desc, s->d_lut, out_dev, S, TR, layout, out_bf16, P, layout ? S / P : 0, kpad, inter_pitch, ident_stage};
         const long long total = (long long)B * tiles;
         const int grid = (int)std::min<long long>(total, 8LL * kNumSMs);
         if (out_bf16) {
@@ -495,17 +587,35 @@ int preprocess_run(PreprocessState* s, const uint8_t* src_dev, const long long* 
         }
         B200_CUDA_OK(cudaGetLastError());
     }
+    if (any_oversize) {
+        // one image at a time through the global-memory pair; the intermediate holds every source row the crop window touches
+        PreParams p{src_dev, s->d_desc, s->d_lut, out_dev, S, 1, layout, out_bf16, P, layout ? S / P : 0, kpad, inter_pitch, 0};
+        for (int i = 0; i < B; ++i) {
+            const ImgDesc& d = hdesc[i];
+            if (d.identity != 2) continue;
+            const std::vector<int>& bv = vtab[i]->h_bounds;
+            const int r_lo = bv[2 * d.top], r_hi = bv[2 * (d.top + S - 1)] + bv[2 * (d.top + S - 1) + 1];
+            const size_t need = (size_t)(r_hi - r_lo) * S * 3;
+            if (need > s->inter_cap) {
+                B200_CUDA_OK(cudaStreamSynchronize(st));
+                cudaFree(s->d_inter); s->d_inter = nullptr; s->inter_cap = 0;
+                B200_CUDA_OK(cudaMalloc(&s->d_inter, need + need / 4));
+                s->inter_cap = need + need / 4;
+            }
+            const long long n1 = (long long)(r_hi - r_lo) * S;
+            hpass_global_kernel<<<(unsigned)((n1 + 255) / 256), 256, 0, st>>>(src_dev, d, S, r_lo, r_hi - r_lo, s->d_inter);
+            B200_CUDA_OK(cudaGetLastError());
+            if (out_bf16) vpass_global_kernel<true><<<(S * S + 255) / 256, 256, 0, st>>>(p, d, i, r_lo, s->d_inter);
+            else vpass_global_kernel<false><<<(S * S + 255) / 256, 256, 0, st>>>(p, d, i, r_lo, s->d_inter);
+            B200_CUDA_OK(cudaGetLastError());
+        }
+    }
     if (!any_resize) return rc;
-    // Resized images.  Staging: two buffers of `stage_bytes` (>= one source row + slack for the zero-weight
-    // over-reads of the register-tiled horizontal pass).
-    int stage_bytes = 16384;
-    while (stage_bytes < max_rowbytes + 32 + 128) stage_bytes *= 2;
-    B200_REQUIRE(stage_bytes <= 65536, "preprocess: source rows wider than 21800 pixels are not supported");
-    auto rows_needed = [&](int tr) { return (int)std::ceil(max_vscale * tr + 4.0 * (max_vscale < 1 ? 1 : max_vscale)) + 3; };
+    // Tile height: as many output rows as keep the uint8 intermediate within ~64 KB (whole tile within 200 KB).
+    auto rows_needed = [&](int tr) { return rows_needed_for(max_vscale, tr); };
     int TR = 32;
-    const size_t budget = 200 * 1024 - 3072 - 2 * (size_t)stage_bytes;
     while (TR > 1 && ((size_t)rows_needed(TR) * inter_pitch > 65536)) TR /= 2;
-    B200_REQUIRE((size_t)rows_needed(TR) * inter_pitch <= budget, "preprocess: vertical downscale factor too large for one tile");
+    B200_REQUIRE((size_t)rows_needed(TR) * inter_pitch <= budget, "preprocess: internal error: tile does not fit (oversize images should have been diverted)");
     const size_t smem = 3072 + 2 * (size_t)stage_bytes + (size_t)rows_needed(TR) * inter_pitch;
     PreParams p{src_dev, s->d_desc, s->d_lut, out_dev, S, TR, layout, out_bf16, P, layout ? S / P : 0, kpad, inter_pitch, stage_bytes};
     const int tiles = (S + TR - 1) / TR;

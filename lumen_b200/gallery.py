@@ -134,6 +134,6 @@ class DeviceGallery:
         return g
 
     # ------------------------------------------------------------------ search
-    def search(self, queries_f16, k: int):
+    def search(self, queries_f16, k: int, events: list | None = None):
         """(scores float32 [Q, k], global indices int64 [Q, k]); across ranks when `group` spans several."""
-        return ShardedGallery(self.engine, self.view(), self.index_base, self.group).search(queries_f16, k)
+        return ShardedGallery(self.engine, self.view(), self.index_base, self.group).search(queries_f16, k, events)

@@ -132,11 +132,23 @@ class ShardedGallery:
         lo = min(n_total, rank * per)
         return lo, min(n_total, lo + per)
 
-    def search(self, queries_f16, k: int):
+    def search(self, queries_f16, k: int, events: list | None = None):
+        """(scores [Q,k], global indices [Q,k]).  `events`, when given, receives four CUDA events recorded on the current stream:
+        start | local top-k done | all-gather done | merge done (bench.py times the phases with them)."""
         torch = _torch()
+
+        def mark():
+            if events is not None:
+                e = torch.cuda.Event(enable_timing=True)
+                e.record()
+                events.append(e)
+
+        mark()
         scores, idx = self.engine.topk(queries_f16, self.shard, k, self.index_base)
+        mark()
         dist = torch.distributed
         if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(self.group) == 1:
+            mark(); mark()
             return scores, idx
         world = dist.get_world_size(self.group)
         all_s = torch.empty((world,) + tuple(scores.shape), dtype=scores.dtype, device=scores.device)
@@ -147,7 +159,10 @@ class ShardedGallery:
         else:                                                # gloo (CPU tests of the host logic)
             dist.all_gather(list(all_s.unbind(0)), scores, group=self.group)
             dist.all_gather(list(all_i.unbind(0)), idx, group=self.group)
-        return self.engine.merge_topk(all_s, all_i)
+        mark()
+        out = self.engine.merge_topk(all_s, all_i)
+        mark()
+        return out
 
 
 class B200BioCLIPModelManager:

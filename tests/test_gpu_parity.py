@@ -84,6 +84,34 @@ def test_preprocess_patch14_padding():
     eng.close()
 
 
+def test_preprocess_oversize_sources_and_many_sizes(eng224):
+    """Sources no shared-memory tile can hold (a 23,000-pixel-wide strip, a 12,000-pixel-tall one: 53x vertical reduction) take the
+    global-memory kernels and are still bit-exact, mixed in one batch with ordinary images; and a stream of ever-new source sizes
+    (more than the coefficient-table cache holds) keeps working - the cache evicts, it never fails."""
+    from oracle import clip_oracle as O
+    rng = np.random.default_rng(8)
+    sizes = [(30, 23000), (300, 400), (12000, 40), (224, 224), (26, 22500)]
+    imgs = [rng.integers(0, 256, (h, w, 3), dtype=np.uint8) for h, w in sizes]
+    for mode in (0, 1):
+        want = O.preprocess_batch(imgs, 224, mode)
+        got = _run_pre(eng224, imgs, mode).cpu().numpy()
+        assert np.array_equal(got, want), mode
+        pm = _run_pre(eng224, imgs, mode, layout=1, bf16=True).float().cpu().numpy()
+        ref = want.reshape(len(imgs), 3, 7, 32, 7, 32).transpose(0, 2, 4, 1, 3, 5).reshape(len(imgs) * 49, 3072)
+        assert np.array_equal(pm, torch.from_numpy(ref).to(torch.bfloat16).float().numpy())
+    # 4500 distinct widths -> 4500 horizontal tables pass through a 4096-entry cache
+    base = rng.integers(0, 256, (40, 5000, 3), dtype=np.uint8)
+    for lo in range(0, 4500, 500):
+        batch = [np.ascontiguousarray(base[:, :300 + lo + j]) for j in range(500)]
+        out = _run_pre(eng224, batch, 0)
+        if lo in (0, 4000):
+            pick = [0, 250, 499]
+            assert np.array_equal(out[pick].cpu().numpy(), O.preprocess_batch([batch[j] for j in pick], 224, 0))
+    # the first sizes were evicted long ago: asking for them again rebuilds their tables
+    again = [np.ascontiguousarray(base[:, :300 + j]) for j in (0, 1, 2)]
+    assert np.array_equal(_run_pre(eng224, again, 0).cpu().numpy(), O.preprocess_batch(again, 224, 0))
+
+
 def test_preprocess_empty_and_errors(eng224):
     from lumen_b200 import _lib
     src = torch.zeros(64, dtype=torch.uint8, device="cuda")

@@ -61,6 +61,20 @@ def test_topk_matches_reference(golden_cls):
     np.testing.assert_allclose(s, golden_cls["bio_s"], rtol=0, atol=2e-6)
 
 
+def test_bioclip_request_port_matches_reference(golden_cls):
+    """The per-request port (what bench.py times as the search CPU baseline) on a unit-length and on a raw gallery."""
+    g = np.random.default_rng(10).standard_normal((5000, 512)).astype(np.float32)
+    g /= np.linalg.norm(g, axis=1, keepdims=True)
+    raw = (g * np.random.default_rng(12).uniform(0.5, 2.0, (5000, 1))).astype(np.float32)
+    for r, q in enumerate(golden_cls["queries"]):
+        for gal, ki, ks in ((g, "bio_idx", "bio_s"), (raw, "bio_raw_idx", "bio_raw_s")):
+            i, s = O.bioclip_classify_image(q, gal, 10)
+            assert np.array_equal(i, golden_cls[ki][r])
+            np.testing.assert_allclose(s, golden_cls[ks][r], rtol=0, atol=1e-6)
+            s2, i2 = O.topk_cosine(q[None], gal, 10)                     # the batched, order-pinned form agrees
+            assert np.array_equal(i2[0], i)
+
+
 def test_topk_tie_order_and_merge():
     g = np.zeros((40, 8), np.float32)
     g[:, 0] = np.array([3, 1, 3, 2, 3] * 8)                      # many exact ties

@@ -176,7 +176,7 @@ def bench_attention(args):
         fl, ex = 4.0 * B * heads * S * S * 64, float(B) * heads * S * S
         byt = B * S * 4 * d * 2
         print(json.dumps({"path": "K5 attention", "model": name, "B": B, "S": S, "heads": heads, "us": ms * 1e3,
-                          "kernel": "attention_tc_kernel (tcgen05)" if S > 64 else "attention_kernel (mma.sync)",
+                          "kernel": "attention_tc_kernel (tcgen05)" if S > 64 else "attention_short_kernel (tcgen05)",
                           "tflops_useful": fl / ms / 1e9, "gexp_per_s": ex / ms / 1e6,
                           "frac_of_sfu_exp2_peak": ex / ms / 1e6 / (148 * 16 * 1.92), "hbm_gbs": byt / ms / 1e6,
                           "hbm_frac": byt / ms / 1e6 / pk["hbm_gbs"]}), flush=True)

@@ -416,8 +416,7 @@ static int encode_chunk(b200clip_handle* h, const __nv_bfloat16* patches, int B,
     for (const Layer& l : h->layers) {
         R_(timed(2, [&] { return launch_layernorm(h->xres, 1, l.ln1_g, l.ln1_b, h->hbuf, M, d, c.ln_eps, st); }));
         R_(timed(1, [&] { return gemm_bf16_tc(h->hbuf, d, l.w_qkv, d, M, 3 * d, d, l.b_qkv, h->qkv, 3 * d, EPI_BIAS_BF16, 0, h->status, st); }));
-        R_(timed(3, [&] { return attention_tc_supported(S, d, c.heads) ? launch_attention_tc(h->qkv, h->hbuf, B, S, d, c.heads, 0, h->status, st)
-                                                                      : launch_attention(h->qkv, h->hbuf, B, S, d, c.heads, st); }));
+        R_(timed(3, [&] { return launch_attention_auto(h->qkv, h->hbuf, B, S, d, c.heads, 0, h->status, st); }));
         R_(timed(1, [&] { return gemm_bf16_tc(h->hbuf, d, l.w_o, d, M, d, d, l.b_o, h->xres, d, EPI_BIAS_RES_F32, 0, h->status, st); }));
         R_(timed(2, [&] { return launch_layernorm(h->xres, 1, l.ln2_g, l.ln2_b, h->hbuf, M, d, c.ln_eps, st); }));
         R_(timed(1, [&] { return gemm_bf16_tc(h->hbuf, d, l.w_fc1, d, M, mlp, d, l.b_fc1, h->mlp, mlp, EPI_BIAS_ACT_BF16, c.activation, h->status, st); }));
@@ -702,8 +701,7 @@ extern "C" int b200clip_attention(b200clip_handle* h, const void* qkv, void* out
                                   void* stream) {
     int rc = set_device(h); if (rc) return rc;
     B200_REQUIRE(!causal || (S > 64 && width == heads * 64), "attention: the causal mask needs S > 64 and head_dim 64 (tcgen05 kernel)");
-    rc = (causal || attention_tc_supported(S, width, heads)) ? launch_attention_tc(qkv, out, B, S, width, heads, causal, h->status, (cudaStream_t)stream)
-                                                             : launch_attention(qkv, out, B, S, width, heads, (cudaStream_t)stream);
+    rc = launch_attention_auto(qkv, out, B, S, width, heads, causal, h->status, (cudaStream_t)stream);
     if (rc == B200_OK) h->launches += 1;
     return rc;
 }

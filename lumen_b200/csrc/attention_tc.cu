@@ -1,13 +1,9 @@
 // K5 on the 5th-generation tensor cores: softmax(Q K^T / 8) V per (image, head), head_dim 64, bf16 in / bf16 out.
 //
-// The mma.sync attention in vit_ops.cu is bound by the legacy HMMA rate (32 % of a ViT-B/16 step, 44 % of ViT-L/14@336);
-// this kernel issues the two matmuls as tcgen05.mma with accumulators in TMEM.
+// Both matmuls are tcgen05.mma with accumulators in TMEM.  Two kernels: attention_tc_kernel (this one) for S > 64, and
+// attention_short_kernel (further down) for S <= 64.
 //
-// Tile = 128 query rows, walked over the keys in steps of 64.
-//   pack == 1 (S > 64): 128 queries of one (image, head); online softmax over ceil(S / 64) key steps.
-//   pack == 2 (S <= 64): two heads of one image share a tile (rows 0..63 head h, rows 64..127 head h + 1) and the tile takes
-//                        two steps: step u holds the keys of head h + u; rows of the other head have probability 0 there
-//                        (written once), so short sequences (S = 50) still fill the 128-row MMA.
+// Tile = 128 query rows of one (image, head), walked over the keys in steps of 64 with an online softmax.
 // Per step g: S[g&1] = Q K^T     UMMA 128x64x16 x4 into one of TWO score buffers in TMEM: the tensor core computes the scores
 //                                of step g + 1 while the softmax warps work on step g
 //             P[g&1] = exp2(..)  softmax warps, thread = query row = TMEM lane; P goes back to TMEM (bf16 pairs, 32 columns,
@@ -44,10 +40,9 @@ static_assert(AT_SMEM <= 227 * 1024, "attention_tc: shared memory plan exceeds o
 
 struct AttnParams {
     int S, d, heads, B;
-    int pack;            // heads per tile (1 or 2)
-    int n_qt, n_kt;      // query tiles per (image, head group), key steps per item
+    int n_qt, n_kt;      // query tiles per (image, head), key steps per item
     int items;
-    int causal;          // 1: key j is visible to query i only when j <= i (text tower); pack == 1 only
+    int causal;          // 1: key j is visible to query i only when j <= i (text tower)
     __nv_bfloat16* out;  // [B*S, d]
     DeviceStatus* status;
 };
@@ -78,8 +73,8 @@ __device__ __forceinline__ uint32_t pack_bf16x2(float a, float b) {
 
 struct AttnItem { int b, h0, qt; };
 __device__ __forceinline__ AttnItem attn_item(const AttnParams& p, int item) {
-    const int hgroups = p.heads / p.pack, rest = item / p.n_qt;
-    return {rest / hgroups, (rest % hgroups) * p.pack, item % p.n_qt};
+    const int rest = item / p.n_qt;
+    return {rest / p.heads, rest % p.heads, item % p.n_qt};
 }
 
 // Bounded mbarrier wait with a suspend-time hint: the thread parks in hardware instead of spinning through the issue slots
@@ -195,13 +190,11 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, AttnParams p) {
                 const int qi = li & 1, row0 = it.b * p.S;
                 if (!(ok = mbar_wait_parked(&b[Q_EMPTY + qi], ((li >> 1) & 1) ^ 1, p.status, 31))) break;
                 mbar_arrive_expect_tx(&b[Q_FULL + qi], AT_Q_BYTES);
-                for (int u = 0; u < 2; ++u) {
-                    if (p.pack == 1) tma_load_2d(base + qi * AT_Q_BYTES + u * 8192, &tmQKV, &b[Q_FULL + qi], it.h0 * AT_DH, row0 + it.qt * AT_ROWS + u * 64);
-                    else tma_load_2d(base + qi * AT_Q_BYTES + u * 8192, &tmQKV, &b[Q_FULL + qi], (it.h0 + u) * AT_DH, row0);
-                }
+                for (int u = 0; u < 2; ++u)
+                    tma_load_2d(base + qi * AT_Q_BYTES + u * 8192, &tmQKV, &b[Q_FULL + qi], it.h0 * AT_DH, row0 + it.qt * AT_ROWS + u * 64);
                 for (int kt = 0; kt < p.n_kt; ++kt, ++g) {
                     const int st = g % AT_STAGES;
-                    const int row = p.pack == 1 ? row0 + kt * AT_KEYS : row0, col = (p.pack == 1 ? it.h0 : it.h0 + kt) * AT_DH;
+                    const int row = row0 + kt * AT_KEYS, col = it.h0 * AT_DH;
                     uint8_t* k_dst = base + AT_OFF_KV + st * 2 * AT_KV_BYTES;
                     if (!(ok = mbar_wait_parked(&b[KV_EMPTY + st], ((g / AT_STAGES) & 1) ^ 1, p.status, 32))) break;
                     mbar_arrive_expect_tx(&b[KV_FULL + st], 2 * AT_KV_BYTES);
@@ -222,7 +215,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, AttnParams p) {
             bool ok = true;
             // keys a step really holds, rounded up to the MMA's K granule
             auto keys16 = [&](int g) {
-                const int left = p.pack == 1 ? p.S - (g % p.n_kt) * AT_KEYS : p.S;
+                const int left = p.S - (g % p.n_kt) * AT_KEYS;
                 return left >= AT_KEYS ? AT_KEYS : ((left + 15) & ~15);
             };
             // S[g & 1] = Q K^T of step g; that score buffer is free once P of step g - 2 was written
@@ -266,21 +259,12 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, AttnParams p) {
     } else {
         // ---- softmax: slot, TMEM lane quarter, tile row (one thread per row)
         const int s = (warp - 2) >> 2, q = warp & 3, r = q * 32 + lane;
-        const int hsel = r >> 6;                       // pack == 2: which head of the pair this row belongs to
         const float sl2 = 0.125f * 1.4426950408889634f;
         const uint32_t t_lane = tmem_base + ((uint32_t)(q * 32) << 16) + s * AT_TM_SLOT;
         const uint32_t t_o = t_lane + AT_TM_O;
         uint64_t* b = bars + s * NBAR;
         uint8_t* base = smem + s * AT_SLOT_BYTES;
         const int my_items = my_pairs - ((s == 1 && odd_tail) ? 1 : 0);
-        if (p.pack == 2) {                                             // the other head's keys: probability 0, written once
-            uint32_t z[16];
-#pragma unroll
-            for (int i = 0; i < 16; ++i) z[i] = 0u;
-#pragma unroll
-            for (int i = 0; i < 4; ++i) tmem_st_32x16(t_lane + AT_TM_P + i * 16, z);
-            tmem_st_wait();
-        }
         int g = 0; bool ok = true;
         float m = 0.f, l = 0.f;                                         // m: reference maximum the probabilities are taken against
         float s4[4];
@@ -310,7 +294,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, AttnParams p) {
             __syncwarp();
             if (lane == 0) mbar_arrive(&b[P_FULL + (gg & 1)]);
         };
-        // One pipelined step (pack == 1): (lo, hi) hold the masked scores of step g and m is already valid for them; the scores of
+        // One pipelined step: (lo, hi) hold the masked scores of step g and m is already valid for them; the scores of
         // step g + 1 are fetched into (nlo, nhi) and reduced to the next maximum while the SFUs work through step g.
         auto step = [&](uint32_t (&lo)[32], uint32_t (&hi)[32], uint32_t (&nlo)[32], uint32_t (&nhi)[32], int kt, int qrow) -> bool {
             const bool has_next = kt + 1 < p.n_kt;
@@ -363,7 +347,7 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, AttnParams p) {
             // A warp whose 32 rows all lie past the end of the sequence (the last query tile of S = 257 holds ONE real row) has
             // nothing to compute: it only keeps the barrier protocol going, paced by the score barriers so that it can never arrive
             // twice in one phase.  Its SFU and issue slots go to the other slot's warps.
-            if (p.pack == 1 && it.qt * AT_ROWS + q * 32 >= p.S) {
+            if (it.qt * AT_ROWS + q * 32 >= p.S) {
                 for (int kt = 0; kt < p.n_kt; ++kt, ++g) {
                     if (!(ok = mbar_wait_parked(&b[S_FULL + (g & 1)], (g >> 1) & 1, p.status, 37))) break;
                     tc_fence_after();
@@ -373,47 +357,24 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, AttnParams p) {
                 if (lane == 0) { mbar_arrive(&b[O_FREE]); mbar_arrive(&b[Q_EMPTY + qi]); }
                 continue;
             }
-            if (p.pack == 1) {
-                // first step of the item: load, mask, take the maximum as the reference
-                if (!(ok = mbar_wait_parked(&b[S_FULL + (g & 1)], (g >> 1) & 1, p.status, 37))) break;
-                tc_fence_after();
-                const uint32_t t_s = t_lane + AT_TM_S + (g & 1) * 64;
-                tmem_ld_32x32(t_s, a_lo);
-                tmem_ld_32x32(t_s + 32, a_hi);
-                tmem_ld_wait();
-                const int qrow = it.qt * AT_ROWS + r;
-                const int nv = p.causal ? min(min(AT_KEYS, p.S), qrow + 1) : min(AT_KEYS, p.S);
-                mask_tail(a_lo, nv);
-                mask_tail(a_hi, nv - 32);
-                m = fmaxf(max32(a_lo), max32(a_hi)) * sl2;
-                for (int kt = 0; kt < p.n_kt && ok; kt += 2) {
-                    if (!(ok = step(a_lo, a_hi, b_lo, b_hi, kt, qrow))) break;
-                    ++g;
-                    if (kt + 1 < p.n_kt) { if (!(ok = step(b_lo, b_hi, a_lo, a_hi, kt + 1, qrow))) break; ++g; }
-                }
-                if (!ok) break;
-            } else {
-                // two heads per tile: step u holds the keys of head u; a row works in its own head's step only
-                for (int kt = 0; kt < 2; ++kt, ++g) {
-                    if (!(ok = mbar_wait_parked(&b[S_FULL + (g & 1)], (g >> 1) & 1, p.status, 37))) break;
-                    tc_fence_after();
-                    if (kt == hsel) {
-                        const uint32_t t_s = t_lane + AT_TM_S + (g & 1) * 64;
-                        tmem_ld_32x32(t_s, a_lo);
-                        tmem_ld_32x32(t_s + 32, a_hi);
-                        tmem_ld_wait();
-                        mask_tail(a_lo, p.S);
-                        mask_tail(a_hi, p.S - 32);
-                        m = fmaxf(max32(a_lo), max32(a_hi)) * sl2;
-                        s4[0] = s4[1] = s4[2] = s4[3] = 0.f;
-                        exp32(a_lo, g, 0);
-                        exp32(a_hi, g, 16);
-                        l = (s4[0] + s4[1]) + (s4[2] + s4[3]);
-                    }
-                    publish(g);
-                }
-                if (!ok) break;
+            // first step of the item: load, mask, take the maximum as the reference
+            if (!(ok = mbar_wait_parked(&b[S_FULL + (g & 1)], (g >> 1) & 1, p.status, 37))) break;
+            tc_fence_after();
+            const uint32_t t_s = t_lane + AT_TM_S + (g & 1) * 64;
+            tmem_ld_32x32(t_s, a_lo);
+            tmem_ld_32x32(t_s + 32, a_hi);
+            tmem_ld_wait();
+            const int qrow = it.qt * AT_ROWS + r;
+            const int nv = p.causal ? min(min(AT_KEYS, p.S), qrow + 1) : min(AT_KEYS, p.S);
+            mask_tail(a_lo, nv);
+            mask_tail(a_hi, nv - 32);
+            m = fmaxf(max32(a_lo), max32(a_hi)) * sl2;
+            for (int kt = 0; kt < p.n_kt && ok; kt += 2) {
+                if (!(ok = step(a_lo, a_hi, b_lo, b_hi, kt, qrow))) break;
+                ++g;
+                if (kt + 1 < p.n_kt) { if (!(ok = step(b_lo, b_hi, a_lo, a_hi, kt + 1, qrow))) break; ++g; }
             }
+            if (!ok) break;
             if (!(ok = mbar_wait_parked(&b[O_FULL + ((g - 1) & 1)], ((g - 1) >> 1) & 1, p.status, 39))) break;
             tc_fence_after();
             // the row's 64 output columns out of TMEM (then the O columns go back to the MMA warp), normalised, staged as one
@@ -441,10 +402,10 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, AttnParams p) {
 #pragma unroll
             for (int t = 0; t < 8; ++t) {                               // the warp's 32 rows, four 128-byte rows per instruction
                 const int rr = q * 32 + t * 4 + (lane >> 3), ch = lane & 7;
-                const int hs = p.pack == 2 ? rr >> 6 : 0, qrow = p.pack == 2 ? (rr & 63) : it.qt * AT_ROWS + rr;
+                const int qrow = it.qt * AT_ROWS + rr;
                 if (qrow < p.S) {
                     const uint4 w = *reinterpret_cast<const uint4*>(stage + rr * 128 + ((ch ^ (rr & 7)) << 4));
-                    *reinterpret_cast<uint4*>(p.out + (size_t)(it.b * p.S + qrow) * p.d + (it.h0 + hs) * AT_DH + ch * 8) = w;
+                    *reinterpret_cast<uint4*>(p.out + (size_t)(it.b * p.S + qrow) * p.d + it.h0 * AT_DH + ch * 8) = w;
                 }
             }
             fence_proxy_async();                                        // the buffer goes back to the TMA producer
@@ -457,11 +418,205 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, AttnParams p) {
     if (warp == 1) { __syncwarp(); tmem_dealloc(tmem_base, 512); }
 }
 
-// B200_ATTN_TC: 0 = always the mma.sync kernel, 1 (default) = this kernel for S > 64, 2 = also for S <= 64 (two heads per tile).
-bool attention_tc_supported(int S, int d, int heads) {
-    static const int on = [] { const char* e = getenv("B200_ATTN_TC"); return e ? atoi(e) : 1; }();
-    if (!on || heads <= 0 || d != heads * AT_DH || S <= 0) return false;
-    return S > 64 || (on >= 2 && (heads % 2) == 0);
+// ------------------------------------------------------------------------------------------ short sequences (S <= 64)
+// ViT-B/32 has 50 tokens: 6,144 (image, head) problems of 50 x 50 per layer at batch 512 - 1 % of the FLOPs, and HBM-bound by rights
+// (118 MB of qkv in, 39 MB out: 24 us at the measured peak).  What bounds a per-problem pipeline there is not a pipe but the chain
+// of hand-offs (TMA -> MMA -> softmax -> MMA -> store), a few microseconds long, so this kernel runs MANY short chains side by
+// side instead of a deep one: four small CTAs per SM, each owning 128 TMEM columns, each walking its own list of tiles.
+//   tile   = two (image, head) problems: rows 0..63 of the 128-row MMA are the queries of the first, rows 64..127 of the second
+//   S      = Q K^T as ONE UMMA 128 x 128 x 16 x 4: Q = two stacked 64-row boxes, K likewise; the off-diagonal 64 x 64 blocks are
+//            scores against the other problem's keys and are never read
+//   P      = exp2(..) by 128 threads (thread = row = TMEM lane), written back over the score columns as bf16 pairs: keys of the
+//            row's own problem get probabilities, the other problem's keys get 0, so that
+//   O      = P V as ONE UMMA chain 128 x 64 x 16 x 8 over the two stacked V boxes (A = P straight from TMEM) leaves both
+//            problems' outputs in columns 64..127 (whose scores are dead by then)
+// Rows / keys past the sequence end inside a 64-row box belong to the next image (or are out of bounds = 0): keys are masked
+// before the softmax (probability 0), query rows are computed and dropped at the store.
+constexpr int SA_THREADS = 160;                               // warps 0..3 softmax (TMEM lane quarters), warp 4 = TMA + MMA issue
+constexpr int SA_BOX = 64 * AT_DH * 2;                        // one 64-row x 128-byte box: 8 KB
+constexpr int SA_SMEM = 6 * SA_BOX + 128 + 1024;
+
+struct ShortAttnParams {
+    int S, d, heads, items, tiles;
+    __nv_bfloat16* out;
+    DeviceStatus* status;
+};
+
+__global__ void __launch_bounds__(SA_THREADS, 4)
+attention_short_kernel(const __grid_constant__ CUtensorMap tmQKV, ShortAttnParams p) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    uint8_t* sQ = smem;                      // 2 boxes: queries of problem 0 | problem 1; reused as the output staging area
+    uint8_t* sK = smem + 2 * SA_BOX;
+    uint8_t* sV = smem + 4 * SA_BOX;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 6 * SA_BOX);
+    uint64_t *ld_full = bars, *s_full = bars + 1, *p_full = bars + 2, *o_full = bars + 3, *q_free = bars + 4;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 5);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+
+    if (warp == 4 && lane == 0) {
+        tma_prefetch_desc(&tmQKV);
+        mbar_init(ld_full, 1); mbar_init(s_full, 1); mbar_init(p_full, 4); mbar_init(o_full, 1); mbar_init(q_free, 4);
+        fence_mbar_init();
+    }
+    if (warp == 4) tmem_alloc(tmem_slot, 128);
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem_base = *tmem_slot;
+    pdl_wait();
+    pdl_trigger();
+
+    if (warp == 4) {
+        if (lane == 0) {
+            constexpr uint32_t idesc_s = attn_idesc(128, 128, 0), idesc_o = attn_idesc(128, 64, 1);
+            bool ok = true;
+            uint32_t ph = 0;
+            for (int t = blockIdx.x; t < p.tiles && ok; t += gridDim.x, ph ^= 1) {
+                // the previous tile's output has left the staging area (= the Q boxes)
+                if (t != (int)blockIdx.x && !(ok = mbar_wait_spin(q_free, ph ^ 1, p.status, 41))) break;
+                mbar_arrive_expect_tx(ld_full, 6 * SA_BOX);
+                for (int u = 0; u < 2; ++u) {
+                    const int item = min(2 * t + u, p.items - 1);
+                    const int row0 = (item / p.heads) * p.S, col = (item % p.heads) * AT_DH;
+                    tma_load_2d(sQ + u * SA_BOX, &tmQKV, ld_full, col, row0);
+                    tma_load_2d(sK + u * SA_BOX, &tmQKV, ld_full, p.d + col, row0);
+                    tma_load_2d(sV + u * SA_BOX, &tmQKV, ld_full, 2 * p.d + col, row0);
+                }
+                if (!(ok = mbar_wait_spin(ld_full, ph, p.status, 42))) break;
+                tc_fence_after();
+                const uint64_t dq = umma_desc_sw128(smem_u32(sQ)), dk = umma_desc_sw128(smem_u32(sK));
+#pragma unroll
+                for (int k = 0; k < 4; ++k) umma_f16(tmem_base, dq + 2 * k, dk + 2 * k, idesc_s, k != 0);
+                umma_commit(s_full);
+                if (!(ok = mbar_wait_spin(p_full, ph, p.status, 43))) break;
+                tc_fence_after();
+                const uint64_t dv = umma_desc_mn_sw128(smem_u32(sV));
+#pragma unroll
+                for (int k = 0; k < 8; ++k) umma_f16_ts(tmem_base + 64, tmem_base + k * 8, dv + (uint64_t)k * (2048 >> 4), idesc_o, k != 0);
+                umma_commit(o_full);
+            }
+        }
+    } else {
+        const int r = warp * 32 + lane, hsel = r >> 6, qrow = r & 63;
+        const float sl2 = 0.125f * 1.4426950408889634f;
+        const uint32_t t_lane = tmem_base + ((uint32_t)(warp * 32) << 16);
+        bool ok = true;
+        uint32_t ph = 0;
+        for (int t = blockIdx.x; t < p.tiles && ok; t += gridDim.x, ph ^= 1) {
+            if (!(ok = mbar_wait_spin(s_full, ph, p.status, 44))) break;
+            tc_fence_after();
+            // this row's scores against its own problem's keys: columns [64 hsel, 64 hsel + 64)
+            uint32_t a[32], b[32];
+            tmem_ld_32x32(t_lane + hsel * 64, a);
+            tmem_ld_32x32(t_lane + hsel * 64 + 32, b);
+            tmem_ld_wait();
+            mask_tail(a, p.S);
+            mask_tail(b, p.S - 32);
+            float m = __uint_as_float(a[0]);
+#pragma unroll
+            for (int j = 1; j < 32; ++j) m = fmaxf(m, __uint_as_float(a[j]));
+#pragma unroll
+            for (int j = 0; j < 32; ++j) m = fmaxf(m, __uint_as_float(b[j]));
+            m *= sl2;
+            float l0 = 0.f, l1 = 0.f;
+            uint32_t w[16];
+            // P columns: keys (2c, 2c + 1) of the stacked key tile in column c; own problem = columns [32 hsel, 32 hsel + 32)
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+                const float e0 = ex2_approx(fmaf(__uint_as_float(a[2 * i]), sl2, -m)), e1 = ex2_approx(fmaf(__uint_as_float(a[2 * i + 1]), sl2, -m));
+                l0 += e0; l1 += e1;
+                w[i] = pack_bf16x2(e0, e1);
+            }
+            tmem_st_32x16(t_lane + hsel * 32, w);
+#pragma unroll
+            for (int i = 0; i < 16; ++i) {
+                const float e0 = ex2_approx(fmaf(__uint_as_float(b[2 * i]), sl2, -m)), e1 = ex2_approx(fmaf(__uint_as_float(b[2 * i + 1]), sl2, -m));
+                l0 += e0; l1 += e1;
+                w[i] = pack_bf16x2(e0, e1);
+            }
+            tmem_st_32x16(t_lane + hsel * 32 + 16, w);
+#pragma unroll
+            for (int i = 0; i < 16; ++i) w[i] = 0u;                     // the other problem's keys
+            tmem_st_32x16(t_lane + (hsel ^ 1) * 32, w);
+            tmem_st_32x16(t_lane + (hsel ^ 1) * 32 + 16, w);
+            tmem_st_wait();
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(p_full);
+            const float inv = 1.f / (l0 + l1);
+            if (!(ok = mbar_wait_spin(o_full, ph, p.status, 45))) break;
+            tc_fence_after();
+            tmem_ld_32x32(t_lane + 64, a);
+            tmem_ld_32x32(t_lane + 96, b);
+            tmem_ld_wait();
+            // normalised row -> one swizzled 128-byte row of the staging area (the Q boxes: both MMAs that read them are done)
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                const uint32_t (&v)[32] = i < 4 ? a : b;
+                const int o = (i & 3) * 8;
+                uint4 x;
+                x.x = pack_bf16x2(__uint_as_float(v[o]) * inv, __uint_as_float(v[o + 1]) * inv);
+                x.y = pack_bf16x2(__uint_as_float(v[o + 2]) * inv, __uint_as_float(v[o + 3]) * inv);
+                x.z = pack_bf16x2(__uint_as_float(v[o + 4]) * inv, __uint_as_float(v[o + 5]) * inv);
+                x.w = pack_bf16x2(__uint_as_float(v[o + 6]) * inv, __uint_as_float(v[o + 7]) * inv);
+                *reinterpret_cast<uint4*>(sQ + r * 128 + ((i ^ (r & 7)) << 4)) = x;
+            }
+            __syncwarp();
+            // the warp's 32 rows, four full 128-byte rows per instruction
+            const int item = 2 * t + hsel;                              // warps 0,1 -> first problem, warps 2,3 -> second
+            if (item < p.items) {
+                const int b_img = item / p.heads, h = item % p.heads;
+#pragma unroll
+                for (int tt = 0; tt < 8; ++tt) {
+                    const int rr = warp * 32 + tt * 4 + (lane >> 3), ch = lane & 7, q = rr & 63;
+                    if (q < p.S) {
+                        const uint4 x = *reinterpret_cast<const uint4*>(sQ + rr * 128 + ((ch ^ (rr & 7)) << 4));
+                        *reinterpret_cast<uint4*>(p.out + (size_t)(b_img * p.S + q) * p.d + h * AT_DH + ch * 8) = x;
+                    }
+                }
+            }
+            (void)qrow;
+            fence_proxy_async();                                        // the Q boxes go back to the TMA engine
+            tc_fence_before();
+            __syncwarp();
+            if (lane == 0) mbar_arrive(q_free);
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 4) { __syncwarp(); tmem_dealloc(tmem_base, 128); }
+}
+
+int launch_attention_short(const void* qkv, void* out, int B, int S, int d, int heads, DeviceStatus* status, cudaStream_t st) {
+    if (B <= 0) return B200_OK;
+    B200_REQUIRE(S > 0 && S <= 64 && heads > 0 && d == heads * AT_DH, "attention_short: needs S <= 64 and head_dim 64");
+    B200_REQUIRE((long long)B * heads < (1LL << 30), "attention_short: too many (image, head) problems");
+    ShortAttnParams p;
+    p.S = S; p.d = d; p.heads = heads; p.items = B * heads; p.tiles = (p.items + 1) / 2;
+    p.out = static_cast<__nv_bfloat16*>(out);
+    p.status = status;
+    CUtensorMap tm;
+    int rc = make_tmap_2d(&tm, qkv, (uint64_t)B * S, (uint64_t)3 * d, (uint64_t)3 * d * 2, 64, false);
+    if (rc) return rc;
+    static bool attr_set[64] = {false};
+    int dev = 0;
+    B200_CUDA_OK(cudaGetDevice(&dev));
+    if (dev >= 64 || !attr_set[dev]) {
+        B200_CUDA_OK(cudaFuncSetAttribute(attention_short_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, SA_SMEM));
+        if (dev < 64) attr_set[dev] = true;
+    }
+    const int grid = p.tiles < 4 * kNumSMs ? p.tiles : 4 * kNumSMs;
+    B200_CUDA_OK(launch_pdl(attention_short_kernel, dim3(grid), dim3(SA_THREADS), SA_SMEM, st, tm, p));
+    B200_CUDA_OK(cudaGetLastError());
+    return B200_OK;
+}
+
+// Picks the kernel by shape: S <= 64 -> attention_short_kernel, longer sequences (and the causal text tower) -> attention_tc_kernel.
+int launch_attention_auto(const void* qkv, void* out, int B, int S, int d, int heads, int causal, DeviceStatus* status, cudaStream_t st) {
+    B200_REQUIRE(heads > 0 && S > 0 && d == heads * AT_DH, "attention: head_dim must be 64");
+    if (!causal && S <= AT_KEYS) return launch_attention_short(qkv, out, B, S, d, heads, status, st);
+    return launch_attention_tc(qkv, out, B, S, d, heads, causal, status, st);
 }
 
 int launch_attention_tc(const void* qkv, void* out, int B, int S, int d, int heads, int causal, DeviceStatus* status, cudaStream_t st) {
@@ -469,10 +624,9 @@ int launch_attention_tc(const void* qkv, void* out, int B, int S, int d, int hea
     B200_REQUIRE(!causal || S > AT_KEYS, "attention_tc: the causal mask is implemented for S > 64 only");
     AttnParams p;
     p.S = S; p.d = d; p.heads = heads; p.B = B;
-    p.pack = S <= 64 ? 2 : 1;
-    p.n_qt = p.pack == 2 ? 1 : (S + AT_ROWS - 1) / AT_ROWS;
-    p.n_kt = p.pack == 2 ? 2 : (S + AT_KEYS - 1) / AT_KEYS;
-    p.items = B * (heads / p.pack) * p.n_qt;
+    p.n_qt = (S + AT_ROWS - 1) / AT_ROWS;
+    p.n_kt = (S + AT_KEYS - 1) / AT_KEYS;
+    p.items = B * heads * p.n_qt;
     p.causal = causal ? 1 : 0;
     p.out = static_cast<__nv_bfloat16*>(out);
     p.status = status;

@@ -25,9 +25,10 @@ int launch_l2_normalize(const float* in, float* out, int rows, int D, cudaStream
 int launch_text_embed(const int* ids, const float* tok, const float* pos, float* x, int rows, int ctx, int d, int vocab, cudaStream_t st);
 int launch_text_eot_gather(const int* ids, const float* x, float* out, int B, int ctx, int d, cudaStream_t st);
 int launch_gallery_pack(const float* in, void* out_f16, long long rows, int D, int normalize, cudaStream_t st);
-int launch_attention(const void* qkv, void* out, int B, int S, int d, int heads, cudaStream_t st);
-// tcgen05 attention (attention_tc.cu): head_dim 64; S <= 64 packs two heads per tile and needs an even head count
-bool attention_tc_supported(int S, int d, int heads);
+// tcgen05 attention (attention_tc.cu), head_dim 64: attention_tc_kernel for S > 64 (and the causal text tower),
+// S <= 64 on tcgen05 (attention_tc.cu): two (image, head) problems per 128-row tile, four small CTAs per SM
+int launch_attention_short(const void* qkv, void* out, int B, int S, int d, int heads, DeviceStatus* status, cudaStream_t st);
+int launch_attention_auto(const void* qkv, void* out, int B, int S, int d, int heads, int causal, DeviceStatus* status, cudaStream_t st);
 int launch_attention_tc(const void* qkv, void* out, int B, int S, int d, int heads, int causal, DeviceStatus* status, cudaStream_t st);
 struct TopkPlan { int splits, qtiles, cpl; long long rows_per_split; size_t cand_bytes, part_bytes, qstage_bytes; };
 int topk_plan(int Q, long long N, int k, TopkPlan* plan);

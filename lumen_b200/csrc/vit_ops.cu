@@ -1,4 +1,5 @@
-// K3 LayerNorm, token assembly (CLS + position + pre-LN), K5 attention, E2 L2-normalise.
+// K3 LayerNorm, token assembly (CLS + position + pre-LN), E2 L2-normalise, text-tower embedding / pooling, gallery packing.
+// (K5 attention lives in attention_tc.cu.)
 // The math follows what the reference's encoder call computes (onnxrt_backend.py:485 / torch_backend.py:652-666;
 // restated in oracle/clip_oracle.py:vit_encode).  The residual stream is fp32, GEMM operands are bf16.
 #include "common.cuh"
@@ -166,171 +167,6 @@ __global__ void __launch_bounds__(256) gallery_pack_kernel(const float* __restri
     }
 }
 
-// ------------------------------------------------------------------------------------------ attention
-// softmax(Q K^T / sqrt(64)) V for one (image, head, 64-query tile), head_dim fixed at 64 (all CLIP ViTs here).
-// Flash-style: keys in tiles of 64 with an online softmax, bf16 mma.sync m16n8k16 with fp32 accumulators.
-// (Attention is 1-9 % of the tower's FLOPs; the tcgen05 budget goes to the GEMMs.)
-constexpr int ATT_PITCH = 72;   // bf16 elements per shared-memory row (64 + 8 pad: conflict-free ldmatrix)
-
-__device__ __forceinline__ void ldsm_x4(uint32_t (&r)[4], const void* p) {
-    asm volatile("ldmatrix.sync.aligned.m8n8.x4.shared.b16 {%0,%1,%2,%3}, [%4];"
-                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(smem_u32(p)));
-}
-__device__ __forceinline__ void ldsm_x4_t(uint32_t (&r)[4], const void* p) {
-    asm volatile("ldmatrix.sync.aligned.m8n8.x4.trans.shared.b16 {%0,%1,%2,%3}, [%4];"
-                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]) : "r"(smem_u32(p)));
-}
-__device__ __forceinline__ void mma_bf16(float (&c)[4], const uint32_t (&a)[4], uint32_t b0, uint32_t b1) {
-    asm volatile("mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
-                 : "+f"(c[0]), "+f"(c[1]), "+f"(c[2]), "+f"(c[3])
-                 : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
-}
-__device__ __forceinline__ uint32_t pack_bf16(float a, float b) {
-    __nv_bfloat162 t = __floats2bfloat162_rn(a, b);
-    return *reinterpret_cast<uint32_t*>(&t);
-}
-
-__device__ __forceinline__ void cp_async16_zfill(void* smem_dst, const void* gsrc, bool valid) {
-    const int n = valid ? 16 : 0;       // src-size 0 -> the 16 destination bytes are zero-filled
-    asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(smem_u32(smem_dst)), "l"(gsrc), "r"(n) : "memory");
-}
-// 64 rows x 64 bf16 (128 B per row) -> 512 16-byte vectors over 128 threads; rows past the end are zero-filled.
-__device__ __forceinline__ void load_tile64_async(__nv_bfloat16* dst, const __nv_bfloat16* src, int row0, int nrows_valid, int ld) {
-#pragma unroll
-    for (int i = threadIdx.x; i < 512; i += 128) {
-        const int r = i >> 3, c = (i & 7) * 8;
-        const bool ok = row0 + r < nrows_valid;
-        cp_async16_zfill(dst + r * ATT_PITCH + c, src + (size_t)(ok ? row0 + r : 0) * ld + c, ok);
-    }
-}
-
-// Persistent CTAs walk a flat list of (image, head, 64-query tile) items; every step consumes one 64-key tile of
-// K and V.  The next step's tiles (and the next item's Q tile) are fetched with cp.async into the other buffer
-// while the current step computes, so global-load latency overlaps the MMAs and softmax.
-constexpr int ATT_TILE = 64 * ATT_PITCH;          // bf16 elements per staged tile
-constexpr int ATT_SMEM = 6 * ATT_TILE * 2;        // Q, K, V double buffered
-
-__global__ void __launch_bounds__(128, 4) attention_kernel(const __nv_bfloat16* __restrict__ qkv, __nv_bfloat16* __restrict__ out,
-                                                           int S, int d, int heads, int n_qt, int total_items) {
-    pdl_wait();
-    pdl_trigger();
-    extern __shared__ __align__(16) __nv_bfloat16 att_sm[];
-    __nv_bfloat16* sQ = att_sm;                    // [2][ATT_TILE]
-    __nv_bfloat16* sK = att_sm + 2 * ATT_TILE;
-    __nv_bfloat16* sV = att_sm + 4 * ATT_TILE;
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, g = lane >> 2, t = lane & 3;
-    const int ld = 3 * d;
-    const int n_kt = (S + 63) >> 6;
-    const float sl2 = 0.125f * 1.4426950408889634f;   // 64^-0.5 * log2(e)
-
-    auto item_base = [&](int item, int& qt) -> const __nv_bfloat16* {
-        qt = item % n_qt;
-        const int bh = item / n_qt, h = bh % heads, b = bh / heads;
-        return qkv + (size_t)b * S * ld + h * 64;
-    };
-    auto issue = [&](int item, int kt, int buf, int qbuf) {
-        int qt;
-        const __nv_bfloat16* base = item_base(item, qt);
-        if (kt == 0) load_tile64_async(sQ + qbuf * ATT_TILE, base, qt * 64, S, ld);
-        load_tile64_async(sK + buf * ATT_TILE, base + d, kt * 64, S, ld);
-        load_tile64_async(sV + buf * ATT_TILE, base + 2 * d, kt * 64, S, ld);
-        asm volatile("cp.async.commit_group;" ::: "memory");
-    };
-
-    int item = blockIdx.x, kt = 0, step = 0, local_item = 0;
-    if (item >= total_items) return;
-    issue(item, 0, 0, 0);
-    uint32_t qa[4][4];
-    float o[8][4];
-    float m0 = -INFINITY, m1 = -INFINITY, l0 = 0.f, l1 = 0.f;
-    while (item < total_items) {
-        // next step: same item / next key tile, or first tile of this CTA's next item
-        int n_item = item, n_kt_idx = kt + 1, n_local = local_item;
-        if (n_kt_idx == n_kt) { n_item = item + gridDim.x; n_kt_idx = 0; n_local = local_item + 1; }
-        if (n_item < total_items) {
-            issue(n_item, n_kt_idx, (step + 1) & 1, n_local & 1);
-            asm volatile("cp.async.wait_group 1;" ::: "memory");
-        } else {
-            asm volatile("cp.async.wait_group 0;" ::: "memory");
-        }
-        __syncthreads();
-        const __nv_bfloat16* cK = sK + (step & 1) * ATT_TILE;
-        const __nv_bfloat16* cV = sV + (step & 1) * ATT_TILE;
-        if (kt == 0) {
-            const __nv_bfloat16* cQ = sQ + (local_item & 1) * ATT_TILE;
-#pragma unroll
-            for (int ks = 0; ks < 4; ++ks)
-                ldsm_x4(qa[ks], cQ + (warp * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * ATT_PITCH + ks * 16 + (lane >> 4) * 8);
-#pragma unroll
-            for (int i = 0; i < 8; ++i) o[i][0] = o[i][1] = o[i][2] = o[i][3] = 0.f;
-            m0 = m1 = -INFINITY; l0 = l1 = 0.f;
-        }
-        const int k0 = kt * 64;
-        float s[8][4];
-#pragma unroll
-        for (int i = 0; i < 8; ++i) s[i][0] = s[i][1] = s[i][2] = s[i][3] = 0.f;
-#pragma unroll
-        for (int ks = 0; ks < 4; ++ks)
-#pragma unroll
-            for (int np = 0; np < 4; ++np) {
-                uint32_t kb[4];
-                ldsm_x4(kb, cK + (np * 16 + (lane & 7) + (lane >> 4) * 8) * ATT_PITCH + ks * 16 + ((lane >> 3) & 1) * 8);
-                mma_bf16(s[2 * np], qa[ks], kb[0], kb[1]);
-                mma_bf16(s[2 * np + 1], qa[ks], kb[2], kb[3]);
-            }
-        float mx0 = m0, mx1 = m1;
-#pragma unroll
-        for (int nt = 0; nt < 8; ++nt) {
-            const int key = k0 + nt * 8 + 2 * t;
-            if (key >= S) { s[nt][0] = -INFINITY; s[nt][2] = -INFINITY; }
-            if (key + 1 >= S) { s[nt][1] = -INFINITY; s[nt][3] = -INFINITY; }
-            mx0 = fmaxf(mx0, fmaxf(s[nt][0], s[nt][1]));
-            mx1 = fmaxf(mx1, fmaxf(s[nt][2], s[nt][3]));
-        }
-        mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 1)); mx0 = fmaxf(mx0, __shfl_xor_sync(0xffffffffu, mx0, 2));
-        mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 1)); mx1 = fmaxf(mx1, __shfl_xor_sync(0xffffffffu, mx1, 2));
-        const float c0 = exp2f((m0 - mx0) * sl2), c1 = exp2f((m1 - mx1) * sl2);   // exp2f(-inf) = 0 on the first tile
-        m0 = mx0; m1 = mx1;
-        l0 *= c0; l1 *= c1;
-#pragma unroll
-        for (int i = 0; i < 8; ++i) { o[i][0] *= c0; o[i][1] *= c0; o[i][2] *= c1; o[i][3] *= c1; }
-        uint32_t pa[4][4];
-#pragma unroll
-        for (int nt = 0; nt < 8; ++nt) {
-            const float p0 = exp2f((s[nt][0] - m0) * sl2), p1 = exp2f((s[nt][1] - m0) * sl2);
-            const float p2 = exp2f((s[nt][2] - m1) * sl2), p3 = exp2f((s[nt][3] - m1) * sl2);
-            l0 += p0 + p1; l1 += p2 + p3;
-            pa[nt >> 1][(nt & 1) * 2 + 0] = pack_bf16(p0, p1);
-            pa[nt >> 1][(nt & 1) * 2 + 1] = pack_bf16(p2, p3);
-        }
-#pragma unroll
-        for (int kk = 0; kk < 4; ++kk)
-#pragma unroll
-            for (int dp = 0; dp < 4; ++dp) {
-                uint32_t vb[4];
-                ldsm_x4_t(vb, cV + (kk * 16 + (lane & 7) + ((lane >> 3) & 1) * 8) * ATT_PITCH + dp * 16 + (lane >> 4) * 8);
-                mma_bf16(o[2 * dp], pa[kk], vb[0], vb[1]);
-                mma_bf16(o[2 * dp + 1], pa[kk], vb[2], vb[3]);
-            }
-        if (kt == n_kt - 1) {
-            float t0 = l0, t1 = l1;
-            t0 += __shfl_xor_sync(0xffffffffu, t0, 1); t0 += __shfl_xor_sync(0xffffffffu, t0, 2);
-            t1 += __shfl_xor_sync(0xffffffffu, t1, 1); t1 += __shfl_xor_sync(0xffffffffu, t1, 2);
-            const float i0 = 1.f / t0, i1 = 1.f / t1;
-            const int qt = item % n_qt, bh = item / n_qt, h = bh % heads, b = bh / heads;
-            const int r0 = qt * 64 + warp * 16 + g, r1 = r0 + 8;
-            __nv_bfloat16* ob = out + (size_t)b * S * d + h * 64;
-#pragma unroll
-            for (int dt = 0; dt < 8; ++dt) {
-                if (r0 < S) *reinterpret_cast<uint32_t*>(ob + (size_t)r0 * d + dt * 8 + 2 * t) = pack_bf16(o[dt][0] * i0, o[dt][1] * i0);
-                if (r1 < S) *reinterpret_cast<uint32_t*>(ob + (size_t)r1 * d + dt * 8 + 2 * t) = pack_bf16(o[dt][2] * i1, o[dt][3] * i1);
-            }
-        }
-        __syncthreads();                               // this step's K/V (and Q) buffers may now be overwritten
-        item = n_item; kt = n_kt_idx; local_item = n_local; ++step;
-    }
-}
-
 // ------------------------------------------------------------------------------------------ launchers
 int launch_layernorm(const float* x, long long row_stride, const float* g, const float* b, void* out, int rows, int d, float eps, cudaStream_t st) {
     B200_REQUIRE(d % 128 == 0 && d <= 128 * LN_MAX_V4, "layernorm: width must be a multiple of 128, at most 1024");
@@ -369,24 +205,4 @@ int launch_l2_normalize(const float* in, float* out, int rows, int D, cudaStream
     B200_CUDA_OK(cudaGetLastError());
     return B200_OK;
 }
-int launch_attention(const void* qkv, void* out, int B, int S, int d, int heads, cudaStream_t st) {
-    B200_REQUIRE(d == heads * 64, "attention: head_dim must be 64");
-    B200_REQUIRE(B > 0 && S > 0, "attention: empty batch");
-    const int n_qt = (S + 63) / 64;
-    const long long items = (long long)B * heads * n_qt;
-    B200_REQUIRE(items < (1LL << 30), "attention: too many (image, head, tile) items");
-    static bool attr_set[64] = {false};
-    int dev = 0;
-    B200_CUDA_OK(cudaGetDevice(&dev));
-    if (dev >= 64 || !attr_set[dev]) {
-        B200_CUDA_OK(cudaFuncSetAttribute(attention_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, ATT_SMEM));
-        if (dev < 64) attr_set[dev] = true;
-    }
-    const int grid = (int)(items < 4LL * kNumSMs ? items : 4LL * kNumSMs);
-    B200_CUDA_OK(launch_pdl(attention_kernel, dim3(grid), dim3(128), ATT_SMEM, st, reinterpret_cast<const __nv_bfloat16*>(qkv),
-                            reinterpret_cast<__nv_bfloat16*>(out), S, d, heads, n_qt, (int)items));
-    B200_CUDA_OK(cudaGetLastError());
-    return B200_OK;
-}
-
 }  // namespace b200

@@ -177,10 +177,10 @@ def test_layernorm_and_attention():
         out = eng.layernorm(x, gam, bet)
         ref = torch.nn.functional.layer_norm(x, (d,), gam, bet, 1e-5)
         torch.testing.assert_close(out.float(), ref, rtol=1e-2, atol=2e-2)
-    # S > 64: tcgen05 kernel, 64-key steps; S <= 64: mma.sync kernel by default (the two-heads-per-tile tcgen05 path is covered by
-    # test_attention_tc_short_sequences); 300 x 50 and 40 x 197 give each persistent CTA several items
+    # S > 64: attention_tc_kernel, 64-key steps; S <= 64: attention_short_kernel (two problems per tile; odd problem counts leave
+    # the last tile half empty); 300 x 50, 513 x 50 and 40 x 197 give each persistent CTA several tiles
     for B, S, heads in ((3, 50, 12), (2, 197, 12), (1, 577, 16), (5, 17, 2), (4, 64, 4), (2, 128, 2), (2, 129, 2), (3, 257, 16),
-                        (300, 50, 12), (40, 197, 12), (2, 50, 3), (1, 1, 2)):
+                        (300, 50, 12), (40, 197, 12), (2, 50, 3), (1, 1, 2), (1, 50, 3), (3, 33, 5), (1, 64, 1), (513, 50, 12)):
         d = heads * 64
         qkv = torch.randn(B * S, 3 * d, device="cuda", generator=g)
         if B == 40:   # keys grow along the sequence: later key steps raise the row maximum by far more than 2^8 (in-place O rescale)
@@ -193,33 +193,6 @@ def test_layernorm_and_attention():
         torch.testing.assert_close(out.float(), ref, rtol=2e-2, atol=2e-2)
     eng.sync()
     eng.close()
-
-
-_ATTN_TC_SHORT = r"""
-import sys, torch
-sys.path.insert(0, ".")
-from lumen_b200.engine import Engine
-eng = Engine({}, device=0)
-g = torch.Generator(device="cuda").manual_seed(5)
-for B, S, heads in ((1, 64, 2), (3, 50, 12), (5, 17, 2), (4, 64, 4), (300, 50, 12), (1, 1, 2), (7, 33, 6)):
-    d = heads * 64
-    qkv = torch.randn(B * S, 3 * d, device="cuda", generator=g).to(torch.bfloat16)
-    out = eng.attention(qkv, B, S, d, heads); eng.sync()
-    q, k, v = [t.view(B, S, heads, 64).transpose(1, 2) for t in qkv.float().split(d, dim=1)]
-    ref = (torch.softmax(q @ k.transpose(-1, -2) * 0.125, -1) @ v).transpose(1, 2).reshape(B * S, d)
-    torch.testing.assert_close(out.float(), ref, rtol=2e-2, atol=2e-2)
-print("ok")
-"""
-
-
-def test_attention_tc_short_sequences():
-    """B200_ATTN_TC=2 routes S <= 64 through the tcgen05 kernel too (two heads per 128-row tile, block-diagonal probabilities);
-    the switch is read once per process, hence the subprocess."""
-    import os, subprocess, sys
-    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-    r = subprocess.run([sys.executable, "-c", _ATTN_TC_SHORT], cwd=root, env=dict(os.environ, B200_ATTN_TC="2"),
-                       capture_output=True, text=True, timeout=300)
-    assert r.returncode == 0 and r.stdout.strip().endswith("ok"), r.stdout[-2000:] + r.stderr[-2000:]
 
 
 # ------------------------------------------------------------------------------------------ encoder end to end

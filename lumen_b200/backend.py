@@ -19,7 +19,7 @@ from .engine import MODE_SHORTEST_CROP, MODE_SQUASH, Engine
 from .interface import (BackendInfo, BaseClipBackend, InferenceError, InvalidInputError, ModelLoadingError)
 from .vit_config import OPENAI_MEAN, OPENAI_STD, VIT_CONFIGS
 
-__all__ = ["B200ClipBackend", "SyntheticResources"]
+__all__ = ["B200ClipBackend", "SyntheticResources", "install_as_reference_backend"]
 
 
 @dataclass
@@ -32,9 +32,12 @@ class SyntheticResources:
     labels: np.ndarray | None = None
     label_embeddings: np.ndarray | None = None
     weights: dict[str, np.ndarray] | None = None
+    model_root_path: Any = None          # a model directory with a checkpoint (weight_loaders.load_vision_weights), as ModelResources has
 
     def get_image_size(self):
-        s = self.config.get("image_size") or VIT_CONFIGS[self.model_name]["image_size"]
+        s = self.config.get("image_size") or (self.config.get("b200_vit") or VIT_CONFIGS.get(self.model_name) or {}).get("image_size")
+        if s is None:
+            return None                  # ModelResources.get_image_size (resources/loader.py:80-99) also returns None when the config is silent
         return (s, s) if isinstance(s, int) else (int(s[0]), int(s[1]))
 
     def get_normalization_stats(self):
@@ -246,3 +249,36 @@ class B200ClipBackend(BaseClipBackend):
     def engine(self) -> Engine:
         self._ensure_initialized()
         return self._engine
+
+
+def install_as_reference_backend(runtime: str = "torch", **backend_kwargs) -> type:
+    """Makes the reference's own `create_backend(backend_config, resources, runtime=...)` (backends/factory.py:75-141) build a
+    `B200ClipBackend`.  The factory hard-codes one class per runtime string and imports it from a fixed module path at call time
+    (:112-139), and the `Runtime` enum is closed (lumen_resources/lumen_config.py:181-188), so the substitution happens at the
+    module level - the technique of the reference's own test (packages/lumen-clip/tests/test_backend_factory.py:37-45): a module
+    object exposing a class of the expected name, with the constructor keywords the factory passes, is placed in `sys.modules`.
+    Call it once at start-up, before `create_backend`; YAML configs that say `runtime: torch` (or `onnx`) then get this backend with
+    no change to any caller.  `backend_kwargs` (e.g. weights=, preprocess_mode=) are forwarded to every instance.  Returns the class."""
+    import sys
+    import types
+    names = {"torch": ("lumen_clip.backends.torch_backend", "TorchBackend"), "onnx": ("lumen_clip.backends.onnxrt_backend", "ONNXRTBackend")}
+    if runtime not in names:
+        raise ValueError(f"runtime must be one of {sorted(names)}")
+    mod_name, cls_name = names[runtime]
+
+    class _B200AsReference(B200ClipBackend):
+        def __init__(self, resources, providers=None, device_preference=None, max_batch_size=None, precision=None):
+            dev = device_preference if device_preference and str(device_preference).startswith("cuda") else "cuda:0"
+            super().__init__(resources, device_preference=dev, max_batch_size=max_batch_size, **backend_kwargs)
+            self.requested_precision = precision            # the tower computes in bf16 whatever ONNX file precision was asked for
+
+    _B200AsReference.__name__ = _B200AsReference.__qualname__ = cls_name
+    mod = types.ModuleType(mod_name)
+    setattr(mod, cls_name, _B200AsReference)
+    sys.modules[mod_name] = mod
+    try:                                                     # a registry filled before the substitution would keep the old class
+        from lumen_clip.backends import factory
+        factory._BACKEND_REGISTRY.pop(runtime, None)
+    except Exception:  # noqa: BLE001 - reference package not importable: nothing to refresh
+        pass
+    return _B200AsReference

@@ -4,6 +4,7 @@
 #include "common.cuh"
 #include "kernels.h"
 
+#include <algorithm>
 #include <cstdlib>
 #include <cstring>
 #include <mutex>

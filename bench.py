@@ -294,7 +294,7 @@ def bench_search(D: Dist, pk: dict, quick: bool) -> dict:
                         "kernel_only_frac": flops_gpu / ph[0] / 1e9 / pk["bf16_burst"],
                         "hbm_frac": (n_local * GALLERY_DIM * 2) / ms / 1e6 / pk["hbm_gbs"],
                         "note": "4,093 flop/B: the tensor pipe binds at Q = 4096; a kernel timed alone for tens of ms -> burst peak"},
-           "allgather_bytes_per_gpu": SEARCH_Q * SEARCH_K * 12}
+           "allgather_bytes_per_gpu": SEARCH_Q * SEARCH_K * 8}
     # small-batch sweep on this rank's shard (no collective): the gallery read binds, graded against HBM
     sweep = []
     for Q in (1, 16, 64, 128):

@@ -163,6 +163,17 @@ int b200clip_topk(b200clip_handle* h, const void* queries_f16_dev, int32_t Q, co
 int b200clip_merge_topk(b200clip_handle* h, const float* part_scores_dev, const int64_t* part_index_dev, int32_t parts,
                         int32_t Q, int32_t k, float* out_scores_dev, int64_t* out_index_dev, void* stream);
 
+/* The same two steps in the form the sharded search exchanges between GPUs (gallery row-sharded, one all-gather of the
+ * per-GPU candidates, merge on every rank; the reference function being sharded is bioclip_model.py:313-316).  b200clip_topk_keys
+ * returns this GPU's top-k as ONE 64-bit key per candidate, out_keys [Q,k]: order-preserving score bits in the high word, ~(row index
+ * inside this shard) in the low word, 0 = empty slot - 8 bytes per candidate instead of 4 + 8, so a single all-gather (NCCL, MPI, or
+ * the caller's own transport: no torch type is involved) moves them.  b200clip_merge_topk_keys takes the gathered keys
+ * [parts][Q][k] and the index_base of every part (device array [parts]) and writes the global top-k like b200clip_merge_topk. */
+int b200clip_topk_keys(b200clip_handle* h, const void* queries_f16_dev, int32_t Q, const void* gallery_f16_dev, int64_t N,
+                       int32_t D, int32_t k, uint64_t* out_keys_dev, void* stream);
+int b200clip_merge_topk_keys(b200clip_handle* h, const uint64_t* part_keys_dev, const int64_t* part_bases_dev, int32_t parts,
+                             int32_t Q, int32_t k, float* out_scores_dev, int64_t* out_index_dev, void* stream);
+
 /* Search without any allocation.  No counterpart in the reference: it exists for callers that are not allowed to
  * allocate device memory at the moment they search — a host thread whose stream is being captured into a CUDA graph,
  * a real-time serving loop that must not hit the allocator's locks, or a plug-in living inside another framework's

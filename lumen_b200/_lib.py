@@ -51,6 +51,8 @@ SIGNATURES = {
     "b200clip_set_labels": (C.c_int, [_P, _I32, _P, _I32, _I32, _P]),
     "b200clip_classify": (C.c_int, [_P, _I32, _P, _I32, _F, _I32, _I32, _P, _P, _P]),
     "b200clip_topk": (C.c_int, [_P, _P, _I32, _P, _I64, _I32, _I32, _I64, _P, _P, _P]),
+    "b200clip_topk_keys": (C.c_int, [_P, _P, _I32, _P, _I64, _I32, _I32, _P, _P]),
+    "b200clip_merge_topk_keys": (C.c_int, [_P, _P, _P, _I32, _I32, _I32, _P, _P, _P]),
     "b200clip_topk_static": (C.c_int, [_P, _I32, _P, _I64, _I32, _I32, _I64, _P, _P, _P]),
     "b200clip_topk_static_status": (C.c_int, [_P]),
     "b200clip_merge_topk": (C.c_int, [_P, _P, _P, _I32, _I32, _I32, _P, _P, _P]),

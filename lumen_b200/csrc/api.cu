@@ -576,6 +576,38 @@ extern "C" int b200clip_topk(b200clip_handle* h, const void* queries, int32_t Q,
     return rc;
 }
 
+extern "C" int b200clip_topk_keys(b200clip_handle* h, const void* queries, int32_t Q, const void* gallery, int64_t N, int32_t D, int32_t k,
+                                  uint64_t* out_keys, void* stream) {
+    int rc = set_device(h); if (rc) return rc;
+    B200_REQUIRE(queries && gallery && out_keys, "topk_keys: null buffer");
+    std::lock_guard<std::mutex> lk(h->mu);
+    TopkPlan plan;
+    if ((rc = topk_plan(Q, N, k, &plan))) return rc;
+    const size_t need = plan.cand_bytes + plan.part_bytes + plan.qstage_bytes + 512;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (need > h->topk_cap) {
+        B200_CUDA_OK(cudaStreamSynchronize(st));
+        cudaFree(h->topk_scratch); h->topk_scratch = nullptr; h->topk_cap = 0;
+        B200_CUDA_OK(cudaMalloc(&h->topk_scratch, need));
+        h->topk_cap = need;
+    }
+    if ((rc = h->ws_begin(st))) return rc;
+    rc = topk_run(queries, gallery, Q, N, D, k, 0, h->topk_scratch, plan, nullptr, nullptr, h->status, st, reinterpret_cast<unsigned long long*>(out_keys));
+    if (rc == B200_OK) h->launches += plan.qstage_bytes ? 3 : 2;
+    if (rc == B200_OK) rc = h->ws_end(st);
+    return rc;
+}
+
+extern "C" int b200clip_merge_topk_keys(b200clip_handle* h, const uint64_t* part_keys, const int64_t* part_bases_dev, int32_t parts, int32_t Q,
+                                        int32_t k, float* out_scores, int64_t* out_index, void* stream) {
+    int rc = set_device(h); if (rc) return rc;
+    B200_REQUIRE(part_keys && part_bases_dev && out_scores && out_index, "merge_topk_keys: null buffer");
+    rc = merge_topk_keys_run(reinterpret_cast<const unsigned long long*>(part_keys), reinterpret_cast<const long long*>(part_bases_dev), parts, Q, k,
+                             out_scores, reinterpret_cast<long long*>(out_index), (cudaStream_t)stream);
+    if (rc == B200_OK && Q > 0) h->launches += 1;
+    return rc;
+}
+
 extern "C" int b200clip_merge_topk(b200clip_handle* h, const float* part_scores, const int64_t* part_index, int32_t parts, int32_t Q,
                                    int32_t k, float* out_scores, int64_t* out_index, void* stream) {
     int rc = set_device(h); if (rc) return rc;

@@ -33,7 +33,9 @@ int launch_attention_tc(const void* qkv, void* out, int B, int S, int d, int hea
 struct TopkPlan { int splits, qtiles, cpl; long long rows_per_split; size_t cand_bytes, part_bytes, qstage_bytes; };
 int topk_plan(int Q, long long N, int k, TopkPlan* plan);
 int topk_run(const void* queries, const void* gallery, int Q, long long N, int D, int k, long long index_base, void* scratch,
-             const TopkPlan& plan, float* out_s, long long* out_i, DeviceStatus* status, cudaStream_t st);
+             const TopkPlan& plan, float* out_s, long long* out_i, DeviceStatus* status, cudaStream_t st,
+             unsigned long long* out_keys = nullptr);   // out_keys: emit 64-bit exchange keys (shard-local indices) instead of (out_s, out_i)
+int merge_topk_keys_run(const unsigned long long* pkeys, const long long* bases_dev, int P, int Q, int k, float* out_s, long long* out_i, cudaStream_t st);
 int merge_topk_run(const float* ps, const long long* pi, int P, int Q, int k, float* out_s, long long* out_i, cudaStream_t st);
 int classify_run(const float* img, const float* labels_unit, int B, int N, int D, float scale, int softmax, int k,
                  float* out_v, long long* out_i, cudaStream_t st);

@@ -381,10 +381,15 @@ __device__ __forceinline__ void scan_hist(const int* hist, int kk, bool hi_first
     }
 }
 
-template <int NT>
-__global__ void __launch_bounds__(NT) merge_topk_kernel(const float* __restrict__ ps, const long long* __restrict__ pi, int P,
+// Candidate exchange format between GPUs: one 64-bit key per candidate = order-preserving score bits (high word) | ~(row index inside
+// the owning shard) (low word), 0 = empty slot.  8 bytes instead of 4 + 8, ONE all-gather instead of two; the receiving merge adds each
+// part's index_base back (bases[part]).  KEYS_IN selects that input form; out_keys != nullptr makes the kernel emit it (indices
+// relative to key_base) instead of (out_s, out_i).
+template <int NT, bool KEYS_IN>
+__global__ void __launch_bounds__(NT) merge_topk_kernel(const float* __restrict__ ps, const long long* __restrict__ pi,
+                                                                   const unsigned long long* __restrict__ pkeys, const long long* __restrict__ bases, int P,
                                                                    int Q, int k, int cache_keys, float* __restrict__ out_s,
-                                                                   long long* __restrict__ out_i) {
+                                                                   long long* __restrict__ out_i, unsigned long long* __restrict__ out_keys, long long key_base) {
     extern __shared__ __align__(16) uint32_t key_cache[];     // [T] order-preserving score keys (0 = empty slot) when cache_keys
     __shared__ int hist[256];
     __shared__ int sh_digit, sh_before, sh_total, sh_count, sh_gt, sh_eq;
@@ -396,22 +401,31 @@ __global__ void __launch_bounds__(NT) merge_topk_kernel(const float* __restrict_
     auto key_of = [&](int e) -> uint32_t {
         if (cache_keys) return key_cache[e];
         const size_t o = offset(e);
+        if (KEYS_IN) return (uint32_t)(pkeys[o] >> 32);
         return pi[o] < 0 ? 0u : flip_f32(ps[o] + 0.0f);
+    };
+    auto id_of = [&](int e) -> long long {       // global index of a valid candidate
+        const size_t o = offset(e);
+        if (KEYS_IN) return bases[e / k] + (long long)(0xffffffffu - (uint32_t)pkeys[o]);
+        return pi[o];
     };
     if (tid == 0) { sh_count = 0; sh_gt = 0; sh_eq = 0; }
     if (cache_keys) {                                          // one pass over global memory, four loads in flight per thread
         for (int e0 = 0; e0 < T; e0 += 4 * NT) {
-            float s[4]; long long id[4];
+            float s[4]; long long id[4]; unsigned long long kk8[4];
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
                 const int e = e0 + u * NT + tid;
-                id[u] = -1; s[u] = 0.f;
-                if (e < T) { const size_t o = offset(e); id[u] = pi[o]; s[u] = ps[o]; }
+                id[u] = -1; s[u] = 0.f; kk8[u] = 0ull;
+                if (e < T) {
+                    const size_t o = offset(e);
+                    if (KEYS_IN) kk8[u] = pkeys[o]; else { id[u] = pi[o]; s[u] = ps[o]; }
+                }
             }
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
                 const int e = e0 + u * NT + tid;
-                if (e < T) key_cache[e] = id[u] < 0 ? 0u : flip_f32(s[u] + 0.0f);
+                if (e < T) key_cache[e] = KEYS_IN ? (uint32_t)(kk8[u] >> 32) : (id[u] < 0 ? 0u : flip_f32(s[u] + 0.0f));
             }
         }
     }
@@ -459,7 +473,7 @@ __global__ void __launch_bounds__(NT) merge_topk_kernel(const float* __restrict_
                     const int e = e0 + tid;
                     bool act = e < T && key_of(e) == prefix;
                     unsigned long long u = 0;
-                    if (act) { u = (unsigned long long)pi[offset(e)]; act = pass == 0 || (u >> (shift + 8)) == (ip >> (shift + 8)); }
+                    if (act) { u = (unsigned long long)id_of(e); act = pass == 0 || (u >> (shift + 8)) == (ip >> (shift + 8)); }
                     hist_add(hist, act, (int)((u >> shift) & 255));
                 }
                 __syncthreads();
@@ -477,11 +491,10 @@ __global__ void __launch_bounds__(NT) merge_topk_kernel(const float* __restrict_
         const uint32_t key = key_of(e);
         if (key == 0u) continue;
         if (all || key > prefix || key == prefix) {
-            const size_t o = offset(e);
-            const long long id = pi[o];
+            const long long id = id_of(e);
             if (all || key > prefix || id <= idx_cut) {
                 const int pos = atomicAdd(&sh_count, 1);
-                if (pos < MERGE_KMAX) { ss[pos] = ps[o] + 0.0f; si[pos] = id; }
+                if (pos < MERGE_KMAX) { ss[pos] = KEYS_IN ? unflip_f32(key) : ps[offset(e)] + 0.0f; si[pos] = id; }
             }
         }
     }
@@ -506,12 +519,18 @@ __global__ void __launch_bounds__(NT) merge_topk_kernel(const float* __restrict_
         }
     for (int e = tid; e < k; e += NT) {
         const bool valid = e < cnt;
-        out_s[(size_t)qi * k + e] = valid ? ss[e] : -INFINITY;
-        out_i[(size_t)qi * k + e] = valid ? si[e] : -1;
+        if (out_keys != nullptr) {
+            out_keys[(size_t)qi * k + e] = valid ? (((unsigned long long)flip_f32(ss[e]) << 32) | (0xffffffffu - (uint32_t)(si[e] - key_base))) : 0ull;
+        } else {
+            out_s[(size_t)qi * k + e] = valid ? ss[e] : -INFINITY;
+            out_i[(size_t)qi * k + e] = valid ? si[e] : -1;
+        }
     }
 }
 
-int merge_topk_run(const float* ps, const long long* pi, int P, int Q, int k, float* out_s, long long* out_i, cudaStream_t st) {
+template <bool KEYS_IN>
+static int merge_launch(const float* ps, const long long* pi, const unsigned long long* pkeys, const long long* bases, int P, int Q, int k,
+                        float* out_s, long long* out_i, unsigned long long* out_keys, long long key_base, cudaStream_t st) {
     B200_REQUIRE(P > 0 && k > 0, "merge_topk: need at least one part and k > 0");
     B200_REQUIRE(k <= MERGE_KMAX, "merge_topk: k larger than 1024 is not supported");
     B200_REQUIRE((long long)P * k < (1LL << 30), "merge_topk: too many candidates per query");
@@ -520,14 +539,21 @@ int merge_topk_run(const float* ps, const long long* pi, int P, int Q, int k, fl
     const int cache = T * 4 <= 160 * 1024;                 // keys fit in shared memory next to the sort buffers
     const size_t smem = cache ? T * 4 : 0;
     if (Q <= 2 * kNumSMs) {
-        if (smem > 32 * 1024) B200_CUDA_OK(cudaFuncSetAttribute(merge_topk_kernel<1024>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        merge_topk_kernel<1024><<<Q, 1024, smem, st>>>(ps, pi, P, Q, k, cache, out_s, out_i);
+        if (smem > 32 * 1024) B200_CUDA_OK(cudaFuncSetAttribute(merge_topk_kernel<1024, KEYS_IN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        merge_topk_kernel<1024, KEYS_IN><<<Q, 1024, smem, st>>>(ps, pi, pkeys, bases, P, Q, k, cache, out_s, out_i, out_keys, key_base);
     } else {
-        if (smem > 32 * 1024) B200_CUDA_OK(cudaFuncSetAttribute(merge_topk_kernel<256>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        merge_topk_kernel<256><<<Q, 256, smem, st>>>(ps, pi, P, Q, k, cache, out_s, out_i);
+        if (smem > 32 * 1024) B200_CUDA_OK(cudaFuncSetAttribute(merge_topk_kernel<256, KEYS_IN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        merge_topk_kernel<256, KEYS_IN><<<Q, 256, smem, st>>>(ps, pi, pkeys, bases, P, Q, k, cache, out_s, out_i, out_keys, key_base);
     }
     B200_CUDA_OK(cudaGetLastError());
     return B200_OK;
+}
+int merge_topk_run(const float* ps, const long long* pi, int P, int Q, int k, float* out_s, long long* out_i, cudaStream_t st) {
+    return merge_launch<false>(ps, pi, nullptr, nullptr, P, Q, k, out_s, out_i, nullptr, 0, st);
+}
+// parts as exchange keys [P][Q][k] + the index_base of every part (device array [P]) -> (scores, global indices)
+int merge_topk_keys_run(const unsigned long long* pkeys, const long long* bases_dev, int P, int Q, int k, float* out_s, long long* out_i, cudaStream_t st) {
+    return merge_launch<true>(nullptr, nullptr, pkeys, bases_dev, P, Q, k, out_s, out_i, nullptr, 0, st);
 }
 
 // ------------------------------------------------------------------------------------------ host side
@@ -583,7 +609,8 @@ template <int CPL> static int launch_topk(const CUtensorMap& tq, const CUtensorM
 // queries fp16 [Q, D], gallery fp16 [N, D] (both row-major, D % 64 == 0).  scratch must hold
 // plan.cand_bytes + plan.part_bytes bytes (256-byte aligned).  Outputs: scores fp32 [Q,k], idx int64 [Q,k].
 int topk_run(const void* queries, const void* gallery, int Q, long long N, int D, int k, long long index_base,
-             void* scratch, const TopkPlan& plan, float* out_s, long long* out_i, DeviceStatus* status, cudaStream_t st) {
+             void* scratch, const TopkPlan& plan, float* out_s, long long* out_i, DeviceStatus* status, cudaStream_t st,
+             unsigned long long* out_keys) {
     B200_REQUIRE(D > 0 && D % 64 == 0, "topk: embedding dim must be a multiple of 64");
     B200_REQUIRE(plan.qstage_bytes == 0 || D <= 1024, "topk: embedding dim above 1024 is not supported for batches below 128 queries");
     B200_REQUIRE(N < (1LL << 31), "topk: at most 2^31-1 gallery rows per GPU");
@@ -611,6 +638,8 @@ int topk_run(const void* queries, const void* gallery, int Q, long long N, int D
                  part_s, part_i, index_base, scatter, status, 0, gtau};
     rc = plan.cpl == 16 ? launch_topk<16>(tq, tg, p, st) : launch_topk<32>(tq, tg, p, st);
     if (rc) return rc;
+    if (out_keys != nullptr)     // exchange form for the sharded search: indices relative to this shard
+        return merge_launch<false>(part_s, part_i, nullptr, nullptr, plan.splits, Q, k, nullptr, nullptr, out_keys, index_base, st);
     return merge_topk_run(part_s, part_i, plan.splits, Q, k, out_s, out_i, st);
 }
 
@@ -681,7 +710,7 @@ extern "C" int b200clip_topk_static(const void* queries_f16_dev, int32_t Q, cons
     // counts live in registers and every result slot that is read is written first.
     B200_CUDA_OK(cudaMemsetAsync(base, 0, 256, st));
     return topk_run(queries_f16_dev, gallery_f16_dev, Q, N, D, k, index_base, reinterpret_cast<unsigned char*>(base) + 256, plan,
-                    out_scores_dev, reinterpret_cast<long long*>(out_index_dev), reinterpret_cast<DeviceStatus*>(base), st);
+                    out_scores_dev, reinterpret_cast<long long*>(out_index_dev), reinterpret_cast<DeviceStatus*>(base), st, nullptr);
 }
 
 extern "C" int b200clip_topk_static_status(void* stream) {

@@ -377,6 +377,27 @@ class Engine:
                                           int(index_base), C.c_void_p(scores.data_ptr()), C.c_void_p(idx.data_ptr()), self._stream()))
         return scores, idx
 
+    def topk_keys(self, queries_f16, gallery_f16, k: int):
+        """This shard's top-k as 64-bit exchange keys [Q, k] (int64 storage): score bits | ~(row inside the shard), 0 = empty."""
+        torch = _torch()
+        Q, D = queries_f16.shape
+        assert queries_f16.dtype == torch.float16 and gallery_f16.dtype == torch.float16
+        assert queries_f16.is_contiguous() and gallery_f16.is_contiguous()
+        keys = torch.empty((Q, k), dtype=torch.int64, device=queries_f16.device)
+        _lib.check(self.lib.b200clip_topk_keys(self._h, C.c_void_p(queries_f16.data_ptr()), Q, C.c_void_p(gallery_f16.data_ptr()), gallery_f16.shape[0],
+                                               D, k, C.c_void_p(keys.data_ptr()), self._stream()))
+        return keys
+
+    def merge_topk_keys(self, part_keys, part_bases):
+        """part_keys [P,Q,k] exchange keys, part_bases [P] int64 (cuda): index_base of every part -> merged ([Q,k] f32, [Q,k] i64)."""
+        torch = _torch()
+        P, Q, k = part_keys.shape
+        scores = torch.empty((Q, k), dtype=torch.float32, device=part_keys.device)
+        idx = torch.empty((Q, k), dtype=torch.int64, device=part_keys.device)
+        _lib.check(self.lib.b200clip_merge_topk_keys(self._h, C.c_void_p(part_keys.data_ptr()), C.c_void_p(part_bases.data_ptr()), P, Q, k,
+                                                     C.c_void_p(scores.data_ptr()), C.c_void_p(idx.data_ptr()), self._stream()))
+        return scores, idx
+
     def merge_topk(self, part_scores, part_idx):
         """part_scores [P,Q,k] f32, part_idx [P,Q,k] i64 (cuda) -> merged ([Q,k], [Q,k])."""
         torch = _torch()

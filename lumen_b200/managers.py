@@ -118,19 +118,29 @@ class B200CLIPModelManager:
 
 class ShardedGallery:
     """An fp16 embedding gallery row-sharded over the ranks of `group` (or a single GPU when torch.distributed is
-    not initialised).  search(): each rank runs the fused GEMM + top-k kernel on its shard, one all-gather moves the
-    [Q,k] (score, index) candidates, every rank merges them with the (score desc, index asc) order."""
+    not initialised).  search(): each rank runs the fused GEMM + top-k kernel on its shard, ONE all-gather moves the candidates
+    as 64-bit keys (score bits | ~row-in-shard: Q*k*8 bytes per GPU), every rank merges them with the (score desc, index asc) order."""
 
     def __init__(self, engine, shard_f16, index_base: int = 0, group=None) -> None:
         torch = _torch()
         assert shard_f16.dtype == torch.float16 and shard_f16.is_contiguous()
         self.engine, self.shard, self.index_base, self.group = engine, shard_f16, int(index_base), group
+        self._bases = None                                  # index_base of every rank, gathered once
 
     @staticmethod
     def shard_bounds(n_total: int, world: int, rank: int) -> tuple[int, int]:
         per = (n_total + world - 1) // world
         lo = min(n_total, rank * per)
         return lo, min(n_total, lo + per)
+
+    def _part_bases(self, world: int, device):
+        torch = _torch()
+        if self._bases is None:
+            mine = torch.tensor([self.index_base], dtype=torch.int64, device=device)
+            allb = torch.empty((world,), dtype=torch.int64, device=device)
+            torch.distributed.all_gather_into_tensor(allb, mine, group=self.group)
+            self._bases = allb
+        return self._bases
 
     def search(self, queries_f16, k: int, events: list | None = None):
         """(scores [Q,k], global indices [Q,k]).  `events`, when given, receives four CUDA events recorded on the current stream:
@@ -143,22 +153,32 @@ class ShardedGallery:
                 e.record()
                 events.append(e)
 
+        dist = torch.distributed
+        sharded = dist.is_available() and dist.is_initialized() and dist.get_world_size(self.group) > 1
+        if sharded and dist.get_backend(self.group) == "nccl" and hasattr(self.engine, "topk_keys"):
+            world = dist.get_world_size(self.group)
+            bases = self._part_bases(world, queries_f16.device)
+            mark()
+            keys = self.engine.topk_keys(queries_f16, self.shard, k)
+            mark()
+            all_k = torch.empty((world,) + tuple(keys.shape), dtype=keys.dtype, device=keys.device)
+            dist.all_gather_into_tensor(all_k, keys, group=self.group)          # the one collective of the design, over NVLink
+            mark()
+            out = self.engine.merge_topk_keys(all_k, bases)
+            mark()
+            return out
         mark()
         scores, idx = self.engine.topk(queries_f16, self.shard, k, self.index_base)
         mark()
-        dist = torch.distributed
-        if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size(self.group) == 1:
+        if not sharded:
             mark(); mark()
             return scores, idx
+        # any other backend (gloo in the CPU tests of the host logic): scores and indices travel as two tensors
         world = dist.get_world_size(self.group)
         all_s = torch.empty((world,) + tuple(scores.shape), dtype=scores.dtype, device=scores.device)
         all_i = torch.empty((world,) + tuple(idx.shape), dtype=idx.dtype, device=idx.device)
-        if dist.get_backend(self.group) == "nccl":          # one fused collective per tensor over NVLink
-            dist.all_gather_into_tensor(all_s, scores, group=self.group)
-            dist.all_gather_into_tensor(all_i, idx, group=self.group)
-        else:                                                # gloo (CPU tests of the host logic)
-            dist.all_gather(list(all_s.unbind(0)), scores, group=self.group)
-            dist.all_gather(list(all_i.unbind(0)), idx, group=self.group)
+        dist.all_gather(list(all_s.unbind(0)), scores, group=self.group)
+        dist.all_gather(list(all_i.unbind(0)), idx, group=self.group)
         mark()
         out = self.engine.merge_topk(all_s, all_i)
         mark()

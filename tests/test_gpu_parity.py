@@ -334,6 +334,31 @@ def test_topk_adversarial_ascending_and_merge():
     eng.close()
 
 
+def test_topk_exchange_keys_merge_like_a_sharded_search():
+    """The 64-bit candidate form the sharded search moves between GPUs, emulated on one GPU: per-shard keys -> merge with the shards'
+    index bases = the unsharded answer, ties across shard boundaries in global index order, ragged last shard, k > rows of a shard."""
+    from lumen_b200.engine import Engine
+    from oracle import clip_oracle as O
+    eng = Engine({}, device=0)
+    rng = np.random.default_rng(21)
+    for N, D, Q, k, shards in ((10007, 64, 37, 100, 4), (1003, 64, 9, 20, 2), (300, 128, 130, 120, 3)):
+        g = rng.integers(-8, 9, (N, D)).astype(np.float16)
+        g[N // 2 - 2:N // 2 + 48] = g[:50]                       # duplicates straddling a shard boundary
+        q = rng.integers(-8, 9, (Q, D)).astype(np.float16)
+        qt = torch.from_numpy(q).cuda()
+        per = (N + shards - 1) // shards
+        bases, keys = [], []
+        for r in range(shards):
+            lo, hi = r * per, min(N, (r + 1) * per)
+            keys.append(eng.topk_keys(qt, torch.from_numpy(g[lo:hi].copy()).cuda(), k))
+            bases.append(lo + 5000)                              # a global offset on top, as DeviceGallery.index_base allows
+        s, i = eng.merge_topk_keys(torch.stack(keys), torch.tensor(bases, dtype=torch.int64, device="cuda"))
+        eng.sync()
+        so, io = O.topk_cosine(q, g, k, index_base=5000)
+        assert np.array_equal(i.cpu().numpy(), io) and np.array_equal(s.cpu().numpy(), so), (N, D, Q, k)
+    eng.close()
+
+
 def test_topk_exact_zero_scores_across_splits():
     """Scores of exactly +0.0 (zero / padding rows, a zero query) tie across the gallery splits that share a threshold: the
     k smallest indices must win, every run (the shared bound must not exclude scores equal to it)."""

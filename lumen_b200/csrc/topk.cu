@@ -32,13 +32,16 @@ struct TopkParams {
     long long rows_per_split;    // multiple of 256
     int splits, qtiles;
     unsigned long long* cand;    // [splits][qtiles*128][32*CPL]
-    float* part_scores;          // [splits][Q][k]
-    long long* part_idx;         // [splits][Q][k]
+    float* part_scores;          // [Q][splits * k]: every split appends its survivors to the query's list (pcount = entries so far)
+    long long* part_idx;         // [Q][splits * k]
     long long index_base;
     int scatter;                 // queries were spread over the four TMEM lane quarters (see scatter_queries_kernel)
     DeviceStatus* status;
     int stages;                  // gallery ring depth when the query tile is resident (QRES)
     unsigned* gtau;              // [Q] best lower bound any split has found for the query's k-th best score (flip_f32 key, 0 = none)
+    unsigned* pubmax;            // [Q][splits] best score each split has seen so far for the query (flip_f32 key, 0 = nothing yet)
+    int share_max;               // splits >= k: the k-th largest of the published maxima bounds the global k-th best (see kth_published_max)
+    int* pcount;                 // [Q] candidates the splits have written for the query
 };
 
 __device__ __forceinline__ uint32_t flip_f32(float s) {
@@ -61,7 +64,7 @@ __device__ __forceinline__ float unflip_f32(uint32_t u) {
 // `tau_out` is the new threshold (-inf while fewer than k candidates exist).
 template <int CPL>
 __device__ __noinline__ int compact_row(unsigned long long* rowptr, int n, int k, int lane, bool exact, int room,
-                                        float* tau_out, float* part_s, long long* part_i, long long index_base) {
+                                        float* tau_out, float* part_s, long long* part_i, long long index_base, bool pad = true) {
     uint32_t hi[CPL], lo[CPL];
     __syncwarp();
 #pragma unroll
@@ -136,14 +139,70 @@ __device__ __noinline__ int compact_row(unsigned long long* rowptr, int n, int k
             const int e = i * 32 + lane;
             if (e < k) {
                 const bool valid = e < n;
-                part_s[e] = valid ? unflip_f32(hi[i]) : -INFINITY;
-                part_i[e] = valid ? index_base + (long long)(0xffffffffu - lo[i]) : -1;
+                if (valid || pad) {
+                    part_s[e] = valid ? unflip_f32(hi[i]) : -INFINITY;
+                    part_i[e] = valid ? index_base + (long long)(0xffffffffu - lo[i]) : -1;
+                }
             }
         }
     }
     *tau_out = tau;
     __syncwarp();
     return keep;
+}
+
+// Whole warp: drop the entries of one row's list that score below `thr` (an order-preserving key).  Entries EQUAL to it stay: the
+// index-ordered tie rule may still prefer them.  One pass, no select; returns the new count.
+template <int CPL>
+__device__ __forceinline__ int filter_row(unsigned long long* rowptr, int n, uint32_t thr, int lane) {
+    unsigned long long key[CPL];
+    __syncwarp();
+#pragma unroll
+    for (int i = 0; i < CPL; ++i) {
+        const int e = i * 32 + lane;
+        key[i] = e < n ? __ldcg(rowptr + e) : 0ull;
+    }
+    __syncwarp();                                     // every lane holds its entries before any slot is overwritten
+    int base = 0;
+    const uint32_t lt = (1u << lane) - 1u;
+#pragma unroll
+    for (int i = 0; i < CPL; ++i) {
+        const bool pred = key[i] != 0ull && (uint32_t)(key[i] >> 32) >= thr;
+        const uint32_t bal = __ballot_sync(0xffffffffu, pred);
+        if (pred) __stcg(rowptr + base + __popc(bal & lt), key[i]);
+        base += __popc(bal);
+    }
+    __syncwarp();
+    return base;
+}
+
+// Small query batches run one CTA per gallery split (148 or 296 of them), each seeing only 1/148 of the rows: a split's own k-th best
+// is a poor bound, and warming it up costs list compactions.  But every split can cheaply publish the BEST score it has seen for a
+// query, and the k-th largest of those maxima is a lower bound of the global k-th best (k distinct rows, one per split, score at
+// least that) - after one tile per split already near the 99.6th percentile, at the end within a hair of the true threshold.
+// Whole warp: that k-th largest for one query, resolved to the top 16 bits of the key (rounded down: still a valid bound); 0 while
+// fewer than k splits have published.
+__device__ __forceinline__ uint32_t kth_published_max(const unsigned* __restrict__ pub, int S, int k, int lane) {
+    constexpr int MAXV = 10;                          // S <= 2 * 148
+    uint32_t v[MAXV];
+    int have = 0;
+#pragma unroll
+    for (int i = 0; i < MAXV; ++i) {
+        const int idx = i * 32 + lane;
+        v[i] = (i * 32 < S && idx < S) ? __ldcg(pub + idx) : 0u;
+        have += __popc(__ballot_sync(0xffffffffu, v[i] != 0u));
+    }
+    if (have < k) return 0u;
+    uint32_t p = 0; int kk = k;
+#pragma unroll 1
+    for (int b = 31; b >= 16; --b) {
+        const uint32_t want = p | (1u << b), m = 0xffffffffu << b;
+        int c = 0;
+#pragma unroll
+        for (int i = 0; i < MAXV; ++i) if (i * 32 < S) c += __popc(__ballot_sync(0xffffffffu, (v[i] & m) == want));
+        if (c >= kk) p = want; else kk -= c;
+    }
+    return p;
 }
 
 // QRES: the CTA's query tile (128 x D fp16, D <= 512: at most 128 KB) is loaded ONCE and stays in shared memory; only gallery
@@ -240,12 +299,46 @@ topk_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         float tau = qrow < p.Q ? -INFINITY : INFINITY;      // padding rows of the last query tile never collect candidates
         int cnt = 0;
         bool ok = true;
+        float rowmax = -INFINITY;                            // best score this split has seen for the row (share_max)
         for (int t = 0; t < tiles && ok; ++t) {
             const int as = t & 1; const uint32_t aph = (t >> 1) & 1;
             if (!(ok = mbar_wait(&acc_full[as], aph, p.status, 14))) break;
             tc_fence_after();
             const long long n0 = n_lo + (long long)t * TK_BN;
             const uint32_t tsrc = tmem_base + ((uint32_t)(q * 32) << 16) + as * TK_BN;
+            if (p.share_max && t == 0) {
+                // No bound exists yet, and appending the whole first tile (256 entries per row, one scattered 8-byte store each) is
+                // what small batches used to pay most for.  So the first tile is read twice from TMEM: once for the row maxima only,
+                // which are published at once; then the CTA waits - bounded, a few microseconds - until k splits have reported for
+                // its query and the bounds of its own rows have arrived from the CTAs that own them; then the normal scan runs
+                // against a bound that already sits near the 99.6th percentile.  If the wait times out the scan just appends more.
+                uint32_t v0[32];
+#pragma unroll 1
+                for (int c = 0; c < TK_BN / 32; ++c) {
+                    tmem_ld_32x32(tsrc + c * 32, v0);
+                    tmem_ld_wait();
+                    const long long lf = n_hi - (n0 + c * 32);
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) if (j < lf) rowmax = fmaxf(rowmax, __uint_as_float(v0[j]));
+                }
+                if (qrow < p.Q && rowmax > -INFINITY) __stcg(p.pubmax + (size_t)qrow * p.splits + sp, flip_f32(rowmax));
+                if (q == 0) {
+                    const int myq = sp % p.Q;
+                    uint32_t kth = 0u;
+#pragma unroll 1
+                    for (int tries = 0; tries < 32 && kth == 0u; ++tries) {
+                        kth = kth_published_max(p.pubmax + (size_t)myq * p.splits, p.splits, p.k, lane);
+                        if (kth == 0u) __nanosleep(400);
+                    }
+                    if (kth != 0u && lane == 0) atomicMax(p.gtau + myq, kth);
+                }
+#pragma unroll 1
+                for (int tries = 0; tries < 96; ++tries) {
+                    const unsigned g0 = qrow < p.Q ? __ldcg(p.gtau + qrow) : 2u;
+                    if (!__any_sync(0xffffffffu, g0 <= 1u)) break;
+                    __nanosleep(400);
+                }
+            }
             // Threshold sharing: the k-th best score another gallery split has already established for this query bounds the global
             // k-th best from below, so nothing below it can reach the final top-k.  Scores EQUAL to it are kept (key - 1 = the next
             // float below): the index-ordered tie rule may still prefer them.  Without this every split warms up on its own.
@@ -261,10 +354,19 @@ topk_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
             // Scan 8 chunks of 32 scores; the TMEM load of chunk c+1 is in flight while chunk c is examined.
             // A thread first reduces its 32 scores to their maximum: only if that beats tau (rare once the
             // threshold has settled) does it walk the chunk and append the survivors.
+            const bool ragged = n_hi - n0 < TK_BN;                               // last tile of the gallery: columns past the end hold zeros
             auto scan = [&](const uint32_t (&v)[32], int c) {
                 float mx = __uint_as_float(v[0]);
 #pragma unroll
                 for (int j = 1; j < 32; ++j) mx = fmaxf(mx, __uint_as_float(v[j]));
+                if (p.share_max) {
+                    if (!ragged) rowmax = fmaxf(rowmax, mx);
+                    else {
+                        const long long lf = n_hi - (n0 + c * 32);
+#pragma unroll
+                        for (int j = 0; j < 32; ++j) if (j < lf) rowmax = fmaxf(rowmax, __uint_as_float(v[j]));
+                    }
+                }
                 if (!__any_sync(0xffffffffu, mx > tau)) return;                   // nothing in this 32x32 block beats any row's threshold
                 // branch-free bit mask of this row's survivors, then one loop iteration per survivor (usually 0 or 1):
                 // the score is picked out of the 32 registers with a 5-level select tree instead of 32 branches
@@ -306,28 +408,54 @@ topk_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
             tc_fence_before();
             __syncwarp();
             if (lane == 0) mbar_arrive(&acc_empty[as]);
-            // make room for the next tile (256 possible appends) while the MMAs of tile t+1 run
+            if (p.share_max) {
+                // publish this split's best score per query, and turn everybody's maxima into a bound for ONE query per CTA and tile
+                // (query (sp + t) mod Q: with at least as many CTAs as queries every query is refreshed by somebody each round;
+                // the result reaches all CTAs through gtau).  One row's worth of work (~1 us) for the first epilogue warp.
+                if (qrow < p.Q && rowmax > -INFINITY) __stcg(p.pubmax + (size_t)qrow * p.splits + sp, flip_f32(rowmax));
+                if (q == 0 && (t < 4 || (t & 3) == 0)) {
+                    const int myq = (sp + t) % p.Q;
+                    const uint32_t kth = kth_published_max(p.pubmax + (size_t)myq * p.splits, p.splits, p.k, lane);
+                    if (kth != 0u && lane == 0) atomicMax(p.gtau + myq, kth);
+                }
+            }
+            // make room for the next tile (256 possible appends) while the MMAs of tile t+1 run: first drop what the shared bound
+            // already rules out (one cheap pass), and only if the list is still too long select its k best
             unsigned need = __ballot_sync(0xffffffffu, cnt + TK_BN > C);
             while (need) {
                 const int src = __ffs(need) - 1;
                 need &= need - 1;
-                const int n = __shfl_sync(0xffffffffu, cnt, src);
-                float tnew;
-                const int keep = compact_row<CPL>(warp_rows + (size_t)src * C, n, p.k, lane, false, C - TK_BN, &tnew, nullptr, nullptr, 0);
-                if (lane == src) {
-                    cnt = keep; tau = fmaxf(tau, tnew);
-                    if (qrow < p.Q) atomicMax(p.gtau + qrow, flip_f32(tnew));       // k rows of THIS split score >= tnew
+                int n = __shfl_sync(0xffffffffu, cnt, src);
+                const long long qs = __shfl_sync(0xffffffffu, qrow, src);
+                const unsigned g = qs < p.Q ? __ldcg(p.gtau + qs) : 0u;
+                if (g > 1u) n = filter_row<CPL>(warp_rows + (size_t)src * C, n, g, lane);
+                float tnew = -INFINITY;
+                if (n + TK_BN > C) {
+                    n = compact_row<CPL>(warp_rows + (size_t)src * C, n, p.k, lane, false, C - TK_BN, &tnew, nullptr, nullptr, 0);
+                    if (lane == src && qrow < p.Q) atomicMax(p.gtau + qrow, flip_f32(tnew));   // k rows of THIS split score >= tnew
                 }
+                if (lane == src) { cnt = n; tau = fmaxf(tau, tnew); }
             }
         }
         // final: every row sorted, best k written as (score, global index) for the merge kernel
+        const size_t cap = (size_t)p.splits * p.k;
         for (int src = 0; src < 32; ++src) {
-            const int n = __shfl_sync(0xffffffffu, cnt, src);
+            int n = __shfl_sync(0xffffffffu, cnt, src);
             float tnew;
             const long long qr = (long long)qt * TK_BM + (p.scatter ? src * 4 + q : q * 32 + src);
-            if (qr < p.Q)       // warp-uniform
-                compact_row<CPL>(warp_rows + (size_t)src * C, n, p.k, lane, true, C, &tnew, p.part_scores + ((size_t)sp * p.Q + qr) * p.k,
-                                 p.part_idx + ((size_t)sp * p.Q + qr) * p.k, p.index_base);
+            if (qr < p.Q) {     // warp-uniform
+                // what the shared bound rules out needs no selecting: with the maxima-based bound a split is usually left with a
+                // handful of candidates, fewer than k, which compact_row then just writes out
+                const unsigned g = __ldcg(p.gtau + qr);
+                if (g > 1u && n > 0) n = filter_row<CPL>(warp_rows + (size_t)src * C, n, g, lane);
+                if (n > 0) {
+                    int base = 0;
+                    if (lane == 0) base = atomicAdd(p.pcount + qr, min(n, p.k));      // this split's slice of the query's candidate list
+                    base = __shfl_sync(0xffffffffu, base, 0);
+                    compact_row<CPL>(warp_rows + (size_t)src * C, n, p.k, lane, true, C, &tnew, p.part_scores + (size_t)qr * cap + base,
+                                     p.part_idx + (size_t)qr * cap + base, p.index_base, /*pad*/ false);
+                }
+            }
         }
     }
     tc_fence_before();
@@ -389,14 +517,22 @@ template <int NT, bool KEYS_IN>
 __global__ void __launch_bounds__(NT) merge_topk_kernel(const float* __restrict__ ps, const long long* __restrict__ pi,
                                                                    const unsigned long long* __restrict__ pkeys, const long long* __restrict__ bases, int P,
                                                                    int Q, int k, int cache_keys, float* __restrict__ out_s,
-                                                                   long long* __restrict__ out_i, unsigned long long* __restrict__ out_keys, long long key_base) {
+                                                                   long long* __restrict__ out_i, unsigned long long* __restrict__ out_keys, long long key_base,
+                                                                   const int* __restrict__ counts) {
     extern __shared__ __align__(16) uint32_t key_cache[];     // [T] order-preserving score keys (0 = empty slot) when cache_keys
     __shared__ int hist[256];
     __shared__ int sh_digit, sh_before, sh_total, sh_count, sh_gt, sh_eq;
     __shared__ float ss[MERGE_KMAX];
     __shared__ long long si[MERGE_KMAX];
-    const int qi = blockIdx.x, T = P * k, tid = threadIdx.x;
-    auto offset = [&](int e) -> size_t { const int part = e / k; return ((size_t)part * Q + qi) * k + (e - part * k); };
+    // counts != nullptr: the query's candidates are one list of counts[qi] entries at [qi][P * k] (what topk_tc_kernel writes);
+    // otherwise P parts of k slots each, [P][Q][k], empty slots marked by a negative index (the public merge entry point)
+    const int qi = blockIdx.x, tid = threadIdx.x;
+    const int T = counts != nullptr ? min(counts[qi], P * k) : P * k;
+    auto offset = [&](int e) -> size_t {
+        if (counts != nullptr) return (size_t)qi * P * k + e;
+        const int part = e / k;
+        return ((size_t)part * Q + qi) * k + (e - part * k);
+    };
     // key of candidate e: from shared memory when cached, else recomputed from global memory
     auto key_of = [&](int e) -> uint32_t {
         if (cache_keys) return key_cache[e];
@@ -530,7 +666,7 @@ __global__ void __launch_bounds__(NT) merge_topk_kernel(const float* __restrict_
 
 template <bool KEYS_IN>
 static int merge_launch(const float* ps, const long long* pi, const unsigned long long* pkeys, const long long* bases, int P, int Q, int k,
-                        float* out_s, long long* out_i, unsigned long long* out_keys, long long key_base, cudaStream_t st) {
+                        float* out_s, long long* out_i, unsigned long long* out_keys, long long key_base, cudaStream_t st, const int* counts = nullptr) {
     B200_REQUIRE(P > 0 && k > 0, "merge_topk: need at least one part and k > 0");
     B200_REQUIRE(k <= MERGE_KMAX, "merge_topk: k larger than 1024 is not supported");
     B200_REQUIRE((long long)P * k < (1LL << 30), "merge_topk: too many candidates per query");
@@ -540,10 +676,10 @@ static int merge_launch(const float* ps, const long long* pi, const unsigned lon
     const size_t smem = cache ? T * 4 : 0;
     if (Q <= 2 * kNumSMs) {
         if (smem > 32 * 1024) B200_CUDA_OK(cudaFuncSetAttribute(merge_topk_kernel<1024, KEYS_IN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        merge_topk_kernel<1024, KEYS_IN><<<Q, 1024, smem, st>>>(ps, pi, pkeys, bases, P, Q, k, cache, out_s, out_i, out_keys, key_base);
+        merge_topk_kernel<1024, KEYS_IN><<<Q, 1024, smem, st>>>(ps, pi, pkeys, bases, P, Q, k, cache, out_s, out_i, out_keys, key_base, counts);
     } else {
         if (smem > 32 * 1024) B200_CUDA_OK(cudaFuncSetAttribute(merge_topk_kernel<256, KEYS_IN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        merge_topk_kernel<256, KEYS_IN><<<Q, 256, smem, st>>>(ps, pi, pkeys, bases, P, Q, k, cache, out_s, out_i, out_keys, key_base);
+        merge_topk_kernel<256, KEYS_IN><<<Q, 256, smem, st>>>(ps, pi, pkeys, bases, P, Q, k, cache, out_s, out_i, out_keys, key_base, counts);
     }
     B200_CUDA_OK(cudaGetLastError());
     return B200_OK;
@@ -558,11 +694,12 @@ int merge_topk_keys_run(const unsigned long long* pkeys, const long long* bases_
 
 // ------------------------------------------------------------------------------------------ host side
 static size_t topk_gtau_bytes(int Q) { return ((size_t)Q * 4 + 255) & ~(size_t)255; }
+// gtau [Q], pcount [Q], pubmax [Q][splits]: all start every call at zero (one memset)
+static size_t topk_shared_bytes(int Q, int splits) { return 2 * topk_gtau_bytes(Q) + (((size_t)Q * splits * 4 + 255) & ~(size_t)255); }
 
 int topk_plan(int Q, long long N, int k, TopkPlan* plan) {
     B200_REQUIRE(Q > 0 && N > 0 && k > 0, "topk: Q, N and k must be positive");
     B200_REQUIRE(k <= 768, "topk: k larger than 768 is not supported");
-    plan->cpl = k <= 256 ? 16 : 32;
     plan->qtiles = (Q + TK_BM - 1) / TK_BM;
     const long long ntiles = (N + TK_BN - 1) / TK_BN;
     // qtiles * splits CTAs: fill one wave of 148 SMs when the query tiles are few, two waves otherwise
@@ -574,9 +711,12 @@ int topk_plan(int Q, long long N, int k, TopkPlan* plan) {
     const long long tiles_per_split = (ntiles + splits - 1) / splits;
     plan->rows_per_split = tiles_per_split * TK_BN;
     plan->splits = (int)((ntiles + tiles_per_split - 1) / tiles_per_split);
+    // lists of 512 entries, or 1024 for k > 256 and in the maxima-sharing mode (one query tile, at least k splits): there the first
+    // tiles are appended whole (no bound exists yet) and must fit until the shared bound arrives, two or three tiles in
+    plan->cpl = (k <= 256 && !(plan->qtiles == 1 && plan->splits >= k)) ? 16 : 32;
     plan->cand_bytes = (size_t)plan->splits * plan->qtiles * TK_BM * 32 * plan->cpl * 8;
     plan->part_bytes = (((size_t)plan->splits * Q * k * 4 + 255) & ~(size_t)255) + (size_t)plan->splits * Q * k * 8;
-    plan->part_bytes = ((plan->part_bytes + 255) & ~(size_t)255) + topk_gtau_bytes(Q);     // the shared thresholds sit at the end
+    plan->part_bytes = ((plan->part_bytes + 255) & ~(size_t)255) + topk_shared_bytes(Q, plan->splits);     // the shared thresholds sit at the end
     plan->qstage_bytes = Q < TK_BM ? (size_t)TK_BM * 1024 * 2 : 0;      // staged, interleaved copy of a small query batch (D <= 1024)
     return B200_OK;
 }
@@ -632,15 +772,18 @@ int topk_run(const void* queries, const void* gallery, int Q, long long N, int D
     if (rc) return rc;
     float* part_s = reinterpret_cast<float*>(sc + plan.cand_bytes);
     long long* part_i = reinterpret_cast<long long*>(sc + plan.cand_bytes + (((size_t)plan.splits * Q * k * 4 + 255) & ~(size_t)255));
-    unsigned* gtau = reinterpret_cast<unsigned*>(sc + plan.cand_bytes + plan.part_bytes - topk_gtau_bytes(Q));
-    B200_CUDA_OK(cudaMemsetAsync(gtau, 0, topk_gtau_bytes(Q), st));
+    unsigned* gtau = reinterpret_cast<unsigned*>(sc + plan.cand_bytes + plan.part_bytes - topk_shared_bytes(Q, plan.splits));
+    int* pcount = reinterpret_cast<int*>(reinterpret_cast<uint8_t*>(gtau) + topk_gtau_bytes(Q));
+    unsigned* pubmax = reinterpret_cast<unsigned*>(reinterpret_cast<uint8_t*>(gtau) + 2 * topk_gtau_bytes(Q));
+    B200_CUDA_OK(cudaMemsetAsync(gtau, 0, topk_shared_bytes(Q, plan.splits), st));
+    static const int share_on = [] { const char* e = getenv("B200_TOPK_SHAREMAX"); return e ? atoi(e) : 1; }();
+    const int share_max = (share_on && plan.qtiles == 1 && plan.splits >= k && plan.splits <= 320) ? 1 : 0;
     TopkParams p{Q, D, k, N, plan.rows_per_split, plan.splits, plan.qtiles, reinterpret_cast<unsigned long long*>(sc),
-                 part_s, part_i, index_base, scatter, status, 0, gtau};
+                 part_s, part_i, index_base, scatter, status, 0, gtau, pubmax, share_max, pcount};
     rc = plan.cpl == 16 ? launch_topk<16>(tq, tg, p, st) : launch_topk<32>(tq, tg, p, st);
     if (rc) return rc;
-    if (out_keys != nullptr)     // exchange form for the sharded search: indices relative to this shard
-        return merge_launch<false>(part_s, part_i, nullptr, nullptr, plan.splits, Q, k, nullptr, nullptr, out_keys, index_base, st);
-    return merge_topk_run(part_s, part_i, plan.splits, Q, k, out_s, out_i, st);
+    // out_keys: exchange form for the sharded search, indices relative to this shard
+    return merge_launch<false>(part_s, part_i, nullptr, nullptr, plan.splits, Q, k, out_s, out_i, out_keys, index_base, st, pcount);
 }
 
 }  // namespace b200
@@ -687,7 +830,7 @@ extern "C" int b200clip_topk_static(const void* queries_f16_dev, int32_t Q, cons
     const size_t budget = kStaticScratchBytes - 256;
     auto need = [&](long long splits) {
         return (size_t)splits * plan.qtiles * TK_BM * 32 * 16 * 8 + (((size_t)splits * Q * k * 4 + 255) & ~(size_t)255) +
-               (((size_t)splits * Q * k * 8 + 255) & ~(size_t)255) + topk_gtau_bytes(Q) + 256;
+               (((size_t)splits * Q * k * 8 + 255) & ~(size_t)255) + topk_shared_bytes(Q, (int)splits) + 256;
     };
     long long splits = (2LL * kNumSMs) / plan.qtiles;
     if (splits < 1) splits = 1;
@@ -703,7 +846,7 @@ extern "C" int b200clip_topk_static(const void* queries_f16_dev, int32_t Q, cons
     plan.splits = (int)((ntiles + tiles_per_split - 1) / tiles_per_split);
     plan.cand_bytes = (size_t)plan.splits * plan.qtiles * TK_BM * 32 * 16 * 8;
     plan.part_bytes = (((size_t)plan.splits * Q * k * 4 + 255) & ~(size_t)255) + (((size_t)plan.splits * Q * k * 8 + 255) & ~(size_t)255) +
-                      topk_gtau_bytes(Q);
+                      topk_shared_bytes(Q, plan.splits);
     plan.qstage_bytes = 0;
     cudaStream_t st = (cudaStream_t)stream;
     // The array keeps whatever the previous call left.  Only the watchdog words have to start at zero: candidate

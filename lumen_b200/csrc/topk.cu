@@ -25,6 +25,7 @@ namespace b200 {
 constexpr int TK_BM = 128, TK_BN = 256, TK_BK = 64, TK_STAGES = 4;
 constexpr int TK_A_BYTES = TK_BM * TK_BK * 2, TK_B_BYTES = TK_BN * TK_BK * 2, TK_STAGE_BYTES = TK_A_BYTES + TK_B_BYTES;
 constexpr int TK_SMEM = TK_STAGES * TK_STAGE_BYTES + 256 + 1024;
+constexpr int TK_THREADS = 64 + 8 * 32;      // TMA warp, MMA warp, eight epilogue warps
 
 struct TopkParams {
     int Q, D, k;
@@ -42,6 +43,8 @@ struct TopkParams {
     unsigned* pubmax;            // [Q][splits] best score each split has seen so far for the query (flip_f32 key, 0 = nothing yet)
     int share_max;               // splits >= k: the k-th largest of the published maxima bounds the global k-th best (see kth_published_max)
     int* pcount;                 // [Q] candidates the splits have written for the query
+    int halves;                  // 2: eight epilogue warps, each lane quarter served by two warps that scan one half of a tile's columns
+                                 // each and keep their own candidate lists (two independent scanners per row); 1: four warps
 };
 
 __device__ __forceinline__ uint32_t flip_f32(float s) {
@@ -209,7 +212,7 @@ __device__ __forceinline__ uint32_t kth_published_max(const unsigned* __restrict
 // tiles go through the ring (3 stages of 32 KB at D = 512).  Without it every gallery tile re-fetches the query tile from L2,
 // a third of the kernel's L2 -> SM traffic, and at Q = 4096 that traffic, not the tensor core, is what bounds the kernel.
 template <int CPL, bool QRES>
-__global__ void __launch_bounds__(192, 1)
+__global__ void __launch_bounds__(TK_THREADS, 1)
 topk_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmG, TopkParams p) {
     constexpr int C = 32 * CPL;
     extern __shared__ uint8_t smem_raw[];
@@ -237,7 +240,7 @@ topk_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         tma_prefetch_desc(&tmG);
         for (int s = 0; s < TK_STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
         mbar_init(q_full, 1);
-        for (int a = 0; a < 2; ++a) { mbar_init(&acc_full[a], 1); mbar_init(&acc_empty[a], 4); }
+        for (int a = 0; a < 2; ++a) { mbar_init(&acc_full[a], 1); mbar_init(&acc_empty[a], 8); }
         fence_mbar_init();
     }
     if (warp == 1) tmem_alloc(tmem_slot, 2 * TK_BN);
@@ -291,17 +294,32 @@ topk_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
         }
     } else {
         const int q = warp & 3;
+        const int half = (warp - 2) >> 2;                           // which half of a tile's columns this warp scans
         const int row = q * 32 + lane;                              // query row inside the tile = TMEM lane
         // query handled by this thread: tile row order, or (small batches) interleaved so all four warps get rows
         const long long qrow = (long long)qt * TK_BM + (p.scatter ? (lane * 4 + q) : row);
-        unsigned long long* rowptr = p.cand + ((size_t)sp * p.qtiles * TK_BM + (size_t)qt * TK_BM + row) * C;   // lists are indexed by tile row
-        unsigned long long* warp_rows = p.cand + ((size_t)sp * p.qtiles * TK_BM + (size_t)qt * TK_BM + q * 32) * C;
+        // lists are indexed by (scanner, tile row): [splits][qtiles][halves][128][C]
+        unsigned long long* warp_rows = p.cand + ((((size_t)sp * p.qtiles + qt) * p.halves + half) * TK_BM + q * 32) * C;
+        unsigned long long* rowptr = warp_rows + (size_t)lane * C;
+        if (half >= p.halves) {                                     // four-warp mode: the second set only keeps the barrier protocol going
+            for (int t = 0; t < tiles; ++t) {
+                const int as = t & 1; const uint32_t aph = (t >> 1) & 1;
+                if (!mbar_wait(&acc_full[as], aph, p.status, 15)) break;
+                tc_fence_after();
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&acc_empty[as]);
+            }
+        } else {
+        const int c_lo = p.halves == 2 ? half * (TK_BN / 64) : 0, c_hi = p.halves == 2 ? c_lo + TK_BN / 64 : TK_BN / 32;   // this warp's 32-column chunks
+        const int span = (c_hi - c_lo) * 32;                        // columns (= possible appends) per tile
         float tau = qrow < p.Q ? -INFINITY : INFINITY;      // padding rows of the last query tile never collect candidates
         int cnt = 0;
         bool ok = true;
         float rowmax = -INFINITY;                            // best score this split has seen for the row (share_max)
         for (int t = 0; t < tiles && ok; ++t) {
             const int as = t & 1; const uint32_t aph = (t >> 1) & 1;
+            const unsigned g_pre = qrow < p.Q ? __ldcg(p.gtau + qrow) : 0u;     // issued before the wait: the latency hides behind it
             if (!(ok = mbar_wait(&acc_full[as], aph, p.status, 14))) break;
             tc_fence_after();
             const long long n0 = n_lo + (long long)t * TK_BN;
@@ -314,15 +332,15 @@ topk_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
                 // against a bound that already sits near the 99.6th percentile.  If the wait times out the scan just appends more.
                 uint32_t v0[32];
 #pragma unroll 1
-                for (int c = 0; c < TK_BN / 32; ++c) {
+                for (int c = c_lo; c < c_hi; ++c) {
                     tmem_ld_32x32(tsrc + c * 32, v0);
                     tmem_ld_wait();
                     const long long lf = n_hi - (n0 + c * 32);
 #pragma unroll
                     for (int j = 0; j < 32; ++j) if (j < lf) rowmax = fmaxf(rowmax, __uint_as_float(v0[j]));
                 }
-                if (qrow < p.Q && rowmax > -INFINITY) __stcg(p.pubmax + (size_t)qrow * p.splits + sp, flip_f32(rowmax));
-                if (q == 0) {
+                if (qrow < p.Q && rowmax > -INFINITY) atomicMax(p.pubmax + (size_t)qrow * p.splits + sp, flip_f32(rowmax));
+                if (warp == 2) {
                     const int myq = sp % p.Q;
                     uint32_t kth = 0u;
 #pragma unroll 1
@@ -343,7 +361,7 @@ topk_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
             // k-th best from below, so nothing below it can reach the final top-k.  Scores EQUAL to it are kept (key - 1 = the next
             // float below): the index-ordered tie rule may still prefer them.  Without this every split warms up on its own.
             if (qrow < p.Q) {
-                unsigned g = __ldcg(p.gtau + qrow);
+                unsigned g = (p.share_max && t == 0) ? __ldcg(p.gtau + qrow) : g_pre;    // tile 0 has just waited for its bound
                 if (g > 1u) {
                     // the float just below the shared bound.  Below +0.0 that is the negative denormal, not -0.0 (key - 1), which
                     // compares EQUAL to +0.0 and would drop exact-zero scores (zero or padding rows) the tie rule may still prefer.
@@ -355,16 +373,20 @@ topk_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
             // A thread first reduces its 32 scores to their maximum: only if that beats tau (rare once the
             // threshold has settled) does it walk the chunk and append the survivors.
             const bool ragged = n_hi - n0 < TK_BN;                               // last tile of the gallery: columns past the end hold zeros
+            // Scan this warp's chunks of 32 scores; the TMEM load of chunk c+1 is in flight while chunk c is examined.
+            // A thread first reduces its 32 scores to their maximum: only if that beats tau (rare once the
+            // threshold has settled) does it walk the chunk and append the survivors.
             auto scan = [&](const uint32_t (&v)[32], int c) {
                 float mx = __uint_as_float(v[0]);
 #pragma unroll
                 for (int j = 1; j < 32; ++j) mx = fmaxf(mx, __uint_as_float(v[j]));
+                const long long nb = n0 + c * 32;
+                const long long left = n_hi - nb;                                 // < 32 only in the last tile of the gallery
                 if (p.share_max) {
                     if (!ragged) rowmax = fmaxf(rowmax, mx);
                     else {
-                        const long long lf = n_hi - (n0 + c * 32);
 #pragma unroll
-                        for (int j = 0; j < 32; ++j) if (j < lf) rowmax = fmaxf(rowmax, __uint_as_float(v[j]));
+                        for (int j = 0; j < 32; ++j) if (j < left) rowmax = fmaxf(rowmax, __uint_as_float(v[j]));
                     }
                 }
                 if (!__any_sync(0xffffffffu, mx > tau)) return;                   // nothing in this 32x32 block beats any row's threshold
@@ -373,8 +395,6 @@ topk_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
                 uint32_t mask = 0;
 #pragma unroll
                 for (int j = 0; j < 32; ++j) mask |= (__uint_as_float(v[j]) > tau ? 1u : 0u) << j;
-                const long long nb = n0 + c * 32;
-                const long long left = n_hi - nb;                                 // < 32 only in the last tile of the gallery
                 if (left < 32) mask = left <= 0 ? 0u : (mask & ((1u << (int)left) - 1u));
                 const uint32_t inv = 0xffffffffu - (uint32_t)nb;
                 while (mask) {
@@ -395,14 +415,14 @@ topk_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
                 }
             };
             uint32_t va[32], vb[32];
-            tmem_ld_32x32(tsrc, va);
+            tmem_ld_32x32(tsrc + c_lo * 32, va);
 #pragma unroll 1
-            for (int c = 0; c < TK_BN / 32; c += 2) {
+            for (int c = c_lo; c < c_hi; c += 2) {
                 tmem_ld_wait();
                 tmem_ld_32x32(tsrc + (c + 1) * 32, vb);
                 scan(va, c);
                 tmem_ld_wait();
-                if (c + 2 < TK_BN / 32) tmem_ld_32x32(tsrc + (c + 2) * 32, va);
+                if (c + 2 < c_hi) tmem_ld_32x32(tsrc + (c + 2) * 32, va);
                 scan(vb, c + 1);
             }
             tc_fence_before();
@@ -412,8 +432,8 @@ topk_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
                 // publish this split's best score per query, and turn everybody's maxima into a bound for ONE query per CTA and tile
                 // (query (sp + t) mod Q: with at least as many CTAs as queries every query is refreshed by somebody each round;
                 // the result reaches all CTAs through gtau).  One row's worth of work (~1 us) for the first epilogue warp.
-                if (qrow < p.Q && rowmax > -INFINITY) __stcg(p.pubmax + (size_t)qrow * p.splits + sp, flip_f32(rowmax));
-                if (q == 0 && (t < 4 || (t & 3) == 0)) {
+                if (qrow < p.Q && rowmax > -INFINITY) atomicMax(p.pubmax + (size_t)qrow * p.splits + sp, flip_f32(rowmax));
+                if (warp == 2 && (t < 4 || (t & 3) == 0)) {
                     const int myq = (sp + t) % p.Q;
                     const uint32_t kth = kth_published_max(p.pubmax + (size_t)myq * p.splits, p.splits, p.k, lane);
                     if (kth != 0u && lane == 0) atomicMax(p.gtau + myq, kth);
@@ -421,7 +441,7 @@ topk_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
             }
             // make room for the next tile (256 possible appends) while the MMAs of tile t+1 run: first drop what the shared bound
             // already rules out (one cheap pass), and only if the list is still too long select its k best
-            unsigned need = __ballot_sync(0xffffffffu, cnt + TK_BN > C);
+            unsigned need = __ballot_sync(0xffffffffu, cnt + span > C);
             while (need) {
                 const int src = __ffs(need) - 1;
                 need &= need - 1;
@@ -430,15 +450,15 @@ topk_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
                 const unsigned g = qs < p.Q ? __ldcg(p.gtau + qs) : 0u;
                 if (g > 1u) n = filter_row<CPL>(warp_rows + (size_t)src * C, n, g, lane);
                 float tnew = -INFINITY;
-                if (n + TK_BN > C) {
-                    n = compact_row<CPL>(warp_rows + (size_t)src * C, n, p.k, lane, false, C - TK_BN, &tnew, nullptr, nullptr, 0);
+                if (n + span > C) {
+                    n = compact_row<CPL>(warp_rows + (size_t)src * C, n, p.k, lane, false, C - span, &tnew, nullptr, nullptr, 0);
                     if (lane == src && qrow < p.Q) atomicMax(p.gtau + qrow, flip_f32(tnew));   // k rows of THIS split score >= tnew
                 }
                 if (lane == src) { cnt = n; tau = fmaxf(tau, tnew); }
             }
         }
         // final: every row sorted, best k written as (score, global index) for the merge kernel
-        const size_t cap = (size_t)p.splits * p.k;
+        const size_t cap = (size_t)p.splits * p.halves * p.k;
         for (int src = 0; src < 32; ++src) {
             int n = __shfl_sync(0xffffffffu, cnt, src);
             float tnew;
@@ -457,6 +477,7 @@ topk_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
                 }
             }
         }
+        }   // scanning warps
     }
     tc_fence_before();
     __syncthreads();
@@ -714,8 +735,13 @@ int topk_plan(int Q, long long N, int k, TopkPlan* plan) {
     // lists of 512 entries, or 1024 for k > 256 and in the maxima-sharing mode (one query tile, at least k splits): there the first
     // tiles are appended whole (no bound exists yet) and must fit until the shared bound arrives, two or three tiles in
     plan->cpl = (k <= 256 && !(plan->qtiles == 1 && plan->splits >= k)) ? 16 : 32;
-    plan->cand_bytes = (size_t)plan->splits * plan->qtiles * TK_BM * 32 * plan->cpl * 8;
-    plan->part_bytes = (((size_t)plan->splits * Q * k * 4 + 255) & ~(size_t)255) + (size_t)plan->splits * Q * k * 8;
+    // two scanners per row (eight epilogue warps) pay for batches of one query tile, where per-row bookkeeping dominates
+    // (Q = 64: 0.312 -> 0.299 ms on a 1.25 M-row shard); with several query tiles they measured neutral to slightly worse
+    static const int halves_env = [] { const char* e = getenv("B200_TOPK_HALVES"); return e ? atoi(e) : 0; }();
+    plan->halves = halves_env ? (halves_env == 1 ? 1 : 2) : (plan->qtiles == 1 ? 2 : 1);
+    const size_t parts = (size_t)plan->splits * plan->halves;
+    plan->cand_bytes = parts * plan->qtiles * TK_BM * 32 * plan->cpl * 8;
+    plan->part_bytes = ((parts * Q * k * 4 + 255) & ~(size_t)255) + parts * Q * k * 8;
     plan->part_bytes = ((plan->part_bytes + 255) & ~(size_t)255) + topk_shared_bytes(Q, plan->splits);     // the shared thresholds sit at the end
     plan->qstage_bytes = Q < TK_BM ? (size_t)TK_BM * 1024 * 2 : 0;      // staged, interleaved copy of a small query batch (D <= 1024)
     return B200_OK;
@@ -737,10 +763,10 @@ template <int CPL> static int launch_topk(const CUtensorMap& tq, const CUtensorM
         p.stages = std::min(TK_STAGES, (227 * 1024 - 256 - 1024 - q_bytes) / TK_B_BYTES);
         const int smem = q_bytes + p.stages * TK_B_BYTES + 256 + 1024;
         B200_CUDA_OK(cudaFuncSetAttribute(topk_tc_kernel<CPL, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        topk_tc_kernel<CPL, true><<<dim3(p.qtiles, p.splits), 192, smem, st>>>(tq, tg, p);
+        topk_tc_kernel<CPL, true><<<dim3(p.qtiles, p.splits), TK_THREADS, smem, st>>>(tq, tg, p);
     } else {
         B200_CUDA_OK(cudaFuncSetAttribute(topk_tc_kernel<CPL, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, TK_SMEM));
-        topk_tc_kernel<CPL, false><<<dim3(p.qtiles, p.splits), 192, TK_SMEM, st>>>(tq, tg, p);
+        topk_tc_kernel<CPL, false><<<dim3(p.qtiles, p.splits), TK_THREADS, TK_SMEM, st>>>(tq, tg, p);
     }
     B200_CUDA_OK(cudaGetLastError());
     return B200_OK;
@@ -771,7 +797,8 @@ int topk_run(const void* queries, const void* gallery, int Q, long long N, int D
     rc = make_tmap_2d(&tg, gallery, (uint64_t)N, D, (uint64_t)D * 2, TK_BN, true);
     if (rc) return rc;
     float* part_s = reinterpret_cast<float*>(sc + plan.cand_bytes);
-    long long* part_i = reinterpret_cast<long long*>(sc + plan.cand_bytes + (((size_t)plan.splits * Q * k * 4 + 255) & ~(size_t)255));
+    const int parts = plan.splits * plan.halves;
+    long long* part_i = reinterpret_cast<long long*>(sc + plan.cand_bytes + (((size_t)parts * Q * k * 4 + 255) & ~(size_t)255));
     unsigned* gtau = reinterpret_cast<unsigned*>(sc + plan.cand_bytes + plan.part_bytes - topk_shared_bytes(Q, plan.splits));
     int* pcount = reinterpret_cast<int*>(reinterpret_cast<uint8_t*>(gtau) + topk_gtau_bytes(Q));
     unsigned* pubmax = reinterpret_cast<unsigned*>(reinterpret_cast<uint8_t*>(gtau) + 2 * topk_gtau_bytes(Q));
@@ -779,11 +806,11 @@ int topk_run(const void* queries, const void* gallery, int Q, long long N, int D
     static const int share_on = [] { const char* e = getenv("B200_TOPK_SHAREMAX"); return e ? atoi(e) : 1; }();
     const int share_max = (share_on && plan.qtiles == 1 && plan.splits >= k && plan.splits <= 320) ? 1 : 0;
     TopkParams p{Q, D, k, N, plan.rows_per_split, plan.splits, plan.qtiles, reinterpret_cast<unsigned long long*>(sc),
-                 part_s, part_i, index_base, scatter, status, 0, gtau, pubmax, share_max, pcount};
+                 part_s, part_i, index_base, scatter, status, 0, gtau, pubmax, share_max, pcount, plan.halves};
     rc = plan.cpl == 16 ? launch_topk<16>(tq, tg, p, st) : launch_topk<32>(tq, tg, p, st);
     if (rc) return rc;
     // out_keys: exchange form for the sharded search, indices relative to this shard
-    return merge_launch<false>(part_s, part_i, nullptr, nullptr, plan.splits, Q, k, out_s, out_i, out_keys, index_base, st, pcount);
+    return merge_launch<false>(part_s, part_i, nullptr, nullptr, parts, Q, k, out_s, out_i, out_keys, index_base, st, pcount);
 }
 
 }  // namespace b200
@@ -825,6 +852,7 @@ extern "C" int b200clip_topk_static(const void* queries_f16_dev, int32_t Q, cons
     // Same work split as b200clip_topk, shrunk until candidate lists + per-split results fit the fixed array.
     TopkPlan plan;
     plan.cpl = 16;
+    plan.halves = 1;                          // four scanning warps: half the list memory of the handle path, so the array holds twice the queries
     plan.qtiles = (Q + TK_BM - 1) / TK_BM;
     const long long ntiles = (N + TK_BN - 1) / TK_BN;
     const size_t budget = kStaticScratchBytes - 256;

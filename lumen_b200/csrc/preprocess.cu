@@ -114,6 +114,12 @@ __device__ __forceinline__ void store8(const PreParams& p, bool vec8, size_t idx
 }
 
 __device__ __forceinline__ uint32_t byte_of(uint32_t w, int i) { return __byte_perm(w, 0, 0x4440 | i); }
+// four unsigned bytes of a times four SIGNED bytes of b, accumulated into c
+__device__ __forceinline__ int dp4a_us(uint32_t a, uint32_t b, int c) {
+    int d;
+    asm("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
+    return d;
+}
 
 // NW+1 aligned 32-bit words starting at the word that holds `p` -> NW words whose byte 0 is *p (little endian).
 template <int NW>
@@ -144,20 +150,44 @@ __device__ __forceinline__ void hpass_chunk(const ImgDesc& d, const uint8_t* __r
         const uint8_t* px0 = rows + xmin * 3;
         uint8_t* o = inter_rows + x * 3;
         if (KMAX > 0) {
-            constexpr int NW = (3 * (KMAX > 0 ? KMAX : 1) + 3) / 4;
-            int w[KMAX > 0 ? KMAX : 1];
+            // Exact 22-bit coefficients on the byte dot-product unit: w = l0 + 256 l1 + 65536 l2 with l0, l1 the low two bytes
+            // (unsigned) and l2 = w >> 16 (signed, |l2| < 128 for normalised cubic weights), four taps per register and limb.
+            // Per four taps and channel: two PRMT gather the channel's four bytes out of three source words, three DP4A
+            // accumulate the limbs - 15 instructions per 12 multiply-adds where IMAD + PRMT per byte took 24.  Still integer
+            // arithmetic end to end, so the bit-exactness tests against Pillow keep guarding it.
+            constexpr int G = KMAX > 0 ? KMAX / 4 : 1;    // tap groups (KMAX is a multiple of 4)
+            constexpr int NW = 3 * G;                     // source words per row: 12 bytes per tap group
+            uint32_t L0[G], L1[G], L2[G];
 #pragma unroll
-            for (int t = 0; t < KMAX; ++t) w[t] = t < cnt ? __ldg(k + t) : 0;
+            for (int g = 0; g < G; ++g) {
+                L0[g] = L1[g] = L2[g] = 0u;
+#pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const int t = 4 * g + i;
+                    const int wt = t < cnt ? __ldg(k + t) : 0;
+                    L0[g] |= ((uint32_t)wt & 255u) << (8 * i);
+                    L1[g] |= (((uint32_t)wt >> 8) & 255u) << (8 * i);
+                    L2[g] |= (((uint32_t)(wt >> 16)) & 255u) << (8 * i);
+                }
+            }
             for (int r = 0; r < nr; ++r) {
                 uint32_t al[NW];
                 load_bytes_aligned<NW>(px0 + r * rowbytes, al);
-                int a0 = 1 << (PRECISION_BITS - 1), a1 = a0, a2 = a0;
+                uint32_t lo0 = 0, lo1 = 0, lo2 = 0, mi0 = 0, mi1 = 0, mi2 = 0;
+                int hi0 = 0, hi1 = 0, hi2 = 0;
 #pragma unroll
-                for (int t = 0; t < KMAX; ++t) {
-                    a0 += (int)byte_of(al[(3 * t) >> 2], (3 * t) & 3) * w[t];
-                    a1 += (int)byte_of(al[(3 * t + 1) >> 2], (3 * t + 1) & 3) * w[t];
-                    a2 += (int)byte_of(al[(3 * t + 2) >> 2], (3 * t + 2) & 3) * w[t];
+                for (int g = 0; g < G; ++g) {
+                    const uint32_t w0 = al[3 * g], w1 = al[3 * g + 1], w2 = al[3 * g + 2];
+                    const uint32_t r4 = __byte_perm(__byte_perm(w0, w1, 0x0630), w2, 0x5210);   // bytes 0, 3, 6, 9 of the 12
+                    const uint32_t g4 = __byte_perm(__byte_perm(w0, w1, 0x0741), w2, 0x6210);   // bytes 1, 4, 7, 10
+                    const uint32_t b4 = __byte_perm(__byte_perm(w0, w1, 0x0052), w2, 0x7410);   // bytes 2, 5, 8, 11
+                    lo0 = __dp4a(r4, L0[g], lo0); mi0 = __dp4a(r4, L1[g], mi0); hi0 = dp4a_us(r4, L2[g], hi0);
+                    lo1 = __dp4a(g4, L0[g], lo1); mi1 = __dp4a(g4, L1[g], mi1); hi1 = dp4a_us(g4, L2[g], hi1);
+                    lo2 = __dp4a(b4, L0[g], lo2); mi2 = __dp4a(b4, L1[g], mi2); hi2 = dp4a_us(b4, L2[g], hi2);
                 }
+                const int a0 = (1 << (PRECISION_BITS - 1)) + (int)lo0 + (int)(mi0 << 8) + (hi0 << 16);
+                const int a1 = (1 << (PRECISION_BITS - 1)) + (int)lo1 + (int)(mi1 << 8) + (hi1 << 16);
+                const int a2 = (1 << (PRECISION_BITS - 1)) + (int)lo2 + (int)(mi2 << 8) + (hi2 << 16);
                 o[0] = (uint8_t)clip8(a0); o[1] = (uint8_t)clip8(a1); o[2] = (uint8_t)clip8(a2);
                 o += inter_pitch;
             }
@@ -274,6 +304,10 @@ __global__ void pull_desc_kernel(const uint4* __restrict__ host, uint4* __restri
 // Identity-size images (resized size == source size, e.g. 224x224 sources for a 224 model): crop + convert only.
 // Persistent CTAs walk (image, row-tile) items; the next item's rows are fetched with cp.async while the current
 // ones are converted, so the kernel streams at memory speed instead of paying one load latency per tile.
+// The descriptor of an item (image geometry, 80 bytes in global memory) is needed before its rows can be requested; read on the spot
+// it put one L2 round trip in front of every cp.async batch and another in front of every conversion (ncu: long-scoreboard stalls on
+// exactly those loads).  So descriptors run two items ahead in registers.
+struct ItemDesc { long long src_off; int w_in, top, left, identity; };
 template <bool BF16>
 __global__ void __launch_bounds__(256, 4) convert_kernel(PreParams p, int B, int tiles) {
     extern __shared__ __align__(16) uint8_t sm[];
@@ -284,9 +318,16 @@ __global__ void __launch_bounds__(256, 4) convert_kernel(PreParams p, int B, int
     const bool vec8 = p.layout == 0 || (p.P & 7) == 0;
     const int wid = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int total = B * tiles;
-    auto fetch = [&](int item, int buf) -> int {               // returns the byte offset of the first row inside the buffer
-        const int b = item / tiles, y0 = (item - b * tiles) * p.TR;
-        const ImgDesc& d = p.desc[b];
+    auto load_desc = [&](int item) -> ItemDesc {
+        ItemDesc r{0, 0, 0, 0, 0};
+        if (item < total) {
+            const ImgDesc& d = p.desc[item / tiles];
+            r.src_off = d.src_off; r.w_in = d.w_in; r.top = d.top; r.left = d.left; r.identity = d.identity;
+        }
+        return r;
+    };
+    auto fetch = [&](int item, const ItemDesc& d, int buf) -> int {   // returns the byte offset of the first row inside the buffer
+        const int y0 = (item % tiles) * p.TR;
         int prefix = 0;
         if (d.identity == 1) {
             const int rowbytes = d.w_in * 3, nr = min(S, y0 + p.TR) - y0;
@@ -297,17 +338,19 @@ __global__ void __launch_bounds__(256, 4) convert_kernel(PreParams p, int B, int
     };
     int item = blockIdx.x, it = 0;
     if (item >= total) return;
-    int prefix = fetch(item, 0);
+    ItemDesc dc = load_desc(item);
+    int prefix = fetch(item, dc, 0);
+    ItemDesc dn = load_desc(item + gridDim.x);
     for (; item < total; item += gridDim.x, ++it) {
         const int next = item + gridDim.x;
+        const ItemDesc dnn = load_desc(next + gridDim.x);          // consumed one iteration from now
         int prefix_next = 0;
-        if (next < total) { prefix_next = fetch(next, (it + 1) & 1); cp_async_wait<1>(); } else cp_async_wait<0>();
+        if (next < total) { prefix_next = fetch(next, dn, (it + 1) & 1); cp_async_wait<1>(); } else cp_async_wait<0>();
         __syncthreads();
         const int b = item / tiles, y0 = (item - b * tiles) * p.TR;
-        const ImgDesc& d = p.desc[b];
-        if (d.identity == 1) {
-            const int rowbytes = d.w_in * 3, nr = min(S, y0 + p.TR) - y0;
-            const uint8_t* base = stage + (it & 1) * p.stage_bytes + prefix + d.left * 3;
+        if (dc.identity == 1) {
+            const int rowbytes = dc.w_in * 3, nr = min(S, y0 + p.TR) - y0;
+            const uint8_t* base = stage + (it & 1) * p.stage_bytes + prefix + dc.left * 3;
             for (int r = wid; r < nr; r += 8)
                 for (int xv = lane; xv < xvecs; xv += 32) {
                     uint32_t al[6];
@@ -324,7 +367,7 @@ __global__ void __launch_bounds__(256, 4) convert_kernel(PreParams p, int B, int
                 }
         }
         __syncthreads();
-        prefix = prefix_next;
+        prefix = prefix_next; dc = dn; dn = dnn;
     }
 }
 
@@ -570,7 +613,7 @@ int preprocess_run(PreprocessState* s, const uint8_t* src_dev, const long long* 
     if (max_ident_rowbytes > 0) {
         // identity images: TR rows per item, one staging buffer per item (double buffered)
         int TR = 16;
-        while (TR > 1 && (size_t)TR * max_ident_rowbytes + 48 > 48 * 1024) TR /= 2;
+        while (TR > 1 && (size_t)TR * max_ident_rowbytes + 48 > 24 * 1024) TR /= 2;      // two buffers per CTA, four CTAs per SM
         const int ident_stage = (TR * max_ident_rowbytes + 48 + 15) & ~15;
         B200_REQUIRE(ident_stage <= 96 * 1024, "preprocess: source rows too wide");
         const size_t smem = 3072 + 2 * (size_t)ident_stage;

@@ -94,7 +94,9 @@ __device__ __forceinline__ void store8(const PreParams& p, bool vec8, size_t idx
         } else {
 #pragma unroll
             for (int i = 0; i < 8; i += 2) {
-                int cs; const size_t e = out_index(p, b, y, x + i, cs) + (size_t)c * cs;
+                int cs;
+                size_t e = out_index(p, b, y, x + i, cs);
+                e += (size_t)c * cs;
                 *reinterpret_cast<__nv_bfloat162*>(o + e) = __floats2bfloat162_rn(f[i], f[i + 1]);
             }
         }
@@ -106,7 +108,9 @@ __device__ __forceinline__ void store8(const PreParams& p, bool vec8, size_t idx
         } else {
 #pragma unroll
             for (int i = 0; i < 8; i += 2) {
-                int cs; const size_t e = out_index(p, b, y, x + i, cs) + (size_t)c * cs;
+                int cs;
+                size_t e = out_index(p, b, y, x + i, cs);
+                e += (size_t)c * cs;
                 *reinterpret_cast<float2*>(o + e) = make_float2(f[i], f[i + 1]);
             }
         }

@@ -68,13 +68,19 @@ def measured_gemm_traffic():
 
 
 def gemm_flops_per_image(cfg: dict) -> float:
+    """FLOPs the GEMM kernels EXECUTE per image (the roofline of the dominant kernel is computed from what it did): K is padded
+    to 64 in the patch embedding, and the last layer computes keys / values for every token but everything else for the CLS
+    row only (lumen_b200/csrc/api.cu:encode_chunk; B200_CLS_LAST=0 turns that off)."""
     n = (cfg["image_size"] // cfg["patch"]) ** 2
     S, d, L, mlp, D, P = n + 1, cfg["width"], cfg["layers"], cfg["mlp_dim"], cfg["embed_dim"], cfg["patch"]
     kpad = (3 * P * P + 63) // 64 * 64
-    return 2.0 * n * kpad * d + L * (2.0 * S * d * 3 * d + 2.0 * S * d * d + 4.0 * S * d * mlp) + 2.0 * d * D
+    layer = 2.0 * S * d * 3 * d + 2.0 * S * d * d + 4.0 * S * d * mlp
+    last = layer if os.environ.get("B200_CLS_LAST", "1") == "0" else 2.0 * S * d * 2 * d + 2.0 * d * d + 2.0 * d * d + 4.0 * d * mlp
+    return 2.0 * n * kpad * d + (L - 1) * layer + last + 2.0 * d * D
 
 
 def total_flops_per_image(cfg: dict) -> float:
+    """ALGORITHMIC FLOPs per image of the full tower (8.8176 G for ViT-B/32), whatever shortcut the kernels take."""
     n = (cfg["image_size"] // cfg["patch"]) ** 2
     S, d, L, mlp, D, P = n + 1, cfg["width"], cfg["layers"], cfg["mlp_dim"], cfg["embed_dim"], cfg["patch"]
     return 2.0 * n * 3 * P * P * d + L * (2.0 * S * d * 3 * d + 4.0 * S * S * d + 2.0 * S * d * d + 4.0 * S * d * mlp) + 2.0 * d * D

@@ -22,6 +22,8 @@ int launch_layernorm(const float* x, long long row_stride, const float* g, const
 int launch_embed_preln(const float* patch, const float* cls, const float* pos, const float* g, const float* b, float* xres,
                        int B, int S, int d, float eps, cudaStream_t st);
 int launch_l2_normalize(const float* in, float* out, int rows, int D, cudaStream_t st);
+// last layer: one query (the CLS row) per (image, head) against all keys / values of the image
+int launch_cls_attention(const void* q_cls_bf16, const void* qkv_bf16, void* out_bf16, int B, int S, int d, int heads, cudaStream_t st);
 int launch_text_embed(const int* ids, const float* tok, const float* pos, float* x, int rows, int ctx, int d, int vocab, cudaStream_t st);
 int launch_text_eot_gather(const int* ids, const float* x, float* out, int B, int ctx, int d, cudaStream_t st);
 int launch_gallery_pack(const float* in, void* out_f16, long long rows, int D, int normalize, cudaStream_t st);

@@ -167,7 +167,77 @@ __global__ void __launch_bounds__(256) gallery_pack_kernel(const float* __restri
     }
 }
 
+// ------------------------------------------------------------------------------------------ last layer: CLS query only
+// The tower's output is the projection of the CLS token's final hidden state (modeling_clip.py:684-694: pooled_output =
+// last_hidden_state[:, 0]), so in the LAST transformer layer only the CLS row of every image is ever read again: its attention
+// needs the keys and values of all tokens but a single query per (image, head).  One warp per (image, head):
+//   scores   eight lanes per key (16 bytes = 8 dims each), four keys per step, partial dots reduced inside the lane group;
+//   softmax  over the warp's score array in shared memory, fp32, max-subtracted like the full kernels;
+//   output   lanes over the 64 head dims (2 each), one 128-byte V row per key.
+// q: bf16 [B, d] (CLS rows only), qkv: bf16 [B*S, 3d] of which only the K and V columns are read, out: bf16 [B, d].
+__global__ void __launch_bounds__(256) cls_attention_kernel(const __nv_bfloat16* __restrict__ q, const __nv_bfloat16* __restrict__ qkv,
+                                                            __nv_bfloat16* __restrict__ out, int B, int S, int d, int heads) {
+    pdl_wait();
+    pdl_trigger();
+    extern __shared__ float cls_sc[];                       // [8 warps][S]
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const long long item = (long long)blockIdx.x * 8 + warp;
+    if (item >= (long long)B * heads) return;
+    const int b = (int)(item / heads), h = (int)(item % heads);
+    float* sc = cls_sc + (size_t)warp * S;
+    const int g = lane >> 3, c = lane & 7;
+    float qv[8];
+    {
+        const uint4 w = *reinterpret_cast<const uint4*>(q + (size_t)b * d + h * 64 + c * 8);
+        const __nv_bfloat162* w2 = reinterpret_cast<const __nv_bfloat162*>(&w);
+#pragma unroll
+        for (int i = 0; i < 4; ++i) { const float2 f = __bfloat1622float2(w2[i]); qv[2 * i] = f.x; qv[2 * i + 1] = f.y; }
+    }
+    const __nv_bfloat16* kbase = qkv + (size_t)b * S * 3 * d + d + h * 64;
+    const __nv_bfloat16* vbase = kbase + d;
+    float mx = -INFINITY;
+    for (int jb = 0; jb < S; jb += 4) {
+        const int j = jb + g;
+        float part = 0.f;
+        if (j < S) {
+            const uint4 w = *reinterpret_cast<const uint4*>(kbase + (size_t)j * 3 * d + c * 8);
+            const __nv_bfloat162* w2 = reinterpret_cast<const __nv_bfloat162*>(&w);
+#pragma unroll
+            for (int i = 0; i < 4; ++i) { const float2 f = __bfloat1622float2(w2[i]); part = fmaf(qv[2 * i], f.x, part); part = fmaf(qv[2 * i + 1], f.y, part); }
+        }
+        part += __shfl_xor_sync(0xffffffffu, part, 1);
+        part += __shfl_xor_sync(0xffffffffu, part, 2);
+        part += __shfl_xor_sync(0xffffffffu, part, 4);
+        part *= 0.125f;
+        if (j < S) { if (c == 0) sc[j] = part; mx = fmaxf(mx, part); }
+    }
+    mx = warp_max(mx);
+    __syncwarp();
+    float sum = 0.f;
+    for (int j = lane; j < S; j += 32) { const float e = __expf(sc[j] - mx); sc[j] = e; sum += e; }
+    sum = warp_sum(sum);
+    __syncwarp();
+    float o0 = 0.f, o1 = 0.f;
+    for (int j = 0; j < S; ++j) {
+        const float pj = sc[j];
+        const float2 v = __bfloat1622float2(*reinterpret_cast<const __nv_bfloat162*>(vbase + (size_t)j * 3 * d + 2 * lane));
+        o0 = fmaf(pj, v.x, o0); o1 = fmaf(pj, v.y, o1);
+    }
+    const float inv = 1.f / sum;
+    *reinterpret_cast<__nv_bfloat162*>(out + (size_t)b * d + h * 64 + 2 * lane) = __floats2bfloat162_rn(o0 * inv, o1 * inv);
+}
+
 // ------------------------------------------------------------------------------------------ launchers
+int launch_cls_attention(const void* q, const void* qkv, void* out, int B, int S, int d, int heads, cudaStream_t st) {
+    B200_REQUIRE(d == heads * 64 && B > 0 && S > 0, "cls_attention: head_dim must be 64");
+    const size_t smem = (size_t)8 * S * sizeof(float);
+    B200_REQUIRE(smem <= 48 * 1024, "cls_attention: sequence too long");
+    const long long items = (long long)B * heads;
+    B200_CUDA_OK(launch_pdl(cls_attention_kernel, dim3((unsigned)((items + 7) / 8)), dim3(256), smem, st, reinterpret_cast<const __nv_bfloat16*>(q),
+                            reinterpret_cast<const __nv_bfloat16*>(qkv), reinterpret_cast<__nv_bfloat16*>(out), B, S, d, heads));
+    B200_CUDA_OK(cudaGetLastError());
+    return B200_OK;
+}
 int launch_layernorm(const float* x, long long row_stride, const float* g, const float* b, void* out, int rows, int d, float eps, cudaStream_t st) {
     B200_REQUIRE(d % 128 == 0 && d <= 128 * LN_MAX_V4, "layernorm: width must be a multiple of 128, at most 1024");
     B200_CUDA_OK(launch_pdl(layernorm_bf16_kernel, dim3((rows + 7) / 8), dim3(256), 0, st, x, row_stride, g, b, reinterpret_cast<__nv_bfloat16*>(out), rows, d, eps));

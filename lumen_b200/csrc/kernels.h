@@ -32,7 +32,7 @@ int launch_gallery_pack(const float* in, void* out_f16, long long rows, int D, i
 int launch_attention_short(const void* qkv, void* out, int B, int S, int d, int heads, DeviceStatus* status, cudaStream_t st);
 int launch_attention_auto(const void* qkv, void* out, int B, int S, int d, int heads, int causal, DeviceStatus* status, cudaStream_t st);
 int launch_attention_tc(const void* qkv, void* out, int B, int S, int d, int heads, int causal, DeviceStatus* status, cudaStream_t st);
-struct TopkPlan { int splits, qtiles, cpl, halves; long long rows_per_split; size_t cand_bytes, part_bytes, qstage_bytes; };
+struct TopkPlan { int splits, qtiles, cpl, halves, room; long long rows_per_split; size_t cand_bytes, part_bytes, qstage_bytes; };
 int topk_plan(int Q, long long N, int k, TopkPlan* plan);
 int topk_run(const void* queries, const void* gallery, int Q, long long N, int D, int k, long long index_base, void* scratch,
              const TopkPlan& plan, float* out_s, long long* out_i, DeviceStatus* status, cudaStream_t st,

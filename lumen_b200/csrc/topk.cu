@@ -43,6 +43,7 @@ struct TopkParams {
     unsigned* pubmax;            // [Q][splits] best score each split has seen so far for the query (flip_f32 key, 0 = nothing yet)
     int share_max;               // splits >= k: the k-th largest of the published maxima bounds the global k-th best (see kth_published_max)
     int* pcount;                 // [Q] candidates the splits have written for the query
+    int room;                    // slots every (split, half) may use in a query's candidate slice (>= k)
     int halves;                  // 2: eight epilogue warps, each lane quarter served by two warps that scan one half of a tile's columns
                                  // each and keep their own candidate lists (two independent scanners per row); 1: four warps
 };
@@ -457,25 +458,95 @@ topk_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
                 if (lane == src) { cnt = n; tau = fmaxf(tau, tnew); }
             }
         }
-        // final: every row sorted, best k written as (score, global index) for the merge kernel
-        const size_t cap = (size_t)p.splits * p.halves * p.k;
-        for (int src = 0; src < 32; ++src) {
-            int n = __shfl_sync(0xffffffffu, cnt, src);
-            float tnew;
-            const long long qr = (long long)qt * TK_BM + (p.scatter ? src * 4 + q : q * 32 + src);
-            if (qr < p.Q) {     // warp-uniform
-                // what the shared bound rules out needs no selecting: with the maxima-based bound a split is usually left with a
-                // handful of candidates, fewer than k, which compact_row then just writes out
-                const unsigned g = __ldcg(p.gtau + qr);
-                if (g > 1u && n > 0) n = filter_row<CPL>(warp_rows + (size_t)src * C, n, g, lane);
-                if (n > 0) {
-                    int base = 0;
-                    if (lane == 0) base = atomicAdd(p.pcount + qr, min(n, p.k));      // this split's slice of the query's candidate list
-                    base = __shfl_sync(0xffffffffu, base, 0);
-                    compact_row<CPL>(warp_rows + (size_t)src * C, n, p.k, lane, true, C, &tnew, p.part_scores + (size_t)qr * cap + base,
-                                     p.part_idx + (size_t)qr * cap + base, p.index_base, /*pad*/ false);
+        // final: what is left of every row's list goes to the query's candidate slice for the merge kernel, as (score, global index).
+        // One LANE per row: the shared bound usually leaves fewer than k entries, which need no selecting - and done one row at a
+        // time by the whole warp this stage was a chain of 32 x (load, atomic, load, store) round trips to L2, ~8 us each, ~250 us
+        // per CTA during which its SM issued no MMA (a tenth of a Q = 4096 search over 1.25 M rows).
+        const size_t cap = (size_t)p.splits * p.halves * p.room;
+        const bool live = qrow < p.Q;
+        int m = 0;
+        if (p.room > p.k) {
+            // several query tiles: the lists go to the merge kernel whole, no filtering (the shared bound is one split's own k-th
+            // best here and removes little).  Warp-wide copy, two rows per step and up to sixteen loads in flight per lane.
+            m = cnt;
+            const bool direct = live && cnt > 0 && cnt <= p.room;
+            int base = 0;
+            if (direct) base = atomicAdd(p.pcount + qrow, cnt);                       // this split's part of the query's candidate slice
+            const unsigned todo = __ballot_sync(0xffffffffu, direct);
+#pragma unroll 1
+            for (int r0 = 0; r0 < 32; r0 += 2) {
+                int n[2]; long long qr[2]; int bs[2];
+#pragma unroll
+                for (int x = 0; x < 2; ++x) {
+                    n[x] = ((todo >> (r0 + x)) & 1u) ? __shfl_sync(0xffffffffu, cnt, r0 + x) : 0;
+                    qr[x] = __shfl_sync(0xffffffffu, qrow, r0 + x);
+                    bs[x] = __shfl_sync(0xffffffffu, base, r0 + x);
+                }
+#pragma unroll 1
+                for (int e0 = 0; e0 < max(n[0], n[1]); e0 += 256) {
+                    unsigned long long key[2][8];
+#pragma unroll
+                    for (int x = 0; x < 2; ++x)
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            const int e = e0 + i * 32 + lane;
+                            key[x][i] = e < n[x] ? __ldcg(warp_rows + (size_t)(r0 + x) * C + e) : 0ull;
+                        }
+#pragma unroll
+                    for (int x = 0; x < 2; ++x)
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) {
+                            const int e = e0 + i * 32 + lane;
+                            if (e < n[x]) {
+                                p.part_scores[(size_t)qr[x] * cap + bs[x] + e] = unflip_f32((uint32_t)(key[x][i] >> 32));
+                                p.part_idx[(size_t)qr[x] * cap + bs[x] + e] = p.index_base + (long long)(0xffffffffu - (uint32_t)key[x][i]);
+                            }
+                        }
                 }
             }
+        } else if (live) {
+            const unsigned g = __ldcg(p.gtau + qrow);
+            const uint32_t thr = g > 1u ? g : 0u;
+#pragma unroll 1
+            for (int e = 0; e < cnt; e += 8) {
+                unsigned long long key[8];
+#pragma unroll
+                for (int j = 0; j < 8; ++j) key[j] = e + j < cnt ? __ldcg(rowptr + e + j) : 0ull;
+#pragma unroll
+                for (int j = 0; j < 8; ++j)
+                    if (key[j] != 0ull && (uint32_t)(key[j] >> 32) >= thr) __stcg(rowptr + m++, key[j]);     // m <= e + j: never ahead of the reads
+            }
+            if (m > 0 && m <= p.room) {
+                const int base = atomicAdd(p.pcount + qrow, m);                       // this split's slice of the query's candidate list
+                float* ps = p.part_scores + (size_t)qrow * cap + base;
+                long long* pi = p.part_idx + (size_t)qrow * cap + base;
+#pragma unroll 1
+                for (int e = 0; e < m; e += 4) {
+                    unsigned long long key[4];
+#pragma unroll
+                    for (int j = 0; j < 4; ++j) key[j] = e + j < m ? __ldcg(rowptr + e + j) : 0ull;
+#pragma unroll
+                    for (int j = 0; j < 4; ++j)
+                        if (e + j < m) { ps[e + j] = unflip_f32((uint32_t)(key[j] >> 32)); pi[e + j] = p.index_base + (long long)(0xffffffffu - (uint32_t)key[j]); }
+                }
+            }
+        }
+        __syncwarp();
+        // rows longer than their share of the slice (rare: the list was close to full when the scan ended): the warp selects the k
+        // best, one row at a time.  Everything shorter goes to the merge kernel as it is - selecting k out of ~200 here, row after
+        // row, only to have the merge select again cost every CTA ~200 us at its end.
+        unsigned big = __ballot_sync(0xffffffffu, live && m > p.room);
+        while (big) {
+            const int src = __ffs(big) - 1;
+            big &= big - 1;
+            const int n = __shfl_sync(0xffffffffu, m, src);
+            const long long qr = __shfl_sync(0xffffffffu, qrow, src);
+            int base = 0;
+            if (lane == 0) base = atomicAdd(p.pcount + qr, p.k);
+            base = __shfl_sync(0xffffffffu, base, 0);
+            float tnew;
+            compact_row<CPL>(warp_rows + (size_t)src * C, n, p.k, lane, true, C, &tnew, p.part_scores + (size_t)qr * cap + base,
+                             p.part_idx + (size_t)qr * cap + base, p.index_base, /*pad*/ false);
         }
         }   // scanning warps
     }
@@ -537,20 +608,21 @@ __device__ __forceinline__ void scan_hist(const int* hist, int kk, bool hi_first
 template <int NT, bool KEYS_IN>
 __global__ void __launch_bounds__(NT) merge_topk_kernel(const float* __restrict__ ps, const long long* __restrict__ pi,
                                                                    const unsigned long long* __restrict__ pkeys, const long long* __restrict__ bases, int P,
-                                                                   int Q, int k, int cache_keys, float* __restrict__ out_s,
+                                                                   int Q, int k, int cache_cap, float* __restrict__ out_s,
                                                                    long long* __restrict__ out_i, unsigned long long* __restrict__ out_keys, long long key_base,
-                                                                   const int* __restrict__ counts) {
+                                                                   const int* __restrict__ counts, int slot) {
     extern __shared__ __align__(16) uint32_t key_cache[];     // [T] order-preserving score keys (0 = empty slot) when cache_keys
     __shared__ int hist[256];
     __shared__ int sh_digit, sh_before, sh_total, sh_count, sh_gt, sh_eq;
     __shared__ float ss[MERGE_KMAX];
     __shared__ long long si[MERGE_KMAX];
-    // counts != nullptr: the query's candidates are one list of counts[qi] entries at [qi][P * k] (what topk_tc_kernel writes);
+    // counts != nullptr: the query's candidates are one list of counts[qi] entries at [qi][slot] (what topk_tc_kernel writes);
     // otherwise P parts of k slots each, [P][Q][k], empty slots marked by a negative index (the public merge entry point)
     const int qi = blockIdx.x, tid = threadIdx.x;
-    const int T = counts != nullptr ? min(counts[qi], P * k) : P * k;
+    const int T = counts != nullptr ? min(counts[qi], slot) : P * k;
+    const bool cache_keys = T <= cache_cap;                    // the keys fit in the shared memory this launch was given
     auto offset = [&](int e) -> size_t {
-        if (counts != nullptr) return (size_t)qi * P * k + e;
+        if (counts != nullptr) return (size_t)qi * slot + e;
         const int part = e / k;
         return ((size_t)part * Q + qi) * k + (e - part * k);
     };
@@ -687,20 +759,24 @@ __global__ void __launch_bounds__(NT) merge_topk_kernel(const float* __restrict_
 
 template <bool KEYS_IN>
 static int merge_launch(const float* ps, const long long* pi, const unsigned long long* pkeys, const long long* bases, int P, int Q, int k,
-                        float* out_s, long long* out_i, unsigned long long* out_keys, long long key_base, cudaStream_t st, const int* counts = nullptr) {
+                        float* out_s, long long* out_i, unsigned long long* out_keys, long long key_base, cudaStream_t st, const int* counts = nullptr,
+                        int slot = 0) {
     B200_REQUIRE(P > 0 && k > 0, "merge_topk: need at least one part and k > 0");
     B200_REQUIRE(k <= MERGE_KMAX, "merge_topk: k larger than 1024 is not supported");
     B200_REQUIRE((long long)P * k < (1LL << 30), "merge_topk: too many candidates per query");
     if (Q == 0) return B200_OK;
-    const size_t T = (size_t)P * k;
-    const int cache = T * 4 <= 160 * 1024;                 // keys fit in shared memory next to the sort buffers
-    const size_t smem = cache ? T * 4 : 0;
+    const size_t T = counts != nullptr ? (size_t)slot : (size_t)P * k;     // most candidates a query can have
+    B200_REQUIRE(T < (1u << 30), "merge_topk: too many candidates per query");
+    // keys are cached in shared memory (next to the sort buffers) when a query's candidates fit; a list of counts[] entries is
+    // usually far shorter than its slice, so the kernel decides per query
+    const int cache = (int)std::min<size_t>(T, 40 * 1024);
+    const size_t smem = (size_t)cache * 4;
     if (Q <= 2 * kNumSMs) {
         if (smem > 32 * 1024) B200_CUDA_OK(cudaFuncSetAttribute(merge_topk_kernel<1024, KEYS_IN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        merge_topk_kernel<1024, KEYS_IN><<<Q, 1024, smem, st>>>(ps, pi, pkeys, bases, P, Q, k, cache, out_s, out_i, out_keys, key_base, counts);
+        merge_topk_kernel<1024, KEYS_IN><<<Q, 1024, smem, st>>>(ps, pi, pkeys, bases, P, Q, k, cache, out_s, out_i, out_keys, key_base, counts, slot);
     } else {
         if (smem > 32 * 1024) B200_CUDA_OK(cudaFuncSetAttribute(merge_topk_kernel<256, KEYS_IN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        merge_topk_kernel<256, KEYS_IN><<<Q, 256, smem, st>>>(ps, pi, pkeys, bases, P, Q, k, cache, out_s, out_i, out_keys, key_base, counts);
+        merge_topk_kernel<256, KEYS_IN><<<Q, 256, smem, st>>>(ps, pi, pkeys, bases, P, Q, k, cache, out_s, out_i, out_keys, key_base, counts, slot);
     }
     B200_CUDA_OK(cudaGetLastError());
     return B200_OK;
@@ -740,8 +816,13 @@ int topk_plan(int Q, long long N, int k, TopkPlan* plan) {
     static const int halves_env = [] { const char* e = getenv("B200_TOPK_HALVES"); return e ? atoi(e) : 0; }();
     plan->halves = halves_env ? (halves_env == 1 ? 1 : 2) : (plan->qtiles == 1 ? 2 : 1);
     const size_t parts = (size_t)plan->splits * plan->halves;
+    // a scanner hands its whole list to the merge kernel when it holds at most `room` entries (a list is compacted as soon as it
+    // cannot take another tile, so it ends a scan with at most C - span + span entries, and nearly always far fewer)
+    const int C = 32 * plan->cpl, span = TK_BN / plan->halves;
+    // Only with several query tiles: a single tile runs with the maxima-sharing bound, which leaves a scanner a handful of entries.
+    plan->room = plan->qtiles > 1 ? std::max(k, std::min(C, C - span + 64)) : k;
     plan->cand_bytes = parts * plan->qtiles * TK_BM * 32 * plan->cpl * 8;
-    plan->part_bytes = ((parts * Q * k * 4 + 255) & ~(size_t)255) + parts * Q * k * 8;
+    plan->part_bytes = ((parts * Q * plan->room * 4 + 255) & ~(size_t)255) + parts * Q * plan->room * 8;
     plan->part_bytes = ((plan->part_bytes + 255) & ~(size_t)255) + topk_shared_bytes(Q, plan->splits);     // the shared thresholds sit at the end
     plan->qstage_bytes = Q < TK_BM ? (size_t)TK_BM * 1024 * 2 : 0;      // staged, interleaved copy of a small query batch (D <= 1024)
     return B200_OK;
@@ -798,7 +879,7 @@ int topk_run(const void* queries, const void* gallery, int Q, long long N, int D
     if (rc) return rc;
     float* part_s = reinterpret_cast<float*>(sc + plan.cand_bytes);
     const int parts = plan.splits * plan.halves;
-    long long* part_i = reinterpret_cast<long long*>(sc + plan.cand_bytes + (((size_t)parts * Q * k * 4 + 255) & ~(size_t)255));
+    long long* part_i = reinterpret_cast<long long*>(sc + plan.cand_bytes + (((size_t)parts * Q * plan.room * 4 + 255) & ~(size_t)255));
     unsigned* gtau = reinterpret_cast<unsigned*>(sc + plan.cand_bytes + plan.part_bytes - topk_shared_bytes(Q, plan.splits));
     int* pcount = reinterpret_cast<int*>(reinterpret_cast<uint8_t*>(gtau) + topk_gtau_bytes(Q));
     unsigned* pubmax = reinterpret_cast<unsigned*>(reinterpret_cast<uint8_t*>(gtau) + 2 * topk_gtau_bytes(Q));
@@ -806,11 +887,11 @@ int topk_run(const void* queries, const void* gallery, int Q, long long N, int D
     static const int share_on = [] { const char* e = getenv("B200_TOPK_SHAREMAX"); return e ? atoi(e) : 1; }();
     const int share_max = (share_on && plan.qtiles == 1 && plan.splits >= k && plan.splits <= 320) ? 1 : 0;
     TopkParams p{Q, D, k, N, plan.rows_per_split, plan.splits, plan.qtiles, reinterpret_cast<unsigned long long*>(sc),
-                 part_s, part_i, index_base, scatter, status, 0, gtau, pubmax, share_max, pcount, plan.halves};
+                 part_s, part_i, index_base, scatter, status, 0, gtau, pubmax, share_max, pcount, plan.room, plan.halves};
     rc = plan.cpl == 16 ? launch_topk<16>(tq, tg, p, st) : launch_topk<32>(tq, tg, p, st);
     if (rc) return rc;
     // out_keys: exchange form for the sharded search, indices relative to this shard
-    return merge_launch<false>(part_s, part_i, nullptr, nullptr, parts, Q, k, out_s, out_i, out_keys, index_base, st, pcount);
+    return merge_launch<false>(part_s, part_i, nullptr, nullptr, parts, Q, k, out_s, out_i, out_keys, index_base, st, pcount, parts * plan.room);
 }
 
 }  // namespace b200
@@ -852,6 +933,7 @@ extern "C" int b200clip_topk_static(const void* queries_f16_dev, int32_t Q, cons
     // Same work split as b200clip_topk, shrunk until candidate lists + per-split results fit the fixed array.
     TopkPlan plan;
     plan.cpl = 16;
+    plan.room = k;                            // per-split results of k slots, as sized below
     plan.halves = 1;                          // four scanning warps: half the list memory of the handle path, so the array holds twice the queries
     plan.qtiles = (Q + TK_BM - 1) / TK_BM;
     const long long ntiles = (N + TK_BN - 1) / TK_BN;

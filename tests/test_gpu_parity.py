@@ -330,6 +330,15 @@ def test_topk_adversarial_ascending_and_merge():
     parts = [eng.topk(qt, gt[lo:lo + 1500].contiguous(), k, index_base=lo) for lo in range(0, N, 1500)]
     ms, mi = eng.merge_topk(torch.stack([p[0] for p in parts]), torch.stack([p[1] for p in parts]))
     assert np.array_equal(mi.cpu().numpy(), io) and np.array_equal(ms.cpu().numpy(), so)
+    # the same with two query tiles: there a scanner hands its whole list to the merge kernel, or - when the list ended the scan
+    # longer than its share of the query's slice, as ascending scores make it - selects its k best first
+    N2 = 40000
+    g2 = np.zeros((N2, D), np.float16); g2[:, 0] = (np.arange(N2) // 3) % 2048; g2[:, 1] = np.arange(N2) // (3 * 2048)
+    q2 = np.zeros((200, D), np.float16); q2[:, 0] = np.resize([1, -1, 0, 2], 200); q2[:, 1] = np.resize([8, 0, -8], 200)
+    for kk in (50, 100):
+        s2, i2 = eng.topk(torch.from_numpy(q2).cuda(), torch.from_numpy(g2).cuda(), kk)
+        so2, io2 = O.topk_cosine(q2, g2, kk)
+        assert np.array_equal(i2.cpu().numpy(), io2) and np.array_equal(s2.cpu().numpy(), so2), kk
     eng.sync()
     eng.close()
 

@@ -66,61 +66,75 @@ __device__ __forceinline__ float unflip_f32(uint32_t u) {
 //     the low word picks the smallest indices.  With part_s/part_i the survivors are also written out as
 //     (score, global index), padded with (-inf, -1); the merge kernel sorts, so no order is needed here.
 // `tau_out` is the new threshold (-inf while fewer than k candidates exist).
+// The select + write-back part works on keys already in registers (lane l holds entries l, 32 + l, ...; 0 = no entry), so that the
+// mid-scan loop can have the next row's loads in flight while this row is processed.  `thr` != 0 first drops what scores below the
+// shared bound (entries EQUAL to it stay: the index-ordered tie rule may still prefer them); the select then only runs if the row
+// is still longer than `room`.
 template <int CPL>
-__device__ __noinline__ int compact_row(unsigned long long* rowptr, int n, int k, int lane, bool exact, int room,
-                                        float* tau_out, float* part_s, long long* part_i, long long index_base, bool pad = true) {
-    uint32_t hi[CPL], lo[CPL];
-    __syncwarp();
-#pragma unroll
-    for (int i = 0; i < CPL; ++i) {
-        const int e = i * 32 + lane;
-        const unsigned long long key = e < n ? __ldcg(rowptr + e) : 0ull;     // 0 sorts below every real key
-        hi[i] = (uint32_t)(key >> 32); lo[i] = (uint32_t)key;
-    }
+__device__ __forceinline__ int compact_regs(unsigned long long* rowptr, uint32_t (&hi)[CPL], uint32_t (&lo)[CPL], int n, int k, int lane,
+                                            bool exact, bool force, int room, uint32_t thr, float* tau_out, float* part_s, long long* part_i,
+                                            long long index_base, bool pad) {
     int keep = n;
     float tau = -INFINITY;
-    if (n >= k) {
+    bool changed = false;
+    if (thr != 0u) {
+        int c = 0;
+#pragma unroll
+        for (int i = 0; i < CPL; ++i) {
+            if (hi[i] < thr) { hi[i] = 0u; lo[i] = 0u; }
+            c += __popc(__ballot_sync(0xffffffffu, hi[i] != 0u));
+        }
+        changed = c != n;
+        n = c;
+    }
+    const bool select = n >= k && (force || n > room);
+    if (select || changed) {
         uint32_t p = 0, pl = 0; int kk = k;
-        auto select_hi = [&](int b_from, int b_to) {
+        if (select) {
+            auto select_hi = [&](int b_from, int b_to) {
 #pragma unroll 1
-            for (int b = b_from; b >= b_to; --b) {
-                const uint32_t want = p | (1u << b), m = 0xffffffffu << b;
-                int c0 = 0, c1 = 0, c2 = 0, c3 = 0;
+                for (int b = b_from; b >= b_to; --b) {
+                    const uint32_t want = p | (1u << b), m = 0xffffffffu << b;
+                    int c0 = 0, c1 = 0, c2 = 0, c3 = 0;
 #pragma unroll
-                for (int i = 0; i < CPL; i += 4) {
-                    c0 += __popc(__ballot_sync(0xffffffffu, (hi[i] & m) == want));
-                    c1 += __popc(__ballot_sync(0xffffffffu, (hi[i + 1] & m) == want));
-                    c2 += __popc(__ballot_sync(0xffffffffu, (hi[i + 2] & m) == want));
-                    c3 += __popc(__ballot_sync(0xffffffffu, (hi[i + 3] & m) == want));
+                    for (int i = 0; i < CPL; i += 4) {
+                        c0 += __popc(__ballot_sync(0xffffffffu, (hi[i] & m) == want));
+                        c1 += __popc(__ballot_sync(0xffffffffu, (hi[i + 1] & m) == want));
+                        c2 += __popc(__ballot_sync(0xffffffffu, (hi[i + 2] & m) == want));
+                        c3 += __popc(__ballot_sync(0xffffffffu, (hi[i + 3] & m) == want));
+                    }
+                    const int c = (c0 + c1) + (c2 + c3);
+                    if (c >= kk) p = want; else kk -= c;
                 }
-                const int c = (c0 + c1) + (c2 + c3);
-                if (c >= kk) p = want; else kk -= c;
-            }
-        };
-        auto count_ge = [&]() {
-            int c = 0;
+            };
+            auto count_ge = [&]() {
+                int c = 0;
 #pragma unroll
-            for (int i = 0; i < CPL; ++i) c += __popc(__ballot_sync(0xffffffffu, hi[i] >= p));
-            return c;
-        };
-        select_hi(31, 16);
-        bool coarse = !exact;
-        if (coarse && count_ge() > room) coarse = false;   // degenerate: too many ties at 16-bit resolution
-        if (!coarse) {
-            select_hi(15, 0);
-            int ceq = 0;
+                for (int i = 0; i < CPL; ++i) c += __popc(__ballot_sync(0xffffffffu, hi[i] >= p));
+                return c;
+            };
+            select_hi(31, 16);
+            bool coarse = !exact;
+            if (coarse && count_ge() > room) coarse = false;   // degenerate: too many ties at 16-bit resolution
+            if (!coarse) {
+                select_hi(15, 0);
+                int ceq = 0;
 #pragma unroll
-            for (int i = 0; i < CPL; ++i) ceq += __popc(__ballot_sync(0xffffffffu, hi[i] == p));
-            if (ceq > kk) {                                // ties at the k-th score: kk-th largest low word = kk-th smallest index
+                for (int i = 0; i < CPL; ++i) ceq += __popc(__ballot_sync(0xffffffffu, hi[i] == p));
+                if (ceq > kk) {                                // ties at the k-th score: kk-th largest low word = kk-th smallest index
 #pragma unroll 1
-                for (int b = 31; b >= 0; --b) {
-                    const uint32_t want = pl | (1u << b), m = 0xffffffffu << b;
-                    int c = 0;
+                    for (int b = 31; b >= 0; --b) {
+                        const uint32_t want = pl | (1u << b), m = 0xffffffffu << b;
+                        int c = 0;
 #pragma unroll
-                    for (int i = 0; i < CPL; ++i) c += __popc(__ballot_sync(0xffffffffu, hi[i] == p && (lo[i] & m) == want));
-                    if (c >= kk) pl = want; else kk -= c;
+                        for (int i = 0; i < CPL; ++i) c += __popc(__ballot_sync(0xffffffffu, hi[i] == p && (lo[i] & m) == want));
+                        if (c >= kk) pl = want; else kk -= c;
+                    }
                 }
             }
+            tau = unflip_f32(p);
+        } else {
+            p = 1u;                                            // keep every entry that is still there
         }
         int base = 0;
         const uint32_t lt = (1u << lane) - 1u;
@@ -136,7 +150,6 @@ __device__ __noinline__ int compact_row(unsigned long long* rowptr, int n, int k
             base += __popc(bal);
         }
         keep = base;
-        tau = unflip_f32(p);
     } else if (part_s != nullptr) {
 #pragma unroll
         for (int i = 0; i < CPL; ++i) {
@@ -151,6 +164,24 @@ __device__ __noinline__ int compact_row(unsigned long long* rowptr, int n, int k
         }
     }
     *tau_out = tau;
+    return keep;
+}
+template <int CPL>
+__device__ __forceinline__ void load_row_keys(const unsigned long long* rowptr, int n, int lane, uint32_t (&hi)[CPL], uint32_t (&lo)[CPL]) {
+#pragma unroll
+    for (int i = 0; i < CPL; ++i) {
+        const int e = i * 32 + lane;
+        const unsigned long long key = e < n ? __ldcg(rowptr + e) : 0ull;     // 0 sorts below every real key
+        hi[i] = (uint32_t)(key >> 32); lo[i] = (uint32_t)key;
+    }
+}
+template <int CPL>
+__device__ __noinline__ int compact_row(unsigned long long* rowptr, int n, int k, int lane, bool exact, int room,
+                                        float* tau_out, float* part_s, long long* part_i, long long index_base, bool pad = true) {
+    uint32_t hi[CPL], lo[CPL];
+    __syncwarp();
+    load_row_keys<CPL>(rowptr, n, lane, hi, lo);
+    const int keep = compact_regs<CPL>(rowptr, hi, lo, n, k, lane, exact, /*force*/ true, room, 0u, tau_out, part_s, part_i, index_base, pad);
     __syncwarp();
     return keep;
 }
@@ -440,22 +471,44 @@ topk_tc_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ 
                     if (kth != 0u && lane == 0) atomicMax(p.gtau + myq, kth);
                 }
             }
-            // make room for the next tile (256 possible appends) while the MMAs of tile t+1 run: first drop what the shared bound
-            // already rules out (one cheap pass), and only if the list is still too long select its k best
+            // make room for the next tile (256 possible appends) while the MMAs of tile t+1 run: drop what the shared bound already
+            // rules out, and only if the list is still too long select its k best.  One row at a time for the whole warp, so the
+            // cost is L2 round trips: every lane fetches its own row's bound up front, a row's keys are loaded once for both steps,
+            // and the next row's loads are in flight while this one is processed (a cold start spends most of its time here).
             unsigned need = __ballot_sync(0xffffffffu, cnt + span > C);
-            while (need) {
-                const int src = __ffs(need) - 1;
-                need &= need - 1;
-                int n = __shfl_sync(0xffffffffu, cnt, src);
-                const long long qs = __shfl_sync(0xffffffffu, qrow, src);
-                const unsigned g = qs < p.Q ? __ldcg(p.gtau + qs) : 0u;
-                if (g > 1u) n = filter_row<CPL>(warp_rows + (size_t)src * C, n, g, lane);
-                float tnew = -INFINITY;
-                if (n + span > C) {
-                    n = compact_row<CPL>(warp_rows + (size_t)src * C, n, p.k, lane, false, C - span, &tnew, nullptr, nullptr, 0);
-                    if (lane == src && qrow < p.Q) atomicMax(p.gtau + qrow, flip_f32(tnew));   // k rows of THIS split score >= tnew
+            if (need) {
+                const unsigned g_mine = qrow < p.Q ? __ldcg(p.gtau + qrow) : 0u;
+                uint32_t hi[CPL], lo[CPL];
+                int src = __ffs(need) - 1;
+                __syncwarp();                                // the row's appends are visible to the whole warp
+                load_row_keys<CPL>(warp_rows + (size_t)src * C, __shfl_sync(0xffffffffu, cnt, src), lane, hi, lo);
+                while (need) {
+                    need &= need - 1;
+                    const int nxt = need ? __ffs(need) - 1 : -1;
+                    constexpr int CP2 = CPL <= 16 ? CPL : 1;      // (1024-entry lists: two rows of keys do not fit the register file)
+                    uint32_t hi2[CP2], lo2[CP2];
+                    if (CPL <= 16 && nxt >= 0) load_row_keys<CP2>(warp_rows + (size_t)nxt * C, __shfl_sync(0xffffffffu, cnt, nxt), lane, hi2, lo2);
+                    const int n0r = __shfl_sync(0xffffffffu, cnt, src);
+                    const unsigned g = __shfl_sync(0xffffffffu, g_mine, src);
+                    float tnew = -INFINITY;
+                    const int n = compact_regs<CPL>(warp_rows + (size_t)src * C, hi, lo, n0r, p.k, lane, false, false, C - span, g > 1u ? g : 0u,
+                                                    &tnew, nullptr, nullptr, 0, false);
+                    if (lane == src) {
+                        if (tnew > -INFINITY && qrow < p.Q) atomicMax(p.gtau + qrow, flip_f32(tnew));   // k rows of THIS split score >= tnew
+                        cnt = n; tau = fmaxf(tau, tnew);
+                    }
+                    if (nxt >= 0) {
+                        if (CPL <= 16) {
+#pragma unroll
+                            for (int i = 0; i < CP2; ++i) { hi[i] = hi2[i]; lo[i] = lo2[i]; }
+                        } else {
+                            __syncwarp();
+                            load_row_keys<CPL>(warp_rows + (size_t)nxt * C, __shfl_sync(0xffffffffu, cnt, nxt), lane, hi, lo);
+                        }
+                    }
+                    src = nxt;
                 }
-                if (lane == src) { cnt = n; tau = fmaxf(tau, tnew); }
+                __syncwarp();
             }
         }
         // final: what is left of every row's list goes to the query's candidate slice for the merge kernel, as (score, global index).

@@ -10,7 +10,7 @@ for w in preprocess search classify models gemm attention decode n4; do python b
 python bench_paths.py search --gallery 10000000 2>/dev/null > gpurun_out/paths_search10m_r2.jsonl
 S="python bench.py --steps 2 --warmup 3 --batches-per-step 1 --cpu-seconds 1 --skip-search --skip-configs"
 $S > gpurun_out/plain.log 2>&1 && \
-ncu --metrics gpu__time_duration.sum --clock-control none -s 273 -c 91 --csv --log-file gpurun_out/launches_r2.csv $S > gpurun_out/ncu_launches.log 2>&1
+ncu --metrics gpu__time_duration.sum --clock-control none -s 276 -c 92 --csv --log-file gpurun_out/launches_r2.csv $S > gpurun_out/ncu_launches.log 2>&1
 $S > gpurun_out/plain2.log 2>&1 && \
 ncu --set full --clock-control none --import-source on -k regex:"gemm_tc|attention|layernorm|convert" -s 2 -c 8 -o gpurun_out/step_r2 $S > gpurun_out/ncu_step.log 2>&1
 python bench_paths.py preprocess > gpurun_out/plain3.log 2>&1 && \

@@ -428,7 +428,8 @@ static int encode_chunk(b200clip_handle* h, const __nv_bfloat16* patches, int B,
             // the CLS row of each image only: B rows instead of B*S.  The CLS rows go through exactly the arithmetic they always
             // did; what is dropped are rows nothing reads.  (5/6 of the last layer's GEMM work: 6.9 % of a 12-layer tower.)
             const long long cls_pitch = (long long)S * d;                  // CLS rows inside the [B*S, d] buffers
-            R_(timed(2, [&] { return launch_layernorm(h->xres, 1, l.ln1_g, l.ln1_b, h->hbuf, M, d, c.ln_eps, st); }));
+            static const int snake_l = [] { const char* e = getenv("B200_SNAKE"); return e ? atoi(e) : 3; }();
+            R_(timed(2, [&] { return launch_layernorm(h->xres, 1, l.ln1_g, l.ln1_b, h->hbuf, M, d, c.ln_eps, st, ((snake_l >> 1) & 1) && li > 0); }));
             R_(timed(1, [&] { return gemm_bf16_tc(h->hbuf, d, l.w_qkv + (size_t)d * d, d, M, 2 * d, d, l.b_qkv + d, h->qkv + d, 3 * d, EPI_BIAS_BF16, 0, h->status, st); }));
             R_(timed(1, [&] { return gemm_bf16_tc(h->hbuf, (int)cls_pitch, l.w_qkv, d, B, d, d, l.b_qkv, h->q_cls, d, EPI_BIAS_BF16, 0, h->status, st); }));
             R_(timed(3, [&] { return launch_cls_attention(h->q_cls, h->qkv, h->attn_cls, B, S, d, c.heads, st); }));
@@ -439,13 +440,15 @@ static int encode_chunk(b200clip_handle* h, const __nv_bfloat16* patches, int B,
             h->launches += 1;                                               // eight kernels instead of the usual seven
             break;
         }
-        R_(timed(2, [&] { return launch_layernorm(h->xres, 1, l.ln1_g, l.ln1_b, h->hbuf, M, d, c.ln_eps, st); }));
+        static const int snake = [] { const char* e = getenv("B200_SNAKE"); return e ? atoi(e) : 3; }();   // bit 0: attention, bit 1: fc2 + LN1
+        const int ra = snake & 1, rf = (snake >> 1) & 1;
+        R_(timed(2, [&] { return launch_layernorm(h->xres, 1, l.ln1_g, l.ln1_b, h->hbuf, M, d, c.ln_eps, st, rf && li > 0); }));
         R_(timed(1, [&] { return gemm_bf16_tc(h->hbuf, d, l.w_qkv, d, M, 3 * d, d, l.b_qkv, h->qkv, 3 * d, EPI_BIAS_BF16, 0, h->status, st); }));
-        R_(timed(3, [&] { return launch_attention_auto(h->qkv, h->hbuf, B, S, d, c.heads, 0, h->status, st); }));
+        R_(timed(3, [&] { return launch_attention_auto(h->qkv, h->hbuf, B, S, d, c.heads, 0, h->status, st, ra); }));
         R_(timed(1, [&] { return gemm_bf16_tc(h->hbuf, d, l.w_o, d, M, d, d, l.b_o, h->xres, d, EPI_BIAS_RES_F32, 0, h->status, st); }));
         R_(timed(2, [&] { return launch_layernorm(h->xres, 1, l.ln2_g, l.ln2_b, h->hbuf, M, d, c.ln_eps, st); }));
         R_(timed(1, [&] { return gemm_bf16_tc(h->hbuf, d, l.w_fc1, d, M, mlp, d, l.b_fc1, h->mlp, mlp, EPI_BIAS_ACT_BF16, c.activation, h->status, st); }));
-        R_(timed(1, [&] { return gemm_bf16_tc(h->mlp, mlp, l.w_fc2, mlp, M, d, mlp, l.b_fc2, h->xres, d, EPI_BIAS_RES_F32, 0, h->status, st); }));
+        R_(timed(1, [&] { return gemm_bf16_tc(h->mlp, mlp, l.w_fc2, mlp, M, d, mlp, l.b_fc2, h->xres, d, EPI_BIAS_RES_F32, 0, h->status, st, rf); }));
     }
     R_(timed(2, [&] { return launch_layernorm(h->xres, S, h->post_g, h->post_b, h->cls_ln, B, d, c.ln_eps, st); }));
     R_(timed(1, [&] { return gemm_bf16_tc(h->cls_ln, d, h->w_proj, d, B, D, d, nullptr, h->emb_raw, D, EPI_F32, 0, h->status, st); }));

@@ -440,6 +440,7 @@ struct ShortAttnParams {
     int S, d, heads, items, tiles;
     __nv_bfloat16* out;
     DeviceStatus* status;
+    int reverse;             // walk the (image, head) problems from the last image to the first
 };
 
 __global__ void __launch_bounds__(SA_THREADS, 4)
@@ -477,7 +478,7 @@ attention_short_kernel(const __grid_constant__ CUtensorMap tmQKV, ShortAttnParam
                 if (t != (int)blockIdx.x && !(ok = mbar_wait_spin(q_free, ph ^ 1, p.status, 41))) break;
                 mbar_arrive_expect_tx(ld_full, 6 * SA_BOX);
                 for (int u = 0; u < 2; ++u) {
-                    const int item = min(2 * t + u, p.items - 1);
+                    const int raw = min(2 * t + u, p.items - 1), item = p.reverse ? p.items - 1 - raw : raw;
                     const int row0 = (item / p.heads) * p.S, col = (item % p.heads) * AT_DH;
                     tma_load_2d(sQ + u * SA_BOX, &tmQKV, ld_full, col, row0);
                     tma_load_2d(sK + u * SA_BOX, &tmQKV, ld_full, p.d + col, row0);
@@ -564,8 +565,9 @@ attention_short_kernel(const __grid_constant__ CUtensorMap tmQKV, ShortAttnParam
             }
             __syncwarp();
             // the warp's 32 rows, four full 128-byte rows per instruction
-            const int item = 2 * t + hsel;                              // warps 0,1 -> first problem, warps 2,3 -> second
-            if (item < p.items) {
+            const int raw = 2 * t + hsel;                               // warps 0,1 -> first problem, warps 2,3 -> second
+            const int item = p.reverse ? p.items - 1 - raw : raw;
+            if (raw < p.items) {
                 const int b_img = item / p.heads, h = item % p.heads;
 #pragma unroll
                 for (int tt = 0; tt < 8; ++tt) {
@@ -588,7 +590,7 @@ attention_short_kernel(const __grid_constant__ CUtensorMap tmQKV, ShortAttnParam
     if (warp == 4) { __syncwarp(); tmem_dealloc(tmem_base, 128); }
 }
 
-int launch_attention_short(const void* qkv, void* out, int B, int S, int d, int heads, DeviceStatus* status, cudaStream_t st) {
+int launch_attention_short(const void* qkv, void* out, int B, int S, int d, int heads, DeviceStatus* status, cudaStream_t st, int reverse) {
     if (B <= 0) return B200_OK;
     B200_REQUIRE(S > 0 && S <= 64 && heads > 0 && d == heads * AT_DH, "attention_short: needs S <= 64 and head_dim 64");
     B200_REQUIRE((long long)B * heads < (1LL << 30), "attention_short: too many (image, head) problems");
@@ -596,6 +598,7 @@ int launch_attention_short(const void* qkv, void* out, int B, int S, int d, int 
     p.S = S; p.d = d; p.heads = heads; p.items = B * heads; p.tiles = (p.items + 1) / 2;
     p.out = static_cast<__nv_bfloat16*>(out);
     p.status = status;
+    p.reverse = reverse;
     CUtensorMap tm;
     int rc = make_tmap_2d(&tm, qkv, (uint64_t)B * S, (uint64_t)3 * d, (uint64_t)3 * d * 2, 64, false);
     if (rc) return rc;
@@ -613,9 +616,9 @@ int launch_attention_short(const void* qkv, void* out, int B, int S, int d, int 
 }
 
 // Picks the kernel by shape: S <= 64 -> attention_short_kernel, longer sequences (and the causal text tower) -> attention_tc_kernel.
-int launch_attention_auto(const void* qkv, void* out, int B, int S, int d, int heads, int causal, DeviceStatus* status, cudaStream_t st) {
+int launch_attention_auto(const void* qkv, void* out, int B, int S, int d, int heads, int causal, DeviceStatus* status, cudaStream_t st, int reverse) {
     B200_REQUIRE(heads > 0 && S > 0 && d == heads * AT_DH, "attention: head_dim must be 64");
-    if (!causal && S <= AT_KEYS) return launch_attention_short(qkv, out, B, S, d, heads, status, st);
+    if (!causal && S <= AT_KEYS) return launch_attention_short(qkv, out, B, S, d, heads, status, st, reverse);
     return launch_attention_tc(qkv, out, B, S, d, heads, causal, status, st);
 }
 

@@ -28,6 +28,7 @@ struct GemmParams {
     int ldc;
     int epi, act;
     DeviceStatus* status;
+    int reverse;          // walk the tiles from the last row block to the first (see gemm_bf16_tc)
 };
 
 constexpr int BM = 128, BK = 64;
@@ -179,7 +180,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         if (lane == 0) {
             int s = 0; uint32_t ph = 0; bool ok = true;
             for (int t = blockIdx.x; t < tiles && ok; t += gridDim.x) {
-                const int m0 = (t / tiles_n) * BM, n0 = (t % tiles_n) * BN;
+                const int tt = p.reverse ? tiles - 1 - t : t;
+                const int m0 = (tt / tiles_n) * BM, n0 = (tt % tiles_n) * BN;
                 for (int kb = 0; kb < kblocks; ++kb) {
                     if (!(ok = mbar_wait(&empty[s], ph ^ 1, p.status, 1))) break;
                     uint8_t* sa = smem + s * Cfg::STAGE_BYTES;
@@ -219,7 +221,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ 
         const bool issuer = threadIdx.x == 64;         // first epilogue thread issues the TMA stores
         int it = 0, box_seq = 0; bool ok = true;
         for (int t = blockIdx.x; t < tiles && ok; t += gridDim.x, ++it) {
-            const int m0 = (t / tiles_n) * BM, n0 = (t % tiles_n) * BN;
+            const int tt = p.reverse ? tiles - 1 - t : t;
+            const int m0 = (tt / tiles_n) * BM, n0 = (tt % tiles_n) * BN;
             const int as = it & 1; const uint32_t aph = (it >> 1) & 1;
             if (!(ok = mbar_wait(&acc_full[as], aph, p.status, 4))) break;
             tc_fence_after();
@@ -295,7 +298,8 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         if (lane == 0) {
             int s = 0; uint32_t ph = 0; bool ok = true;
             for (int t = pair; t < tiles && ok; t += npairs) {
-                const int m0 = (t / tiles_n) * 2 * BM + (int)rank * BM, n0 = (t % tiles_n) * BN + (int)rank * (BN / 2);
+                const int tt = p.reverse ? tiles - 1 - t : t;
+                const int m0 = (tt / tiles_n) * 2 * BM + (int)rank * BM, n0 = (tt % tiles_n) * BN + (int)rank * (BN / 2);
                 for (int kb = 0; kb < kblocks; ++kb) {
                     if (!(ok = mbar_wait(&empty[s], ph ^ 1, p.status, 21))) break;
                     uint8_t* sa = smem + s * Cfg::STAGE_BYTES;
@@ -335,7 +339,8 @@ gemm_tc2_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__
         const uint32_t leader_acc_empty0 = mapa_u32(smem_u32(&acc_empty[0]), 0);
         int it = 0, box_seq = 0; bool ok = true;
         for (int t = pair; t < tiles && ok; t += npairs, ++it) {
-            const int m0 = (t / tiles_n) * 2 * BM + (int)rank * BM, n0 = (t % tiles_n) * BN;
+            const int tt = p.reverse ? tiles - 1 - t : t;
+            const int m0 = (tt / tiles_n) * 2 * BM + (int)rank * BM, n0 = (tt % tiles_n) * BN;
             const int as = it & 1; const uint32_t aph = (it >> 1) & 1;
             if (!(ok = mbar_wait(&acc_full[as], aph, p.status, 24))) break;
             tc_fence_after();
@@ -454,7 +459,7 @@ template <int BN> static int dispatch_gemm(const CUtensorMap& ta, const CUtensor
 
 // A: bf16 [M, lda] (lda >= K, K % 64 == 0, zero padded), W: bf16 [N, ldw].
 int gemm_bf16_tc(const void* A, int lda, const void* W, int ldw, int M, int N, int K, const float* bias, void* out,
-                 int ldc, int epi, int act, DeviceStatus* status, cudaStream_t st) {
+                 int ldc, int epi, int act, DeviceStatus* status, cudaStream_t st, int reverse) {
     B200_REQUIRE(M > 0 && N > 0 && K > 0 && K % BK == 0, "gemm: K must be a positive multiple of 64 (pad the operands)");
     B200_REQUIRE(N % 4 == 0 && ldc % 4 == 0, "gemm: N and the output pitch must be multiples of 4");
     // 128x256 tiles read 96 B/clk of shared memory per MMA against 128 B/clk for 128x128, so prefer them unless
@@ -483,7 +488,7 @@ int gemm_bf16_tc(const void* A, int lda, const void* W, int ldw, int M, int N, i
     // measured on B200 (M = 25,600): the CTA pair wins on every encoder shape except the small out-proj (N = K = 768)
     const bool pair = force == 1 || (force != 0 && M >= 2048 && N >= 256 && !(N <= 768 && K <= 768));
     if (pair) {
-        GemmParams p2{M, N, K, bias, out, ldc, epi, act, status};
+        GemmParams p2{M, N, K, bias, out, ldc, epi, act, status, reverse};
         int rc2 = make_tmap_2d(&ta, A, M, K, (uint64_t)lda * 2, BM, false);
         if (rc2) return rc2;
         rc2 = make_tmap_2d(&tb, W, N, K, (uint64_t)ldw * 2, 128, false);      // each CTA loads half of the 256-wide W tile
@@ -494,7 +499,7 @@ int gemm_bf16_tc(const void* A, int lda, const void* W, int ldw, int M, int N, i
     if (rc) return rc;
     rc = make_tmap_2d(&tb, W, N, K, (uint64_t)ldw * 2, bn, false);
     if (rc) return rc;
-    GemmParams p{M, N, K, bias, out, ldc, epi, act, status};
+    GemmParams p{M, N, K, bias, out, ldc, epi, act, status, reverse};
     return bn == 64 ? dispatch_gemm<64>(ta, tb, tc, p, st) : bn == 128 ? dispatch_gemm<128>(ta, tb, tc, p, st) :
            bn == 192 ? dispatch_gemm<192>(ta, tb, tc, p, st) : dispatch_gemm<256>(ta, tb, tc, p, st);
 }

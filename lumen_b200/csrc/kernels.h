@@ -17,8 +17,9 @@ void preprocess_state_destroy(PreprocessState*);
 int preprocess_run(PreprocessState*, const uint8_t* src_dev, const long long* offsets, const int* hw, int B, int S, int mode,
                    int layout, int out_bf16, int P, int kpad, void* out_dev, cudaStream_t st);
 int gemm_bf16_tc(const void* A, int lda, const void* W, int ldw, int M, int N, int K, const float* bias, void* out, int ldc,
-                 int epi, int act, DeviceStatus* status, cudaStream_t st);
-int launch_layernorm(const float* x, long long row_stride, const float* g, const float* b, void* out, int rows, int d, float eps, cudaStream_t st);
+                 int epi, int act, DeviceStatus* status, cudaStream_t st, int reverse = 0);
+int launch_layernorm(const float* x, long long row_stride, const float* g, const float* b, void* out, int rows, int d, float eps, cudaStream_t st,
+                     int forward = 0);
 int launch_embed_preln(const float* patch, const float* cls, const float* pos, const float* g, const float* b, float* xres,
                        int B, int S, int d, float eps, cudaStream_t st);
 int launch_l2_normalize(const float* in, float* out, int rows, int D, cudaStream_t st);
@@ -29,8 +30,8 @@ int launch_text_eot_gather(const int* ids, const float* x, float* out, int B, in
 int launch_gallery_pack(const float* in, void* out_f16, long long rows, int D, int normalize, cudaStream_t st);
 // tcgen05 attention (attention_tc.cu), head_dim 64: attention_tc_kernel for S > 64 (and the causal text tower),
 // S <= 64 on tcgen05 (attention_tc.cu): two (image, head) problems per 128-row tile, four small CTAs per SM
-int launch_attention_short(const void* qkv, void* out, int B, int S, int d, int heads, DeviceStatus* status, cudaStream_t st);
-int launch_attention_auto(const void* qkv, void* out, int B, int S, int d, int heads, int causal, DeviceStatus* status, cudaStream_t st);
+int launch_attention_short(const void* qkv, void* out, int B, int S, int d, int heads, DeviceStatus* status, cudaStream_t st, int reverse = 0);
+int launch_attention_auto(const void* qkv, void* out, int B, int S, int d, int heads, int causal, DeviceStatus* status, cudaStream_t st, int reverse = 0);
 int launch_attention_tc(const void* qkv, void* out, int B, int S, int d, int heads, int causal, DeviceStatus* status, cudaStream_t st);
 struct TopkPlan { int splits, qtiles, cpl, halves, room; long long rows_per_split; size_t cand_bytes, part_bytes, qstage_bytes; };
 int topk_plan(int Q, long long N, int k, TopkPlan* plan);

@@ -30,13 +30,14 @@ __device__ __forceinline__ void ln_row(float4 (&v)[LN_MAX_V4], int nv, int d, fl
 // x: fp32 rows (row r at x + r*row_stride*d), out: bf16 [rows, d].
 __global__ void __launch_bounds__(256) layernorm_bf16_kernel(const float* __restrict__ x, long long row_stride,
                                                              const float* __restrict__ gamma, const float* __restrict__ beta,
-                                                             __nv_bfloat16* __restrict__ out, int rows, int d, float eps) {
+                                                             __nv_bfloat16* __restrict__ out, int rows, int d, float eps, int forward) {
     pdl_wait();
     pdl_trigger();
     // rows are walked from the end: the GEMM that just updated x finished with the last row blocks, so those are the
-    // lines most likely still in L2
-    const int row = rows - 1 - (blockIdx.x * 8 + (threadIdx.x >> 5)), lane = threadIdx.x & 31;
-    if (row < 0) return;
+    // lines most likely still in L2 (forward != 0: that GEMM itself ran from the end)
+    const int r0 = blockIdx.x * 8 + (threadIdx.x >> 5);
+    const int row = forward ? r0 : rows - 1 - r0, lane = threadIdx.x & 31;
+    if (row < 0 || row >= rows) return;
     const int nv = d >> 7;
     const float4* xr = reinterpret_cast<const float4*>(x + (size_t)row * row_stride * d);
     float4 v[LN_MAX_V4];
@@ -238,9 +239,10 @@ int launch_cls_attention(const void* q, const void* qkv, void* out, int B, int S
     B200_CUDA_OK(cudaGetLastError());
     return B200_OK;
 }
-int launch_layernorm(const float* x, long long row_stride, const float* g, const float* b, void* out, int rows, int d, float eps, cudaStream_t st) {
+int launch_layernorm(const float* x, long long row_stride, const float* g, const float* b, void* out, int rows, int d, float eps, cudaStream_t st,
+                     int forward) {
     B200_REQUIRE(d % 128 == 0 && d <= 128 * LN_MAX_V4, "layernorm: width must be a multiple of 128, at most 1024");
-    B200_CUDA_OK(launch_pdl(layernorm_bf16_kernel, dim3((rows + 7) / 8), dim3(256), 0, st, x, row_stride, g, b, reinterpret_cast<__nv_bfloat16*>(out), rows, d, eps));
+    B200_CUDA_OK(launch_pdl(layernorm_bf16_kernel, dim3((rows + 7) / 8), dim3(256), 0, st, x, row_stride, g, b, reinterpret_cast<__nv_bfloat16*>(out), rows, d, eps, forward));
     B200_CUDA_OK(cudaGetLastError());
     return B200_OK;
 }

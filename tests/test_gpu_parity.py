@@ -281,7 +281,8 @@ def test_topk_exact_integer_gallery_with_ties():
     from oracle import clip_oracle as O
     eng = Engine({}, device=0)
     rng = np.random.default_rng(20)
-    for Q, N, D, k in ((5, 3000, 64, 10), (130, 20000, 512, 100), (1, 700, 128, 256), (33, 257, 64, 300), (4, 50, 64, 100)):
+    # (the last case is large enough for the seeding pass: two query tiles, more than 16 x 16384 rows)
+    for Q, N, D, k in ((5, 3000, 64, 10), (130, 20000, 512, 100), (1, 700, 128, 256), (33, 257, 64, 300), (4, 50, 64, 100), (200, 300000, 64, 100)):
         g = rng.integers(-8, 9, (N, D)).astype(np.float16)
         g[N // 2:N // 2 + N // 10] = g[:N // 10]                   # exact duplicates -> index-ordered ties
         q = rng.integers(-8, 9, (Q, D)).astype(np.float16)

@@ -117,8 +117,8 @@ L.append("\n## K5 attention (`paths_r2.jsonl`)\n\n| tower | B x S x heads | kern
 for d in paths:
     if d.get("path") == "K5 attention":
         L.append(f"| {d['model']} | {d['B']} x {d['S']} x {d['heads']} | {d['kernel']} | {d['us']:.1f} | {d['hbm_frac']:.3f} | {d['frac_of_sfu_exp2_peak']:.3f} |")
-L.append("\nS = 50 (ViT-B/32): round 1's mma.sync kernel took 50 us per layer; `attention_short_kernel` (tcgen05, four small CTAs per SM) takes 32.  Its 64-row TMA boxes "
-         "fetch 28 % more rows than the 50 a sequence holds, which is most of the remaining distance to the HBM floor.\n")
+L.append("\nS = 50 (ViT-B/32): round 1's mma.sync kernel took 50 us per layer; `attention_short_kernel` (tcgen05, four small CTAs per SM - the TMEM limit) takes 32.  "
+         "What it waits for is the hand-off chain of a tile (TMA -> MMA -> softmax -> MMA -> store), not bytes: boxes of exactly 50 rows instead of 64 (28 % fewer bytes) changed nothing.\n")
 for title, rows_ in (("1.25 M-row shard (the per-GPU share of C5)", [d for d in paths if d.get("path") == "K10+K12 gallery search"]), ("10 M rows on one GPU", s10)):
     if rows_:
         L.append(f"## K10 + K12 gallery search, {title}, k = 100\n\n| Q | ms | queries/s | of burst bf16 peak | of HBM peak |\n|---|---|---|---|---|")

@@ -17,5 +17,5 @@ python bench_paths.py preprocess > gpurun_out/plain3.log 2>&1 && \
 ncu --set full --clock-control none -k regex:"preprocess_kernel" -s 2 -c 1 -o gpurun_out/k1_resize_r2 python bench_paths.py preprocess > gpurun_out/ncu_k1.log 2>&1
 python bench_paths.py search --qs 64,4096 > gpurun_out/plain4.log 2>&1 && \
 ncu --set full --clock-control none -k regex:"topk_tc|merge_topk" -s 2 -c 2 -o gpurun_out/search_q64_r2 python bench_paths.py search --qs 64 > gpurun_out/ncu_s1.log 2>&1
-ncu --set full --clock-control none -k regex:"topk_tc" -s 2 -c 1 -o gpurun_out/search_q4096_r2 python bench_paths.py search --qs 4096 > gpurun_out/ncu_s2.log 2>&1
+ncu --set full --clock-control none -k regex:"topk_tc" -s 2 -c 2 -o gpurun_out/search_q4096_r2 python bench_paths.py search --qs 4096 > gpurun_out/ncu_s2.log 2>&1
 ls -la gpurun_out

@@ -174,6 +174,16 @@ int b200clip_topk_keys(b200clip_handle* h, const void* queries_f16_dev, int32_t 
 int b200clip_merge_topk_keys(b200clip_handle* h, const uint64_t* part_keys_dev, const int64_t* part_bases_dev, int32_t parts,
                              int32_t Q, int32_t k, float* out_scores_dev, int64_t* out_index_dev, void* stream);
 
+/* Sharded gallery search in ONE call for a caller that brings an NCCL communicator - SURVEY §8(b)'s b200clip_merge_topk(..., ncclComm_t);
+ * the reference has no counterpart (bioclip_model.py:313-316 searches one in-process matrix).  Every rank passes the same queries and
+ * its own row shard (N_local may be 0) with the global index of the shard's first row; the call runs the fused top-k on the shard, moves
+ * the [Q,k] 64-bit exchange keys and the index bases with one grouped ncclAllGather on `stream`, merges, and leaves the global top-k
+ * (scores fp32 [Q,k], indices int64 [Q,k], -1 = empty slot) on EVERY rank.  `nccl_comm` is an ncclComm_t of `world` ranks; NCCL is
+ * resolved at run time from the libnccl the process has loaded (the library does not link against it): B200CLIP_ESTATE if there is none. */
+int b200clip_search_sharded(b200clip_handle* h, const void* queries_f16_dev, int32_t Q, const void* gallery_shard_f16_dev, int64_t N_local,
+                            int32_t D, int32_t k, int64_t index_base, void* nccl_comm, int32_t world, float* out_scores_dev,
+                            int64_t* out_index_dev, void* stream);
+
 /* Search without any allocation.  No counterpart in the reference: it exists for callers that are not allowed to
  * allocate device memory at the moment they search — a host thread whose stream is being captured into a CUDA graph,
  * a real-time serving loop that must not hit the allocator's locks, or a plug-in living inside another framework's

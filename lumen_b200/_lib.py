@@ -53,6 +53,7 @@ SIGNATURES = {
     "b200clip_topk": (C.c_int, [_P, _P, _I32, _P, _I64, _I32, _I32, _I64, _P, _P, _P]),
     "b200clip_topk_keys": (C.c_int, [_P, _P, _I32, _P, _I64, _I32, _I32, _P, _P]),
     "b200clip_merge_topk_keys": (C.c_int, [_P, _P, _P, _I32, _I32, _I32, _P, _P, _P]),
+    "b200clip_search_sharded": (C.c_int, [_P, _P, _I32, _P, C.c_int64, _I32, _I32, C.c_int64, _P, _I32, _P, _P, _P]),
     "b200clip_topk_static": (C.c_int, [_P, _I32, _P, _I64, _I32, _I32, _I64, _P, _P, _P]),
     "b200clip_topk_static_status": (C.c_int, [_P]),
     "b200clip_merge_topk": (C.c_int, [_P, _P, _P, _I32, _I32, _I32, _P, _P, _P]),

@@ -4,6 +4,8 @@
 #include "common.cuh"
 #include "kernels.h"
 
+#include <dlfcn.h>
+
 #include <algorithm>
 #include <cstdlib>
 #include <cstring>
@@ -76,6 +78,7 @@ struct b200clip_handle {
     float* labels[2] = {nullptr, nullptr}; int labels_n[2] = {0, 0}, labels_d[2] = {0, 0};
     // search scratch
     void* topk_scratch = nullptr; size_t topk_cap = 0;
+    void* shard_buf = nullptr; size_t shard_cap = 0;      // b200clip_search_sharded: own keys | gathered keys | own base | gathered bases
     PreprocessState* pre = nullptr;
     JpegState* jpeg = nullptr;          // created on first decode
     TextTower* text = nullptr;          // b200clip_text_init
@@ -203,7 +206,7 @@ extern "C" void b200clip_destroy(b200clip_handle* h) {
     for (void* p : h->allocs) cudaFree(p);
     for (cudaEvent_t e : h->ev_pool) cudaEventDestroy(e);
     if (h->ws_done) cudaEventDestroy(h->ws_done);
-    cudaFree(h->upload_tmp); cudaFree(h->img_dev); cudaFree(h->emb_dev); cudaFree(h->topk_scratch);
+    cudaFree(h->upload_tmp); cudaFree(h->img_dev); cudaFree(h->emb_dev); cudaFree(h->topk_scratch); cudaFree(h->shard_buf);
     cudaFree(h->labels[0]); cudaFree(h->labels[1]);
     if (h->pre) preprocess_state_destroy(h->pre);
     jpeg_state_destroy(h->jpeg);
@@ -632,6 +635,86 @@ extern "C" int b200clip_merge_topk_keys(b200clip_handle* h, const uint64_t* part
     rc = merge_topk_keys_run(reinterpret_cast<const unsigned long long*>(part_keys), reinterpret_cast<const long long*>(part_bases_dev), parts, Q, k,
                              out_scores, reinterpret_cast<long long*>(out_index), (cudaStream_t)stream);
     if (rc == B200_OK && Q > 0) h->launches += 1;
+    return rc;
+}
+
+// NCCL is looked up at run time (the library does not link against it): the libnccl the process has already loaded - the one the
+// caller's communicator belongs to - or, failing that, the system's.
+namespace {
+typedef int (*NcclAllGatherFn)(const void*, void*, size_t, int, void*, cudaStream_t);
+typedef int (*NcclGroupFn)();
+typedef const char* (*NcclErrorStringFn)(int);
+struct NcclApi { NcclAllGatherFn all_gather = nullptr; NcclGroupFn group_start = nullptr, group_end = nullptr; NcclErrorStringFn error_string = nullptr; };
+NcclApi g_nccl;
+std::once_flag g_nccl_once;
+const NcclApi* nccl_api() {
+    std::call_once(g_nccl_once, [] {
+        void* lib = dlopen("libnccl.so.2", RTLD_NOW | RTLD_NOLOAD);
+        if (!lib) lib = dlopen("libnccl.so.2", RTLD_NOW);
+        if (!lib) lib = dlopen("libnccl.so", RTLD_NOW);
+        if (!lib) return;
+        g_nccl.all_gather = reinterpret_cast<NcclAllGatherFn>(dlsym(lib, "ncclAllGather"));
+        g_nccl.group_start = reinterpret_cast<NcclGroupFn>(dlsym(lib, "ncclGroupStart"));
+        g_nccl.group_end = reinterpret_cast<NcclGroupFn>(dlsym(lib, "ncclGroupEnd"));
+        g_nccl.error_string = reinterpret_cast<NcclErrorStringFn>(dlsym(lib, "ncclGetErrorString"));
+    });
+    return g_nccl.all_gather && g_nccl.group_start && g_nccl.group_end ? &g_nccl : nullptr;
+}
+}  // namespace
+
+extern "C" int b200clip_search_sharded(b200clip_handle* h, const void* queries, int32_t Q, const void* gallery_shard, int64_t N_local, int32_t D,
+                                       int32_t k, int64_t index_base, void* nccl_comm, int32_t world, float* out_scores, int64_t* out_index,
+                                       void* stream) {
+    int rc = set_device(h); if (rc) return rc;
+    B200_REQUIRE(queries && out_scores && out_index && nccl_comm, "search_sharded: null buffer or communicator");
+    B200_REQUIRE(Q > 0 && k > 0 && world >= 1 && N_local >= 0 && (N_local == 0 || gallery_shard), "search_sharded: bad sizes");
+    const NcclApi* nccl = nccl_api();
+    if (!nccl) return fail(B200CLIP_ESTATE, "search_sharded: no NCCL library in this process (libnccl.so.2 not found)");
+    std::lock_guard<std::mutex> lk(h->mu);
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t nk = (size_t)Q * k;
+    const size_t bases_off = ((nk * 8 * ((size_t)world + 1) + 255) & ~(size_t)255);
+    const size_t need_sh = bases_off + 256 + (size_t)world * 8;
+    if (need_sh > h->shard_cap) {
+        B200_CUDA_OK(cudaStreamSynchronize(st));
+        cudaFree(h->shard_buf); h->shard_buf = nullptr; h->shard_cap = 0;
+        B200_CUDA_OK(cudaMalloc(&h->shard_buf, need_sh));
+        h->shard_cap = need_sh;
+    }
+    uint8_t* sb = static_cast<uint8_t*>(h->shard_buf);
+    unsigned long long* own = reinterpret_cast<unsigned long long*>(sb);
+    unsigned long long* all = own + nk;
+    long long* own_base = reinterpret_cast<long long*>(sb + bases_off);
+    long long* all_bases = reinterpret_cast<long long*>(sb + bases_off + 256);
+    if ((rc = h->ws_begin(st))) return rc;
+    if (N_local > 0) {
+        TopkPlan plan;
+        if ((rc = topk_plan(Q, N_local, k, &plan))) return rc;
+        const size_t need = plan.cand_bytes + plan.part_bytes + plan.qstage_bytes + 512;
+        if (need > h->topk_cap) {
+            B200_CUDA_OK(cudaStreamSynchronize(st));
+            cudaFree(h->topk_scratch); h->topk_scratch = nullptr; h->topk_cap = 0;
+            B200_CUDA_OK(cudaMalloc(&h->topk_scratch, need));
+            h->topk_cap = need;
+        }
+        if ((rc = topk_run(queries, gallery_shard, Q, N_local, D, k, 0, h->topk_scratch, plan, nullptr, nullptr, h->status, st, own))) return rc;
+        h->launches += plan.qstage_bytes ? 3 : 2;
+    } else {
+        B200_CUDA_OK(cudaMemsetAsync(own, 0, nk * 8, st));          // an empty shard contributes empty slots
+    }
+    B200_CUDA_OK(cudaMemcpyAsync(own_base, &index_base, 8, cudaMemcpyHostToDevice, st));   // (pageable source: copied before the call returns)
+    auto nccl_ok = [&](int r, const char* what) -> int {
+        if (r == 0) return B200_OK;
+        return fail(B200CLIP_ECUDA, std::string("search_sharded: ") + what + ": " + (nccl->error_string ? nccl->error_string(r) : "NCCL error"));
+    };
+    if ((rc = nccl_ok(nccl->group_start(), "ncclGroupStart"))) return rc;
+    int r1 = nccl->all_gather(own, all, nk, /*ncclUint64*/ 5, nccl_comm, st);
+    int r2 = nccl->all_gather(own_base, all_bases, 1, /*ncclInt64*/ 4, nccl_comm, st);
+    int r3 = nccl->group_end();
+    if ((rc = nccl_ok(r1, "ncclAllGather(keys)")) || (rc = nccl_ok(r2, "ncclAllGather(bases)")) || (rc = nccl_ok(r3, "ncclGroupEnd"))) return rc;
+    rc = merge_topk_keys_run(all, all_bases, world, Q, k, out_scores, reinterpret_cast<long long*>(out_index), st);
+    if (rc == B200_OK) h->launches += 1;
+    if (rc == B200_OK) rc = h->ws_end(st);
     return rc;
 }
 

@@ -388,6 +388,22 @@ class Engine:
                                                D, k, C.c_void_p(keys.data_ptr()), self._stream()))
         return keys
 
+    def search_sharded(self, queries_f16, gallery_shard_f16, k: int, index_base: int, nccl_comm: int, world: int):
+        """Sharded search in one C-ABI call on a raw ncclComm_t (an integer address): local top-k, grouped all-gather, merge.
+        Every rank gets the global ([Q,k] f32 scores, [Q,k] i64 indices)."""
+        torch = _torch()
+        Q, D = queries_f16.shape
+        N = 0 if gallery_shard_f16 is None else gallery_shard_f16.shape[0]
+        assert queries_f16.dtype == torch.float16 and queries_f16.is_contiguous()
+        assert N == 0 or (gallery_shard_f16.dtype == torch.float16 and gallery_shard_f16.is_contiguous())
+        scores = torch.empty((Q, k), dtype=torch.float32, device=queries_f16.device)
+        idx = torch.empty((Q, k), dtype=torch.int64, device=queries_f16.device)
+        _lib.check(self.lib.b200clip_search_sharded(self._h, C.c_void_p(queries_f16.data_ptr()), Q,
+                                                    C.c_void_p(gallery_shard_f16.data_ptr() if N else 0), N, D, k, int(index_base),
+                                                    C.c_void_p(nccl_comm), world, C.c_void_p(scores.data_ptr()), C.c_void_p(idx.data_ptr()),
+                                                    self._stream()))
+        return scores, idx
+
     def merge_topk_keys(self, part_keys, part_bases):
         """part_keys [P,Q,k] exchange keys, part_bases [P] int64 (cuda): index_base of every part -> merged ([Q,k] f32, [Q,k] i64)."""
         torch = _torch()

@@ -49,6 +49,39 @@ def _worker(rank, world, port, out_dir):
     s, i = dg.search(torch.from_numpy(qf.astype(np.float16)).cuda(), 10)
     eng.sync()
     out["c_s"], out["c_i"], out["c_rows"], out["c_q"] = s.cpu().numpy(), i.cpu().numpy(), dg.view().cpu().numpy(), qf
+    # (d) the one-call C-ABI form on a RAW ncclComm_t (what a caller without torch.distributed would hold): the communicator is made
+    # with ncclCommInitRank through ctypes on the libnccl torch has loaded; its unique id travels over the process group above
+    import ctypes as C
+    nccl = None
+    for cand in (os.path.join(os.path.dirname(torch.__file__), "..", "nvidia", "nccl", "lib", "libnccl.so.2"), "libnccl.so.2"):
+        try:
+            nccl = C.CDLL(cand); break
+        except OSError:
+            continue
+    if nccl is not None:
+        class UniqueId(C.Structure):
+            _fields_ = [("internal", C.c_byte * 128)]
+        uid = UniqueId()
+        if rank == 0:
+            assert nccl.ncclGetUniqueId(C.byref(uid)) == 0
+        t = torch.frombuffer(bytearray(bytes(uid)), dtype=torch.uint8).cuda()
+        dist.broadcast(t, 0)
+        C.memmove(C.byref(uid), bytes(t.cpu().numpy().tobytes()), 128)
+        comm = C.c_void_p()
+        nccl.ncclCommInitRank.argtypes = [C.POINTER(C.c_void_p), C.c_int, UniqueId, C.c_int]
+        assert nccl.ncclCommInitRank(C.byref(comm), world, uid, rank) == 0
+        g, q = out["b_g"], out["b_q"]
+        lo, hi = ShardedGallery.shard_bounds(g.shape[0], world, rank)
+        s, i = eng.search_sharded(torch.from_numpy(q).cuda(), torch.from_numpy(g[lo:hi].copy()).cuda(), 100, lo, comm.value, world)
+        eng.sync()
+        out["d_s"], out["d_i"] = s.cpu().numpy(), i.cpu().numpy()
+        # an empty shard on rank 1 (all rows on rank 0) must still give the global answer everywhere
+        shard = torch.from_numpy(g.copy()).cuda() if rank == 0 else None
+        s, i = eng.search_sharded(torch.from_numpy(q).cuda(), shard, 100, 0 if rank == 0 else g.shape[0], comm.value, world)
+        eng.sync()
+        out["e_s"], out["e_i"] = s.cpu().numpy(), i.cpu().numpy()
+        nccl.ncclCommDestroy.argtypes = [C.c_void_p]
+        nccl.ncclCommDestroy(comm)
     np.savez(os.path.join(out_dir, f"r{rank}.npz"), **out)
     eng.close()
     dist.destroy_process_group()
@@ -67,6 +100,11 @@ def test_sharded_gallery_world2_nccl(tmp_path):
         for r in (r0, r1):                                     # every rank holds the merged global answer
             assert np.array_equal(r[tag + "_i"], want_i), tag
             assert np.array_equal(r[tag + "_s"], want_s), tag
+    assert "d_i" in r0.files and "d_i" in r1.files, "libnccl not loadable through ctypes"
+    want_s, want_i = O.topk_cosine(r0["b_q"], r0["b_g"], 100)
+    for r in (r0, r1):                                         # b200clip_search_sharded on a raw communicator; with an empty shard
+        for tag in ("d", "e"):
+            assert np.array_equal(r[tag + "_i"], want_i) and np.array_equal(r[tag + "_s"], want_s), tag
     g16 = np.concatenate([r0["c_rows"], r1["c_rows"]])        # the rows as the device packed them (<= 1 fp16 ulp from the oracle's)
     assert g16.shape == (5000, 128)
     want_s, want_i = O.topk_cosine(r0["c_q"].astype(np.float16), g16, 10)

@@ -34,7 +34,8 @@ struct ImgDesc {
     const int* bounds_h; const int* kk_h;   // per output x of the resized width: (xmin, count), coefficients
     const int* bounds_v; const int* kk_v;
     int identity;                      // 0 = resize in preprocess_kernel, 1 = resized size == source size (pure crop + convert in
-                                       // convert_kernel), 2 = too wide / too tall for a shared-memory tile (the two global-memory kernels)
+                                       // convert_kernel), 2 = too wide / too tall for a shared-memory tile (the two global-memory kernels),
+                                       // 3 = more than 100 times taller than wide and shrinking vertically: vertical resize first, as PIL does
     int pad_[3];                       // sizeof == 80: pulled to the device as five 16-byte words
 };
 
@@ -420,6 +421,51 @@ __global__ void __launch_bounds__(256) vpass_global_kernel(PreParams p, ImgDesc 
     }
 }
 
+// PIL.Image.resize runs the VERTICAL resize first (a complete resize, rounded to 8 bits) when the source is more than 100 times taller
+// than wide and shrinks vertically; the bytes differ from horizontal-first.  Such strips take these two kernels: columns c_lo.. of the
+// source that the crop window's horizontal taps touch -> S rows of uint8, then the horizontal pass + normalise.  One thread per element.
+__global__ void __launch_bounds__(256) vfirst_v_kernel(const uint8_t* __restrict__ src, ImgDesc d, int S, int c_lo, int ncols,
+                                                       uint8_t* __restrict__ inter) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= S * ncols) return;
+    const int y = i / ncols, x = i - y * ncols, yo = d.top + y;
+    const int ymin = d.bounds_v[2 * yo], cnt = d.bounds_v[2 * yo + 1];
+    const int* k = d.kk_v + (size_t)yo * d.ksize_v;
+    const uint8_t* col = src + d.src_off + ((long long)ymin * d.w_in + (c_lo + x)) * 3;
+    int a0 = 1 << (PRECISION_BITS - 1), a1 = a0, a2 = a0;
+    for (int t = 0; t < cnt; ++t) {
+        const int w = k[t];
+        const uint8_t* q = col + (long long)t * d.w_in * 3;
+        a0 += q[0] * w; a1 += q[1] * w; a2 += q[2] * w;
+    }
+    uint8_t* o = inter + ((size_t)y * ncols + x) * 3;
+    o[0] = (uint8_t)clip8(a0); o[1] = (uint8_t)clip8(a1); o[2] = (uint8_t)clip8(a2);
+}
+template <bool BF16>
+__global__ void __launch_bounds__(256) vfirst_h_kernel(PreParams p, ImgDesc d, int b, int c_lo, int ncols, const uint8_t* __restrict__ inter) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x, S = p.S;
+    if (i >= S * S) return;
+    const int y = i / S, x = i - y * S, xo = d.left + x;
+    const int xmin = d.bounds_h[2 * xo], cnt = d.bounds_h[2 * xo + 1];
+    const int* k = d.kk_h + (size_t)xo * d.ksize_h;
+    const uint8_t* px = inter + ((size_t)y * ncols + (xmin - c_lo)) * 3;
+    int a0 = 1 << (PRECISION_BITS - 1), a1 = a0, a2 = a0;
+    for (int j = 0; j < cnt; ++j) {
+        const int w = k[j];
+        a0 += px[3 * j] * w; a1 += px[3 * j + 1] * w; a2 += px[3 * j + 2] * w;
+    }
+    int cstride;
+    const size_t idx = out_index(p, b, y, x, cstride);
+    const float f0 = p.lut[clip8(a0)], f1 = p.lut[256 + clip8(a1)], f2 = p.lut[512 + clip8(a2)];
+    if (BF16) {
+        __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(p.out);
+        o[idx] = __float2bfloat16_rn(f0); o[idx + cstride] = __float2bfloat16_rn(f1); o[idx + 2 * (size_t)cstride] = __float2bfloat16_rn(f2);
+    } else {
+        float* o = reinterpret_cast<float*>(p.out);
+        o[idx] = f0; o[idx + cstride] = f1; o[idx + 2 * (size_t)cstride] = f2;
+    }
+}
+
 // ------------------------------------------------------------------------------------------ host side
 struct AxisTable {
     int ksize = 0; int* d_bounds = nullptr; int* d_kk = nullptr; double scale = 1.0;   // both arrays live in one allocation (d_bounds)
@@ -571,7 +617,7 @@ int preprocess_run(PreprocessState* s, const uint8_t* src_dev, const long long* 
     const int inter_pitch = (S * 3 + 15) & ~15;
     constexpr int kMaxStage = 65536;                       // largest staging buffer of the tiled kernel
     auto rows_needed_for = [&](double vs, int tr) { return (int)std::ceil(vs * tr + 4.0 * (vs < 1 ? 1 : vs)) + 3; };
-    std::vector<const AxisTable*> vtab(B, nullptr);
+    std::vector<const AxisTable*> vtab(B, nullptr), htab(B, nullptr);
     int max_rowbytes = 0, max_ident_rowbytes = 0;
     for (int i = 0; i < B; ++i) {
         const int h = hw[2 * i], w = hw[2 * i + 1];
@@ -593,8 +639,9 @@ int preprocess_run(PreprocessState* s, const uint8_t* src_dev, const long long* 
             rc = get_table(s, h, new_h, &tv, st); if (rc) return rc;
             d.bounds_h = th->d_bounds; d.kk_h = th->d_kk; d.ksize_h = th->ksize;
             d.bounds_v = tv->d_bounds; d.kk_v = tv->d_kk; d.ksize_v = tv->ksize;
-            vtab[i] = tv;
-            if (w * 3 + 32 + 128 > kMaxStage) d.identity = 2;      // a source row does not fit a staging buffer
+            vtab[i] = tv; htab[i] = th;
+            if ((long long)h > (long long)w * 100 && new_h < h) d.identity = 3;      // PIL resizes such strips vertically first (see vfirst_v_kernel)
+            else if (w * 3 + 32 + 128 > kMaxStage) d.identity = 2;      // a source row does not fit a staging buffer
             else if (w * 3 > max_rowbytes) max_rowbytes = w * 3;
         } else if (w * 3 > max_ident_rowbytes) max_ident_rowbytes = w * 3;
     }
@@ -608,7 +655,7 @@ int preprocess_run(PreprocessState* s, const uint8_t* src_dev, const long long* 
         ImgDesc& d = hdesc[i];
         if (d.identity == 0 && (size_t)rows_needed_for(vtab[i]->scale, 1) * inter_pitch > budget) d.identity = 2;   // taps of ONE output row do not fit
         if (d.identity == 0) { any_resize = true; if (vtab[i]->scale > max_vscale) max_vscale = vtab[i]->scale; }
-        any_oversize |= d.identity == 2;
+        any_oversize |= d.identity >= 2;
     }
     pull_desc_kernel<<<(B * 5 + 255) / 256, 256, 0, st>>>(reinterpret_cast<const uint4*>(hdesc), reinterpret_cast<uint4*>(s->d_desc), B * 5);
     B200_CUDA_OK(cudaGetLastError());
@@ -639,6 +686,23 @@ int preprocess_run(PreprocessState* s, const uint8_t* src_dev, const long long* 
         PreParams p{src_dev, s->d_desc, s->d_lut, out_dev, S, 1, layout, out_bf16, P, layout ? S / P : 0, kpad, inter_pitch, 0};
         for (int i = 0; i < B; ++i) {
             const ImgDesc& d = hdesc[i];
+            if (d.identity == 3) {
+                const std::vector<int>& bh = htab[i]->h_bounds;
+                const int c_lo = bh[2 * d.left], c_hi = bh[2 * (d.left + S - 1)] + bh[2 * (d.left + S - 1) + 1], ncols = c_hi - c_lo;
+                const size_t need = (size_t)S * ncols * 3;
+                if (need > s->inter_cap) {
+                    B200_CUDA_OK(cudaStreamSynchronize(st));
+                    cudaFree(s->d_inter); s->d_inter = nullptr; s->inter_cap = 0;
+                    B200_CUDA_OK(cudaMalloc(&s->d_inter, need + need / 4));
+                    s->inter_cap = need + need / 4;
+                }
+                vfirst_v_kernel<<<(S * ncols + 255) / 256, 256, 0, st>>>(src_dev, d, S, c_lo, ncols, s->d_inter);
+                B200_CUDA_OK(cudaGetLastError());
+                if (out_bf16) vfirst_h_kernel<true><<<(S * S + 255) / 256, 256, 0, st>>>(p, d, i, c_lo, ncols, s->d_inter);
+                else vfirst_h_kernel<false><<<(S * S + 255) / 256, 256, 0, st>>>(p, d, i, c_lo, ncols, s->d_inter);
+                B200_CUDA_OK(cudaGetLastError());
+                continue;
+            }
             if (d.identity != 2) continue;
             const std::vector<int>& bv = vtab[i]->h_bounds;
             const int r_lo = bv[2 * d.top], r_hi = bv[2 * (d.top + S - 1)] + bv[2 * (d.top + S - 1) + 1];

@@ -82,6 +82,37 @@ void oracle_resize_bicubic_rgb(const uint8_t *src, int h_in, int w_in, uint8_t *
     int32_t *bh, *kh, *bv, *kv;
     int ksh = oracle_resample_coeffs(w_in, w_out, &bh, &kh);
     int ksv = oracle_resample_coeffs(h_in, h_out, &bv, &kv);
+    /* PIL.Image.Image.resize (Pillow >= 12, the reference's pin: packages/lumen-clip/pyproject.toml "pillow>=12.0.0"):
+     *     if self.size[1] > self.size[0] * 100 and size[1] < self.size[1]:   # very tall and narrow, shrinking vertically
+     *         im = self.im.resize((self.size[0], size[1]), ...); im = im.resize(size, ...)
+     * i.e. two complete resizes, VERTICAL FIRST, each rounding to 8 bits - the results differ from horizontal-first by up to
+     * ~12 grey levels (checked against Pillow 12.2.0 on 300 random sizes: this rule explains every difference). */
+    if ((long long)h_in > (long long)w_in * 100 && h_out < h_in) {
+        uint8_t *tv = (uint8_t *)malloc((size_t)h_out * w_in * 3);
+        for (int yy = 0; yy < h_out; yy++) {
+            int ymin = bv[yy * 2], cnt = bv[yy * 2 + 1];
+            const int32_t *k = kv + (size_t)yy * ksv;
+            for (int i = 0; i < w_in * 3; i++) {
+                int32_t ss = 1 << (PRECISION_BITS - 1);
+                for (int y = 0; y < cnt; y++) ss += (int32_t)src[(size_t)(y + ymin) * w_in * 3 + i] * k[y];
+                tv[(size_t)yy * w_in * 3 + i] = clip8(ss);
+            }
+        }
+        for (int y = 0; y < h_out; y++) {
+            const uint8_t *row = tv + (size_t)y * w_in * 3;
+            for (int xx = 0; xx < w_out; xx++) {
+                int xmin = bh[xx * 2], cnt = bh[xx * 2 + 1];
+                const int32_t *k = kh + (size_t)xx * ksh;
+                for (int c = 0; c < 3; c++) {
+                    int32_t ss = 1 << (PRECISION_BITS - 1);
+                    for (int x = 0; x < cnt; x++) ss += (int32_t)row[(x + xmin) * 3 + c] * k[x];
+                    dst[((size_t)y * w_out + xx) * 3 + c] = clip8(ss);
+                }
+            }
+        }
+        free(tv); free(bh); free(kh); free(bv); free(kv);
+        return;
+    }
     uint8_t *tmp = (uint8_t *)malloc((size_t)h_in * w_out * 3);
     for (int y = 0; y < h_in; y++) {
         const uint8_t *row = src + (size_t)y * w_in * 3;

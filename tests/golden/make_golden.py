@@ -43,6 +43,9 @@ def synth_image(seed: int, h: int, w: int) -> np.ndarray:
 PRE_CASES = [  # (seed, h_in, w_in, S)
     (1, 224, 224, 224), (2, 97, 131, 64), (3, 480, 640, 224), (4, 500, 333, 224),
     (5, 768, 1024, 64), (6, 50, 40, 64), (7, 1080, 1920, 224), (8, 336, 336, 336), (9, 700, 300, 336),
+    # more than 100 times taller than wide and shrinking vertically: PIL.Image.resize runs the VERTICAL resize first (two complete
+    # resizes); the last one is tall enough to take that branch under the shortest-side transform as well
+    (10, 1000, 7, 224), (11, 500, 3, 64), (12, 26000, 240, 224),
 ]
 
 

@@ -55,7 +55,9 @@ def test_preprocess_golden_bit_exact(golden_pre, mode):
 def test_preprocess_ragged_batch_and_layouts(eng224):
     from oracle import clip_oracle as O
     rng = np.random.default_rng(3)
-    sizes = [(224, 224), (31, 57), (640, 480), (480, 640), (1000, 200), (225, 224), (224, 223), (1080, 1920)]
+    # (the last three are more than 100 times taller than wide: PIL resizes those vertically first, and so must the device)
+    sizes = [(224, 224), (31, 57), (640, 480), (480, 640), (1000, 200), (225, 224), (224, 223), (1080, 1920), (1, 1), (2, 3), (1, 400),
+             (2300, 19), (701, 7), (700, 7), (450, 1)]
     imgs = [rng.integers(0, 256, (h, w, 3), dtype=np.uint8) for h, w in sizes]
     for mode in (0, 1):
         want = O.preprocess_batch(imgs, 224, mode)

@@ -22,6 +22,26 @@ def test_resize_crop_bit_exact(golden_pre):
         assert np.array_equal(u8, golden_pre[f"crop_u8_{n}"]), f"case {n}"
 
 
+def test_resize_matches_installed_pillow_on_random_sizes():
+    """The resize restatement against the dependency itself (Pillow, pinned >= 12 by the reference) on 120 random shapes: ordinary,
+    short and wide, and tall and narrow - where PIL.Image.resize switches to a vertical-first pair of resizes once the source is
+    more than 100 times taller than wide (found by exactly this kind of fuzz; the golden cases 9-11 pin it too)."""
+    Image = pytest.importorskip("PIL.Image")
+    rng = np.random.default_rng(8)
+    tall = 0
+    for n in range(120):
+        kind = n % 3
+        if kind == 0: h, w = int(rng.integers(1, 40)), int(rng.integers(50, 3000))
+        elif kind == 1: h, w = int(rng.integers(50, 3000)), int(rng.integers(1, 40))
+        else: h, w = int(rng.integers(1, 1200)), int(rng.integers(1, 1200))
+        S = int(rng.choice([64, 224, 336]))
+        img = rng.integers(0, 256, (h, w, 3), dtype=np.uint8)
+        want = np.asarray(Image.fromarray(img).resize((S, S), Image.Resampling.BICUBIC))
+        assert np.array_equal(O.resize_bicubic(img, S, S), want), (h, w, S)
+        tall += h > 100 * w and S < h
+    assert tall >= 5                                   # the vertical-first branch was exercised
+
+
 def test_closure_float_bit_exact(golden_pre):
     hit = 0
     for n, (seed, h, w, S) in enumerate(golden_pre["cases"]):

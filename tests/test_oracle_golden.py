@@ -42,6 +42,25 @@ def test_resize_matches_installed_pillow_on_random_sizes():
     assert tall >= 5                                   # the vertical-first branch was exercised
 
 
+def test_crop_mode_matches_installed_torchvision_on_random_sizes():
+    """Mode 1 (the open_clip transform of torch_backend.py:201-204 = torchvision Resize(S, BICUBIC) + CenterCrop(S) on a PIL image)
+    against torchvision itself: shortest side to S with int(S * long / short), round-half-even crop offsets, PIL's resize underneath."""
+    Image = pytest.importorskip("PIL.Image")
+    T = pytest.importorskip("torchvision.transforms")
+    rng = np.random.default_rng(9)
+    for n in range(60):
+        kind = n % 3
+        if kind == 0: h, w = int(rng.integers(8, 60)), int(rng.integers(60, 1500))
+        elif kind == 1: h, w = int(rng.integers(60, 1500)), int(rng.integers(8, 60))
+        else: h, w = int(rng.integers(8, 900)), int(rng.integers(8, 900))
+        S = int(rng.choice([64, 224]))
+        img = rng.integers(0, 256, (h, w, 3), dtype=np.uint8)
+        tf = T.Compose([T.Resize(S, interpolation=T.InterpolationMode.BICUBIC), T.CenterCrop(S)])
+        want = np.asarray(tf(Image.fromarray(img, "RGB")))
+        _, u8 = O.preprocess(img, S, mode=1, return_u8=True)
+        assert np.array_equal(u8, want), (h, w, S)
+
+
 def test_closure_float_bit_exact(golden_pre):
     hit = 0
     for n, (seed, h, w, S) in enumerate(golden_pre["cases"]):

@@ -309,6 +309,15 @@ def bench_search(D: Dist, pk: dict, quick: bool) -> dict:
         byts = n_local * GALLERY_DIM * 2 + Q * GALLERY_DIM * 2 + Q * SEARCH_K * 12
         sweep.append({"Q": Q, "rows": n_local, "ms": t, "queries_per_s": Q / t * 1e3, "hbm_gbs": byts / t / 1e6, "hbm_frac": byts / t / 1e6 / pk["hbm_gbs"]})
     out["small_batch_sweep"] = {"what": "K10+K12 on this rank's shard, k = 100; algorithmic bytes = rows*D*2 + Q*D*2 + Q*k*12", "peak_gbs": pk["hbm_gbs"], "runs": sweep}
+    # batches of a few query tiles (256 .. 1024 queries): between the two roofs, both fractions reported
+    mid = []
+    for Q in (256, 512, 1024):
+        q = q_all[:Q].contiguous()
+        t = D.timed(lambda: eng.topk(q, g, SEARCH_K, lo), iters=8, warm=3)
+        fl = 2.0 * Q * n_local * GALLERY_DIM
+        mid.append({"Q": Q, "rows": n_local, "ms": t, "queries_per_s": Q / t * 1e3, "tensor_frac_of_burst": fl / t / 1e9 / pk["bf16_burst"],
+                    "hbm_frac": (n_local * GALLERY_DIM * 2) / t / 1e6 / pk["hbm_gbs"]})
+    out["mid_batch_sweep"] = {"what": "K10+K12 on this rank's shard, k = 100, a few query tiles", "runs": mid}
     eng.close()
     del g, gal
     torch.cuda.empty_cache()

@@ -74,6 +74,8 @@ if b:
         L.append(f"* Q = 4096, k = 100: **{s['ms']:.2f} ms** = {s['queries_per_s']:.0f} queries/s; {s['roofline']['frac']:.3f} of the burst tensor peak "
                  f"({s['roofline']['frac_vs_sustained']:.3f} of sustained); phases: local top-k {s['local_topk_ms']:.2f} ms, all-gather {s['allgather_ms']:.3f} ms, merge {s['merge_ms']:.3f} ms.")
         L.append("* small batches on the same shard (HBM-bound): " + ", ".join(f"Q={x['Q']}: {x['ms']:.2f} ms = {x['hbm_frac']:.2f} of HBM" for x in s["small_batch_sweep"]["runs"]) + ".")
+        if "mid_batch_sweep" in s:
+            L.append("* a few query tiles, same shard: " + ", ".join(f"Q={x['Q']}: {x['ms']:.2f} ms = {x['tensor_frac_of_burst']:.2f} of the burst tensor peak / {x['hbm_frac']:.2f} of HBM" for x in s["mid_batch_sweep"]["runs"]) + ".")
         if "cpu_baseline" in s:
             L.append(f"* CPU baseline (reference per-request search, extrapolated): {s['cpu_baseline']['value']:.3f} queries/s on {s['cpu_baseline']['cores']} threads.\n")
     c = b.get("configs") or {}

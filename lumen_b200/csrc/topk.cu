@@ -867,9 +867,14 @@ static int merge_launch(const float* ps, const long long* pi, const unsigned lon
     // usually far shorter than its slice, so the kernel decides per query
     const int cache = (int)std::min<size_t>(T, 40 * 1024);
     const size_t smem = (size_t)cache * 4;
+    static const int mid_nt = [] { const char* e = getenv("B200_MERGE_MID"); return e ? atoi(e) : 512; }();
     if (Q <= 2 * kNumSMs) {
         if (smem > 32 * 1024) B200_CUDA_OK(cudaFuncSetAttribute(merge_topk_kernel<1024, KEYS_IN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         merge_topk_kernel<1024, KEYS_IN><<<Q, 1024, smem, st>>>(ps, pi, pkeys, bases, P, Q, k, cache, out_s, out_i, out_keys, key_base, counts, slot);
+    } else if (Q <= 10 * kNumSMs && mid_nt == 512) {
+        // a few CTAs per SM (the key cache bounds the occupancy, not the threads): longer CTAs shorten every pass of the latency chain
+        if (smem > 32 * 1024) B200_CUDA_OK(cudaFuncSetAttribute(merge_topk_kernel<512, KEYS_IN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        merge_topk_kernel<512, KEYS_IN><<<Q, 512, smem, st>>>(ps, pi, pkeys, bases, P, Q, k, cache, out_s, out_i, out_keys, key_base, counts, slot);
     } else {
         if (smem > 32 * 1024) B200_CUDA_OK(cudaFuncSetAttribute(merge_topk_kernel<256, KEYS_IN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         merge_topk_kernel<256, KEYS_IN><<<Q, 256, smem, st>>>(ps, pi, pkeys, bases, P, Q, k, cache, out_s, out_i, out_keys, key_base, counts, slot);

@@ -310,7 +310,10 @@ attention_tc_kernel(const __grid_constant__ CUtensorMap tmQKV, AttnParams p) {
                 tmem_ld_32x32(t_next, nlo);
                 tmem_ld_32x32(t_next + 32, nhi);
             }
-            exp32(hi, g, 16);
+            // the last key step of an image tower usually holds a handful of keys (S = 197: 5, S = 257: 1, S = 577: 1): the P V MMA of
+            // the step then reads 16 or 32 probability columns only (keys16), and the upper 32 need not be computed at all.  (Causal
+            // rows of one tile differ in how many keys they see, so there the columns are read and must be written.)
+            if (p.causal || p.S - kt * AT_KEYS > 32) exp32(hi, g, 16);
             l += (s4[0] + s4[1]) + (s4[2] + s4[3]);
             publish(g);
             if (has_next) {

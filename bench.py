@@ -400,17 +400,35 @@ def run_b200(args, cfg, weights, src_hw):
     eng = be.engine
     batches = device_batches(torch, D.dev, np.random.default_rng(1234 + rank), B, src_hw, copies=2)
     out_dev = torch.empty((B, cfg["embed_dim"]), dtype=torch.float32, device=D.dev)
+    # two batches in flight, as B200ClipBackend.embed_stream runs them: even batches on the engine, odd ones on its twin (same weights,
+    # own activations; b200clip_clone), each on a stream of its own, so that one batch's memory-bound kernels run under the other's GEMMs
+    twin = not args.single_stream
+    engs = [eng, eng.twin()] if twin else [eng, eng]
+    outs = [out_dev, torch.empty_like(out_dev)] if twin else [out_dev, out_dev]
+    side = [torch.cuda.Stream(device=D.dev), torch.cuda.Stream(device=D.dev)] if twin else None
 
     def step():
+        if not twin:
+            for j in range(R):
+                bt = batches[j & 1]
+                eng.embed_u8(bt["dev"], bt["offsets"], bt["hw"], 0, out=out_dev)
+            return
+        cur = torch.cuda.current_stream(D.dev)
+        for st in side:
+            st.wait_stream(cur)
         for j in range(R):
-            bt = batches[j & 1]
-            eng.embed_u8(bt["dev"], bt["offsets"], bt["hw"], 0, out=out_dev)
+            k = j & 1
+            bt = batches[k]
+            with torch.cuda.stream(side[k]):
+                engs[k].embed_u8(bt["dev"], bt["offsets"], bt["hw"], 0, out=outs[k])
+        for st in side:
+            cur.wait_stream(st)
 
     # ---- device-resident throughput (`value`): W warm-up steps, then K timed steps; no instrumentation inside
     for _ in range(args.warmup):
         step()
     eng.sync()
-    launches0 = eng.launches
+    launches0 = eng.launches + (engs[1].launches if twin else 0)
     sampler = ClockSampler(D.local) if rank == 0 else None
     D.barrier()
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
@@ -423,15 +441,17 @@ def run_b200(args, cfg, weights, src_hw):
     t_b = time.monotonic()
     ms = D.reduce_max(ev0.elapsed_time(ev1))
     clocks = sampler.stop(t_a, t_b) if sampler else None
-    launches = eng.launches - launches0
+    launches = eng.launches + (engs[1].launches if twin else 0) - launches0
     eng.sync()
 
-    # ---- roofline pass, after the timed region: CUDA events around every kernel launch of two more steps
+    # ---- roofline pass (one engine, one stream: every kernel timed on its own), after the timed region: CUDA events around every kernel launch of two more steps
     eng.profile_read()
     eng.profile(True)
     prof_batches = 0
     for _ in range(2):
-        step()
+        for j in range(R):
+            bt = batches[j & 1]
+            eng.embed_u8(bt["dev"], bt["offsets"], bt["hw"], 0, out=out_dev)
         prof_batches += R
     prof = eng.profile_read()
     eng.profile(False)
@@ -491,10 +511,12 @@ def run_b200(args, cfg, weights, src_hw):
             "ms_per_step": step_ms, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "bf16", "data": "synthetic",
             "config": workload_config(args, cfg, src_hw, world),
             "notes": {"l2": "per-batch working set ~0.9 GB (activations + 77 MB input, two input batches alternate) exceeds the 126 MB L2; no explicit flush",
-                      "timing": "CUDA events on the launch stream, barrier+synchronize both sides, max over ranks; no per-kernel events inside the timed region"},
+                      "timing": "CUDA events on the launch stream, barrier+synchronize both sides, max over ranks; no per-kernel events inside the timed region",
+                      "in_flight": ("two batches at a time (engine + twin sharing the weights, two streams that fork from / join the timed stream every step)"
+                                    if twin else "one batch at a time")},
             "e2e": {"value": images / (e2e_ms / 1e3), "unit": UNIT, "h2d_bytes_per_step": total_bytes * R, "d2h_bytes_per_step": int(B * cfg["embed_dim"] * 4) * R,
                     "wall_clock_value": images / (e2e_wall_ms / 1e3),
-                    "call": "B200ClipBackend.embed_stream (pinned host batches in, host float32 out; the upload of batch i+1 overlaps the encode of batch i)"},
+                    "call": "B200ClipBackend.embed_stream (pinned host batches in, host float32 out; the upload of batch i+1 overlaps the encode of batch i, two batches in flight on engine + twin)"},
             "gpu_launches": int(launches),
             "roofline": {"bound": "tensor", "kernel": "gemm_tc2_kernel / gemm_tc_kernel (tcgen05, all encoder GEMMs)", "achieved": achieved, "peak": peak,
                          "unit": "TFLOP/s", "frac": achieved / peak, "regime": regime,
@@ -534,6 +556,7 @@ def main():
     ap.add_argument("--batches-per-step", type=int, default=20, help="512-image batches per step (a step of ~0.1 s keeps 20 steps in the steady state)")
     ap.add_argument("--src", default="224x224", help="source image HxW")
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
+    ap.add_argument("--single-stream", action="store_true", help="one batch in flight instead of two (A/B against the default)")
     ap.add_argument("--skip-search", action="store_true", help="leave the gallery-search block out (development runs)")
     ap.add_argument("--skip-configs", action="store_true", help="leave the C1/C3/C4/K1 block out (development runs)")
     ap.add_argument("--quick", action="store_true", help="1.25 M-row gallery instead of 10 M (development runs; the line says so)")

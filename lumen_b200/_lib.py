@@ -39,6 +39,7 @@ SIGNATURES = {
     "b200clip_sync": (C.c_int, [_P, _P]),
     "b200clip_load_weight": (C.c_int, [_P, C.c_char_p, _P, C.POINTER(_I64), _I32]),
     "b200clip_finalize_weights": (C.c_int, [_P]),
+    "b200clip_clone": (C.c_int, [_P, C.POINTER(_P)]),
     "b200clip_preprocess": (C.c_int, [_P, _P, _P, _P, _I32, _I32, _I32, _I32, _P, _P]),
     "b200clip_encode": (C.c_int, [_P, _P, _I32, _P, _P]),
     "b200clip_embed_u8": (C.c_int, [_P, _P, _P, _P, _I32, _I32, _P, _P]),

@@ -9,6 +9,7 @@
 #include <algorithm>
 #include <cstdlib>
 #include <cstring>
+#include <memory>
 #include <mutex>
 #include <set>
 #include <string>
@@ -107,11 +108,21 @@ struct b200clip_handle {
         return ev_pool[ev_used++];
     }
 
+    // The image tower's weights live in a block that b200clip_clone()d handles share (freed with the last of them); everything else
+    // (activations, descriptors, scratch) is per handle.
+    struct WeightBlock {
+        std::vector<void*> allocs;
+        ~WeightBlock() { for (void* q : allocs) cudaFree(q); }
+    };
+    std::shared_ptr<WeightBlock> wblock;
+    bool alloc_into_wblock = false;
+    bool is_clone = false;
+
     template <class T> int alloc(T** p, size_t count, bool zero = false) {
         void* q = nullptr;
         B200_CUDA_OK(cudaMalloc(&q, count * sizeof(T) + 256));
         if (zero) B200_CUDA_OK(cudaMemset(q, 0, count * sizeof(T) + 256));
-        allocs.push_back(q);
+        if (alloc_into_wblock) wblock->allocs.push_back(q); else allocs.push_back(q);
         *p = reinterpret_cast<T*>(q);
         return B200_OK;
     }
@@ -140,6 +151,9 @@ static int set_device(b200clip_handle* h) {
 }
 
 extern "C" const char* b200clip_last_error(void) { return g_last_error.c_str(); }
+
+static int alloc_activations(b200clip_handle* h);
+static int require_encoder(b200clip_handle* h);
 
 extern "C" int b200clip_create(const b200clip_config* cfg, b200clip_handle** out) {
     B200_REQUIRE(cfg && out, "create: null argument");
@@ -172,6 +186,8 @@ extern "C" int b200clip_create(const b200clip_config* cfg, b200clip_handle** out
         const size_t Bm = cfg->max_batch, M = Bm * h->S, Mp = Bm * h->n;
         h->layers.resize(L);
 #define A_(call) if ((rc = (call))) return bail(rc)
+        h->wblock = std::make_shared<b200clip_handle::WeightBlock>();
+        h->alloc_into_wblock = true;
         A_(h->alloc(&h->w_patch, (size_t)d * h->kpad, true));
         A_(h->alloc(&h->w_proj, (size_t)D * d));
         A_(h->alloc(&h->cls, d)); A_(h->alloc(&h->pos, (size_t)h->S * d));
@@ -183,6 +199,22 @@ extern "C" int b200clip_create(const b200clip_config* cfg, b200clip_handle** out
             A_(h->alloc(&l.w_fc2, (size_t)d * mlp)); A_(h->alloc(&l.b_fc2, d));
             A_(h->alloc(&l.ln1_g, d)); A_(h->alloc(&l.ln1_b, d)); A_(h->alloc(&l.ln2_g, d)); A_(h->alloc(&l.ln2_b, d));
         }
+        h->alloc_into_wblock = false;
+        if ((rc = alloc_activations(h))) return bail(rc);
+#undef A_
+    }
+    *out = h;
+    return B200_OK;
+}
+
+// activations and per-handle scratch of the image tower (b200clip_create and b200clip_clone)
+static int alloc_activations(b200clip_handle* h) {
+    const b200clip_config* cfg = &h->cfg;
+    const int d = cfg->width, mlp = cfg->mlp_dim, D = cfg->embed_dim;
+    const size_t Bm = cfg->max_batch, M = Bm * h->S, Mp = Bm * h->n;
+    int rc;
+    {
+#define A_(call) if ((rc = (call))) return rc
         A_(h->alloc(&h->patches, Mp * h->kpad, true));     // K padding must read as zero
         A_(h->alloc(&h->patch_out, Mp * d));
         A_(h->alloc(&h->xres, M * d));
@@ -195,6 +227,30 @@ extern "C" int b200clip_create(const b200clip_config* cfg, b200clip_handle** out
         A_(h->alloc(&h->q_cls, Bm * d)); A_(h->alloc(&h->attn_cls, Bm * d)); A_(h->alloc(&h->mlp_cls, Bm * mlp));
 #undef A_
     }
+    return B200_OK;
+}
+
+extern "C" int b200clip_clone(b200clip_handle* src, b200clip_handle** out) {
+    int rc = set_device(src); if (rc) return rc;
+    B200_REQUIRE(out != nullptr, "clone: null argument");
+    std::lock_guard<std::mutex> lk(src->mu);
+    B200_REQUIRE(src->cfg.layers > 0, "clone: the handle has no image tower");
+    if ((rc = require_encoder(src))) return rc;
+    auto* h = new b200clip_handle();
+    h->cfg = src->cfg;
+    h->is_clone = true;
+    h->pre = preprocess_state_create(h->cfg.mean, h->cfg.std, &rc);
+    if (!h->pre) { delete h; return rc; }
+    auto bail = [&](int code) { b200clip_destroy(h); return code; };
+    if ((rc = h->alloc(&h->status, 1, true))) return bail(rc);
+    h->n = src->n; h->S = src->S; h->kpad = src->kpad;
+    // the weights: same device memory, kept alive by the shared block
+    h->wblock = src->wblock;
+    h->w_patch = src->w_patch; h->w_proj = src->w_proj; h->cls = src->cls; h->pos = src->pos;
+    h->pre_g = src->pre_g; h->pre_b = src->pre_b; h->post_g = src->post_g; h->post_b = src->post_b;
+    h->layers = src->layers;
+    h->loaded = src->loaded;
+    if ((rc = alloc_activations(h))) return bail(rc);
     *out = h;
     return B200_OK;
 }
@@ -341,6 +397,7 @@ static int load_text_weight(b200clip_handle* h, const std::string& nm, const flo
 extern "C" int b200clip_load_weight(b200clip_handle* h, const char* name, const float* data, const int64_t* shape, int32_t ndim) {
     int rc = set_device(h); if (rc) return rc;
     B200_REQUIRE(name && data && shape && ndim >= 1 && ndim <= 4, "load_weight: null argument or bad rank");
+    B200_REQUIRE(!h->is_clone, "load_weight: a cloned handle shares its source's weights; load them through the source");
     std::lock_guard<std::mutex> lk(h->mu);
     const std::string nm(name);
     if (nm.compare(0, 5, "text_") == 0) return load_text_weight(h, nm, data, shape, ndim);

@@ -3,6 +3,7 @@ pinned memory and to name the current CUDA stream; all arithmetic happens inside
 from __future__ import annotations
 
 import ctypes as C
+import os
 from collections.abc import Sequence
 
 import numpy as np
@@ -71,9 +72,31 @@ class Engine:
         self.text_cfg = None
         self._jpeg_dev = None
         self._pin_out = None
+        self._twin = None
 
     # ------------------------------------------------------------------ lifecycle
+    def clone(self) -> "Engine":
+        """A second engine on the same GPU sharing this one's image-tower weights, with activations and scratch of its own
+        (b200clip_clone): two batches can then be in flight on two streams.  Weights must be loaded first."""
+        other = object.__new__(Engine)
+        other.lib, other.cfg, other.device, other.image_size = self.lib, self.cfg, self.device, self.image_size
+        other.embed_dim, other.max_batch = self.embed_dim, self.max_batch
+        other._h = C.c_void_p()
+        _lib.check(self.lib.b200clip_clone(self._h, C.byref(other._h)))
+        other._pin_in = other._jpeg_dev = other._pin_out = other._twin = None
+        other.text_cfg = None
+        return other
+
+    def twin(self) -> "Engine":
+        """The engine `embed_stream` alternates with (made on first use, closed with this one)."""
+        if self._twin is None:
+            self._twin = self.clone()
+        return self._twin
+
     def close(self) -> None:
+        if getattr(self, "_twin", None) is not None:
+            self._twin.close()
+            self._twin = None
         if getattr(self, "_h", None) is not None and self._h:
             self.lib.b200clip_destroy(self._h)
             self._h = C.c_void_p()
@@ -291,65 +314,79 @@ class Engine:
         torch = _torch()
         dev = torch.device("cuda", self.device)
         caller = torch.cuda.current_stream(dev)
-        compute = torch.cuda.Stream(device=dev)
+        # Two batches in flight: even batches on this engine, odd ones on its twin (same weights, own activations), each on a compute
+        # stream of its own.  One handle serialises its calls; with two, the memory-bound kernels of one batch (LayerNorm, attention,
+        # out-projection) run under the tensor-bound GEMMs of the other (+4-5 % images/s at batch 512).  B200_STREAM_TWIN=0: one engine.
+        two = os.environ.get("B200_STREAM_TWIN", "1") != "0" and self.cfg.get("layers", 0) > 0
+        engines = [self, self.twin()] if two else [self, self]
+        computes = [torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)] if two else [torch.cuda.Stream(device=dev)] * 2
         copy = torch.cuda.Stream(device=dev)
-        compute.wait_stream(caller)
-        src = [None, None]; out = [None, None]; pin_out = [None, None]; meta = [None, None]
-        ready = [torch.cuda.Event(), torch.cuda.Event()]      # H2D of the slot finished
-        done = [torch.cuda.Event(), torch.cuda.Event()]       # D2H of the slot's result finished
+        for c in set(computes):
+            c.wait_stream(caller)
+        NS = 4 if two else 2                                   # buffer slots: two per engine, so an upload never waits for the engine it feeds
+        src = [None] * NS; out = [None] * NS; pin_out = [None] * NS; meta = [None] * NS
+        ready = [torch.cuda.Event() for _ in range(NS)]        # H2D of the slot finished
+        done = [torch.cuda.Event() for _ in range(NS)]         # D2H of the slot's result finished
 
         def stage(i, item):
             pinned, total, offsets, hw = item
-            s, need = i & 1, int(total)
+            s, need = i % NS, int(total)
             if src[s] is None or src[s].numel() < need:
                 src[s] = torch.empty(int(need * 1.25) + 64, dtype=torch.uint8, device=dev)
             with torch.cuda.stream(copy):
-                if i >= 2:
-                    # wait for the END of batch i-2 (its result download included), not just for its last read of the
-                    # slot: released any earlier, this big upload grabs the copy engine just before the next batch's
-                    # small descriptor upload becomes eligible and delays that batch's kernels by a whole transfer
+                if i >= NS:
+                    # wait for the END of the batch that used the slot (its result download included), not just for its last read of
+                    # the slot: released any earlier, this big upload grabs the copy engine just before the next batch's small
+                    # descriptor upload becomes eligible and delays that batch's kernels by a whole transfer
                     copy.wait_event(done[s])
                 src[s][:need].copy_(pinned[:need], non_blocking=True)
                 ready[s].record(copy)
             meta[s] = (np.ascontiguousarray(offsets, np.int64), np.ascontiguousarray(hw, np.int32))
 
         def launch(i):
-            s = i & 1
+            s, e = i % NS, i & 1
             offsets, hw = meta[s]
             B = int(len(offsets))
             if out[s] is None or out[s].shape[0] < B:
                 out[s] = torch.empty((B, self.embed_dim), dtype=torch.float32, device=dev)
                 pin_out[s] = torch.empty((B, self.embed_dim), dtype=torch.float32, pin_memory=True)
-            with torch.cuda.stream(compute):
-                compute.wait_event(ready[s])
-                self.embed_u8(src[s], offsets, hw, mode, out=out[s][:B])
+            with torch.cuda.stream(computes[e]):
+                computes[e].wait_event(ready[s])
+                engines[e].embed_u8(src[s], offsets, hw, mode, out=out[s][:B])
                 pin_out[s][:B].copy_(out[s][:B], non_blocking=True)
-                done[s].record(compute)
+                done[s].record(computes[e])
             return B
 
         it = iter(batches)
         pending = []                                           # (index, B): launched, result not yet yielded
-        nxt = next(it, None)
-        i = 0
-        if nxt is not None:
-            stage(0, nxt)
-        while nxt is not None:
-            cur_i = i
+        ahead = NS // 2                                        # uploads staged ahead of the launches
+        staged = []
+        for _ in range(ahead):
             nxt = next(it, None)
-            while pending and pending[0][0] <= cur_i - 2:      # this batch reuses the result buffers of batch cur_i - 2
+            if nxt is None:
+                break
+            stage(len(staged), nxt)
+            staged.append(True)
+        n_staged = len(staged)
+        i = 0
+        while i < n_staged:
+            while pending and pending[0][0] <= i - NS:         # this batch reuses the result buffers of batch i - NS
                 pi, pB = pending.pop(0)
-                done[pi & 1].synchronize()
-                yield pin_out[pi & 1][:pB].numpy().copy()
-            pending.append((cur_i, launch(cur_i)))
+                done[pi % NS].synchronize()
+                yield pin_out[pi % NS][:pB].numpy().copy()
+            pending.append((i, launch(i)))
+            nxt = next(it, None)
             if nxt is not None:
-                stage(cur_i + 1, nxt)                          # upload overlaps the encode of batch cur_i
+                stage(n_staged, nxt)                           # upload overlaps the encodes in flight (its slot is guarded on the device)
+                n_staged += 1
             i += 1
         for pi, pB in pending:
-            done[pi & 1].synchronize()
-            yield pin_out[pi & 1][:pB].numpy().copy()
-        with torch.cuda.stream(compute):
-            self.sync()
-        caller.wait_stream(compute)
+            done[pi % NS].synchronize()
+            yield pin_out[pi % NS][:pB].numpy().copy()
+        for e, c in {id(c): (e, c) for e, c in zip(engines, computes)}.values():
+            with torch.cuda.stream(c):
+                e.sync()
+            caller.wait_stream(c)
 
     # ------------------------------------------------------------------ classify / search
     def set_labels(self, labels: np.ndarray, slot: int = 0) -> None:

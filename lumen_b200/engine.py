@@ -357,36 +357,46 @@ class Engine:
                 done[s].record(computes[e])
             return B
 
-        it = iter(batches)
-        pending = []                                           # (index, B): launched, result not yet yielded
-        ahead = NS // 2                                        # uploads staged ahead of the launches
-        staged = []
-        for _ in range(ahead):
-            nxt = next(it, None)
-            if nxt is None:
-                break
-            stage(len(staged), nxt)
-            staged.append(True)
-        n_staged = len(staged)
-        i = 0
-        while i < n_staged:
-            while pending and pending[0][0] <= i - NS:         # this batch reuses the result buffers of batch i - NS
-                pi, pB = pending.pop(0)
+        finished = False
+        try:
+            it = iter(batches)
+            pending = []                                           # (index, B): launched, result not yet yielded
+            ahead = NS // 2                                        # uploads staged ahead of the launches
+            staged = []
+            for _ in range(ahead):
+                nxt = next(it, None)
+                if nxt is None:
+                    break
+                stage(len(staged), nxt)
+                staged.append(True)
+            n_staged = len(staged)
+            i = 0
+            while i < n_staged:
+                while pending and pending[0][0] <= i - NS:         # this batch reuses the result buffers of batch i - NS
+                    pi, pB = pending.pop(0)
+                    done[pi % NS].synchronize()
+                    yield pin_out[pi % NS][:pB].numpy().copy()
+                pending.append((i, launch(i)))
+                nxt = next(it, None)
+                if nxt is not None:
+                    stage(n_staged, nxt)                           # upload overlaps the encodes in flight (its slot is guarded on the device)
+                    n_staged += 1
+                i += 1
+            for pi, pB in pending:
                 done[pi % NS].synchronize()
                 yield pin_out[pi % NS][:pB].numpy().copy()
-            pending.append((i, launch(i)))
-            nxt = next(it, None)
-            if nxt is not None:
-                stage(n_staged, nxt)                           # upload overlaps the encodes in flight (its slot is guarded on the device)
-                n_staged += 1
-            i += 1
-        for pi, pB in pending:
-            done[pi % NS].synchronize()
-            yield pin_out[pi % NS][:pB].numpy().copy()
-        for e, c in {id(c): (e, c) for e, c in zip(engines, computes)}.values():
-            with torch.cuda.stream(c):
-                e.sync()
-            caller.wait_stream(c)
+            for e, c in {id(c): (e, c) for e, c in zip(engines, computes)}.values():
+                with torch.cuda.stream(c):
+                    e.sync()
+                caller.wait_stream(c)
+            finished = True
+        finally:
+            if not finished:
+                # the consumer stopped early (or a call failed): nothing may still be running on the side streams when the staging
+                # buffers of this generator are released
+                copy.synchronize()
+                for c in set(computes):
+                    c.synchronize()
 
     # ------------------------------------------------------------------ classify / search
     def set_labels(self, labels: np.ndarray, slot: int = 0) -> None:

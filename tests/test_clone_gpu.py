@@ -61,6 +61,12 @@ def test_embed_stream_with_twin_equals_single_engine(monkeypatch):
         want.append(eng.embed_host(imgs))
     got = list(eng.embed_stream(iter(items)))
     assert len(got) == len(want) and all(np.array_equal(g, w) for g, w in zip(got, want))
+    # a consumer that walks away after two results leaves nothing running behind it
+    gen = eng.embed_stream(iter(items))
+    first = [next(gen), next(gen)]
+    gen.close()
+    assert np.array_equal(first[0], want[0]) and np.array_equal(first[1], want[1])
+    assert all(np.array_equal(g, w) for g, w in zip(eng.embed_stream(iter(items)), want))
     monkeypatch.setenv("B200_STREAM_TWIN", "0")
     got1 = list(eng.embed_stream(iter(items)))
     assert all(np.array_equal(g, w) for g, w in zip(got1, want))

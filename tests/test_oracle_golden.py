@@ -137,3 +137,31 @@ def test_encoder_matches_transformers(golden_enc, name):
     np.testing.assert_allclose(emb, want, rtol=2e-4, atol=2e-4)
     cos = np.sum(O.l2_normalize(emb) * O.l2_normalize(want), axis=1)
     assert cos.min() > 0.999999
+
+
+def test_tower_oracle_matches_transformers_on_random_small_configs():
+    """The fp32 tower restatement against the class family the reference's torch backend runs (torch_backend.py:290-295:
+    transformers CLIPModel -> CLIPVisionModelWithProjection), live, on shapes and activations the goldens do not hold: exact GELU
+    (LAION open_clip weights) and QuickGELU, patch 14 / 16 / 32, odd head counts, embed_dim != width."""
+    torch = pytest.importorskip("torch")
+    tr = pytest.importorskip("transformers")
+    rng = np.random.default_rng(31)
+    for case in range(6):
+        heads = int(rng.choice([2, 3, 4, 6])); width = heads * 64
+        patch = int(rng.choice([14, 16, 32])); grid = int(rng.choice([2, 3, 4])); S = patch * grid
+        cfg = dict(image_size=S, patch=patch, width=width, layers=int(rng.choice([1, 2, 3])), heads=heads,
+                   mlp_dim=int(rng.choice([64, 192, 512])), embed_dim=int(rng.choice([32, 100, 512])),
+                   activation=str(rng.choice(["quick_gelu", "gelu"])), ln_eps=1e-5)
+        hf = tr.CLIPVisionConfig(hidden_size=width, intermediate_size=cfg["mlp_dim"], projection_dim=cfg["embed_dim"],
+                                 num_hidden_layers=cfg["layers"], num_attention_heads=heads, image_size=S, patch_size=patch,
+                                 hidden_act=cfg["activation"], layer_norm_eps=1e-5)
+        model = tr.CLIPVisionModelWithProjection(hf).eval()
+        w = synthetic_weights(cfg, seed=case)
+        missing, unexpected = model.load_state_dict({k: torch.from_numpy(v) for k, v in w.items()}, strict=False)
+        assert not unexpected and all("position_ids" in m for m in missing)
+        px = rng.standard_normal((3, 3, S, S)).astype(np.float32)
+        with torch.no_grad():
+            want = model(pixel_values=torch.from_numpy(px)).image_embeds.numpy()
+        want = want / np.linalg.norm(want, axis=1, keepdims=True)
+        got = O.vit_encode(w, px, cfg)
+        np.testing.assert_allclose(got, want, atol=3e-6, err_msg=str(cfg))

@@ -68,6 +68,11 @@ if b:
             agg[key] += t; tot += t
         L.append(f"* ncu launch list (`launches_{TAG}.csv`) shares of one pass: " + ", ".join(f"{k} {v / tot:.3f}" for k, v in agg.most_common()) +
                  " - agrees with the CUDA-event shares above.\n")
+    two, single = one(f"bench_{TAG}_two_in_flight.json"), one(f"bench_{TAG}_single_stream.json")
+    if two and single:
+        L.append(f"* two batches in flight against one, same box, back to back (`bench_{TAG}_two_in_flight.json`, `bench_{TAG}_single_stream.json`): "
+                 f"{two['value']:.0f} vs {single['value']:.0f} images/s device-resident ({two['value'] / single['value'] - 1:+.1%}), "
+                 f"{two['e2e']['value']:.0f} vs {single['e2e']['value']:.0f} end to end ({two['e2e']['value'] / single['e2e']['value'] - 1:+.1%}).\n")
     s = b.get("search")
     if s:
         L.append(f"## Search block of the same line (BASELINE configs[4] on {s['n_gpus']} GPU: {s['rows_per_gpu']} rows per GPU)\n")

@@ -418,6 +418,9 @@ class Engine:
         N = gallery_f16.shape[0]
         assert queries_f16.dtype == torch.float16 and gallery_f16.dtype == torch.float16
         assert queries_f16.is_contiguous() and gallery_f16.is_contiguous()
+        if N == 0:                                              # an empty shard (more ranks than rows): nothing to report
+            return (torch.full((Q, k), float("-inf"), dtype=torch.float32, device=queries_f16.device),
+                    torch.full((Q, k), -1, dtype=torch.int64, device=queries_f16.device))
         scores = torch.empty((Q, k), dtype=torch.float32, device=queries_f16.device)
         idx = torch.empty((Q, k), dtype=torch.int64, device=queries_f16.device)
         _lib.check(self.lib.b200clip_topk(self._h, C.c_void_p(queries_f16.data_ptr()), Q, C.c_void_p(gallery_f16.data_ptr()), N, D, k,
@@ -430,6 +433,8 @@ class Engine:
         Q, D = queries_f16.shape
         assert queries_f16.dtype == torch.float16 and gallery_f16.dtype == torch.float16
         assert queries_f16.is_contiguous() and gallery_f16.is_contiguous()
+        if gallery_f16.shape[0] == 0:                           # an empty shard contributes empty slots (key 0)
+            return torch.zeros((Q, k), dtype=torch.int64, device=queries_f16.device)
         keys = torch.empty((Q, k), dtype=torch.int64, device=queries_f16.device)
         _lib.check(self.lib.b200clip_topk_keys(self._h, C.c_void_p(queries_f16.data_ptr()), Q, C.c_void_p(gallery_f16.data_ptr()), gallery_f16.shape[0],
                                                D, k, C.c_void_p(keys.data_ptr()), self._stream()))

@@ -371,6 +371,27 @@ def test_topk_exchange_keys_merge_like_a_sharded_search():
     eng.close()
 
 
+def test_topk_empty_shard_contributes_nothing():
+    """More ranks than gallery rows leave some shards empty: their part is all empty slots and the merge ignores it."""
+    from lumen_b200.engine import Engine
+    from oracle import clip_oracle as O
+    eng = Engine({}, device=0)
+    rng = np.random.default_rng(4)
+    g = rng.integers(-8, 9, (300, 64)).astype(np.float16); q = rng.integers(-8, 9, (7, 64)).astype(np.float16)
+    gt, qt = torch.from_numpy(g).cuda(), torch.from_numpy(q).cuda()
+    s0, i0 = eng.topk(qt, gt[:0].contiguous(), 10)
+    assert bool((i0 == -1).all()) and bool(torch.isinf(s0).all())
+    keys = torch.stack([eng.topk_keys(qt, gt[:0].contiguous(), 10), eng.topk_keys(qt, gt, 10)])
+    ms, mi = eng.merge_topk_keys(keys, torch.tensor([0, 5], dtype=torch.int64, device="cuda"))
+    so, io = O.topk_cosine(q, g, 10, index_base=5)
+    eng.sync()
+    assert np.array_equal(mi.cpu().numpy(), io) and np.array_equal(ms.cpu().numpy(), so)
+    ps, pi = eng.merge_topk(torch.stack([s0, eng.topk(qt, gt, 10, 5)[0]]), torch.stack([i0, eng.topk(qt, gt, 10, 5)[1]]))
+    eng.sync()
+    assert np.array_equal(pi.cpu().numpy(), io) and np.array_equal(ps.cpu().numpy(), so)
+    eng.close()
+
+
 def test_topk_exact_zero_scores_across_splits():
     """Scores of exactly +0.0 (zero / padding rows, a zero query) tie across the gallery splits that share a threshold: the
     k smallest indices must win, every run (the shared bound must not exclude scores equal to it)."""

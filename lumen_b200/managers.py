@@ -99,7 +99,11 @@ class B200CLIPModelManager:
                                "Ensure ImageNet_1k.npz exists in the model directory.")
         if self.text_embeddings is None:
             raise RuntimeError("Text embeddings are not available")
-        vals, idx = self.classify_embeddings(self.encode_image(image_bytes), top_k)
+        emb = self.encode_image(image_bytes)
+        if top_k == 0:                                   # `sorted_idx[:0]` in the reference: an empty list, after the same guards
+            self.classify_embeddings(emb, 1)
+            return []
+        vals, idx = self.classify_embeddings(emb, min(int(top_k), len(self.labels)))
         return [(self.labels[int(i)], float(v)) for v, i in zip(vals[0], idx[0]) if i >= 0]
 
     def classify_images(self, images: Sequence[bytes], top_k: int = 5) -> list[list[tuple[str, float]]]:
@@ -268,5 +272,8 @@ class B200BioCLIPModelManager:
                                "Ensure TreeOfLife dataset exists in the model directory.")
         if self._gallery is None:
             raise RuntimeError("Text embeddings are not available")
-        s, i = self.search_embeddings(self.encode_image(image_bytes), top_k)
+        emb = self.encode_image(image_bytes)
+        if top_k == 0:                                   # `[:0]` in the reference
+            return []
+        s, i = self.search_embeddings(emb, top_k)
         return [(self.extract_name(self.labels[int(j)]), float(v)) for v, j in zip(s[0], i[0]) if j >= 0]

@@ -42,7 +42,11 @@ def _worker(rank, world, port, out_dir):
     lo, hi = ShardedGallery.shard_bounds(N, world, rank)
     gal = ShardedGallery(OracleEngine(), torch.from_numpy(g[lo:hi].copy()), index_base=lo)
     s, i = gal.search(torch.from_numpy(q), k)
-    np.savez(os.path.join(out_dir, f"r{rank}.npz"), s=s.numpy(), i=i.numpy(), g=g, q=q)
+    # a gallery of ONE row over two ranks: rank 1's shard is empty and contributes only empty slots
+    lo1, hi1 = ShardedGallery.shard_bounds(1, world, rank)
+    tiny = ShardedGallery(OracleEngine(), torch.from_numpy(g[lo1:hi1].copy()), index_base=lo1)
+    s1, i1 = tiny.search(torch.from_numpy(q), 3)
+    np.savez(os.path.join(out_dir, f"r{rank}.npz"), s=s.numpy(), i=i.numpy(), g=g, q=q, s1=s1.numpy(), i1=i1.numpy(), empty=np.array(hi1 - lo1))
     dist.destroy_process_group()
 
 
@@ -56,3 +60,7 @@ def test_sharded_gallery_world2_gloo(tmp_path):
     want_s, want_i = O.topk_cosine(r0["q"], r0["g"], 20)
     for r in (r0, r1):                                     # every rank holds the merged global answer
         assert np.array_equal(r["i"], want_i) and np.array_equal(r["s"], want_s)
+    assert int(r0["empty"]) == 1 and int(r1["empty"]) == 0
+    w1s, w1i = O.topk_cosine(r0["q"], r0["g"][:1], 3)
+    for r in (r0, r1):
+        assert np.array_equal(r["i1"], w1i) and np.array_equal(r["s1"], w1s)

@@ -31,6 +31,7 @@ L.append("Produced by `profiles/capture_r2.sh` on one B200 (`gpurun`), summarise
 L.append("| file | what |\n|---|---|")
 L.append(f"| `bench_{TAG}.json` / `bench_{TAG}_reference.json` | `python bench.py --steps 20 --warmup 5` and `--impl reference` lines |")
 L.append(f"| `bench_{TAG}_n2.json`, `_n4.json`, `_n8.json` | the same line under torchrun on 2 / 4 / 8 GPUs of one box (NCCL): weak-scaling embed, strong-scaling search and C2 |")
+L.append(f"| `bench_{TAG}_two_in_flight.json`, `bench_{TAG}_single_stream.json` | the headline part of the line twice on one box, back to back: two batches in flight (the default) and `--single-stream` |")
 L.append(f"| `paths_{TAG}.jsonl`, `paths_search10m_{TAG}.jsonl` | `bench_paths.py` per-kernel lines (search sweep on a 1.25 M-row shard and on 10 M rows) |")
 L.append(f"| `launches_{TAG}.csv` | ncu `gpu__time_duration.sum` for every launch of one 512-image pass (cold cache, serialised: compare shares) |")
 L.append(f"| `step_{TAG}_ncu.csv` | `--set full` metrics of the per-layer kernels (GEMM shapes, attention_short_kernel, LayerNorm) |")

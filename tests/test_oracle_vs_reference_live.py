@@ -119,3 +119,15 @@ def test_bioclip_manager_live(ref):
             idx, sc = O.bioclip_classify_image(be.vec, g, k)
             assert [int(l.split("_")[1]) for l, _ in got] == list(idx), (N, D, k)
             np.testing.assert_allclose([s for _, s in got], sc, rtol=1e-5, atol=1e-7)
+
+
+def test_extract_name_matches_the_reference(ref):
+    """`B200BioCLIPModelManager.extract_name` against the reference's static method on every label shape a TreeOfLife file can hold
+    (and a few it should not): host-only, so it runs wherever the reference tree is."""
+    from lumen_b200.managers import B200BioCLIPModelManager as M
+    R = ref["Bio"]
+    cases = ["sp_3", "", ["a", "b", "c"], [["Animalia", "Chordata", "Panthera", "leo"], "Lion"], [["Animalia", "Chordata", "Panthera", "leo"], ""],
+             [["Animalia", "Chordata", "Panthera", "leo"], "   "], [["leo"], ""], [[], ""], [["x", "y"], None], [["x", "y"], 7], ["tax", "Common"],
+             [("a", "b"), ""], [["a", "b"], "\t\n"], [["a", "b", "c"], " Tiger "], [None, None], [[1, 2], ""]]
+    for c in cases:
+        assert M.extract_name(c) == R.extract_name(c), c

@@ -131,3 +131,11 @@ def test_extract_name_matches_the_reference(ref):
              [("a", "b"), ""], [["a", "b"], "\t\n"], [["a", "b", "c"], " Tiger "], [None, None], [[1, 2], ""]]
     for c in cases:
         assert M.extract_name(c) == R.extract_name(c), c
+
+
+def test_scene_prompts_match_the_reference(ref):
+    from lumen_b200.managers import B200CLIPModelManager as M
+    be = ref["FakeBackend"]()
+    be.scene = np.zeros((8, 4), np.float32)
+    mgr = ref["CLIP"](be, ref["Res"](np.array(["a"], dtype=object), np.ones((1, 4), np.float32)))
+    assert list(M.scene_prompts) == list(mgr.scene_prompts)
